@@ -1,0 +1,156 @@
+"""CPU oracle for the light-curtain planning / sensing glue and the Bayesian LC loop
+(TEST INFRASTRUCTURE — never imported by the product).
+
+Restates lc/light_curtain.py (FieldWarp :18-204, plan_default :646-739, sense_high :820-910)
+and BaseModel.lc_process (models/models.py:980-1129) for the configuration the KITTI-sim
+path builds (rTc = I, zero distortion, lTc = x+0.2 m; light_curtain.py:343-371), on top of the
+restated lcsim in oracle/lcsim.py.  Pinned against the unmodified reference module by
+tests/golden/make_golden.py (which drives the reference's LightCurtain class on the same
+oracle lcsim back end).
+"""
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from . import dpv_oracle as O
+from . import lcsim
+
+
+def digitize_soft(val, arr):
+    """FieldWarp.digitize_soft, light_curtain.py:60-77."""
+    pos = int(np.digitize([val], arr)[0]) - 1
+    if abs(val - arr[-1]) < 1e-7:
+        return len(arr) - 1
+    if abs(val - arr[0]) < 1e-7:
+        return 0
+    if pos == len(arr) - 1:
+        return 100000000
+    if pos == -1:
+        return -100000000
+    lp, rp = arr[pos], arr[pos + 1]
+    return pos + 1.0 * (float(val - lp) / float(rp - lp))
+
+
+def polar_flowfield(angles, d_candi, r_candi):
+    """FieldWarp._ztheta2zrange, light_curtain.py:87-116: flow [1,R,W,2] (float32 store)."""
+    R, W = len(r_candi), len(angles)
+    flow = torch.zeros((1, R, W, 2))
+    for r in range(R):
+        for c in range(W):
+            rng, theta = r_candi[r], angles[c]
+            zval = rng * np.cos(np.radians(theta))
+            flow[0, r, c, 0] = c - digitize_soft(theta, angles)
+            flow[0, r, c, 1] = r - digitize_soft(zval, d_candi)
+    return flow
+
+
+def flow_warp(field, flow):
+    """FieldWarp.warp, light_curtain.py:47-58."""
+    ax = torch.arange(0, field.shape[0]).float()
+    bx = torch.arange(0, field.shape[1]).float()
+    yv, xv = torch.meshgrid([ax, bx], indexing="ij")
+    ystep = 2.0 / float(field.shape[0] - 1)
+    xstep = 2.0 / float(field.shape[1] - 1)
+    g = torch.zeros(flow.shape)
+    g[0, :, :, 0] = -1 + xv * xstep - flow[0, :, :, 0] * xstep
+    g[0, :, :, 1] = -1 + yv * ystep - flow[0, :, :, 1] * ystep
+    return F.grid_sample(field.unsqueeze(0).unsqueeze(0), g, mode="bilinear", padding_mode="zeros",
+                         align_corners=False).squeeze(0).squeeze(0)
+
+
+def invert(x, p=0.5):
+    """light_curtain.py:221-225."""
+    return ((x ** p) * ((1 - x) ** (1 - p))) / ((p ** p) * ((1 - p) ** (1 - p)))
+
+
+class LightCurtainOracle:
+    """LightCurtain (light_curtain.py:255-373) reduced to the 'high' device of the KITTI-sim set-up."""
+
+    def __init__(self, K_up, W, H, d_candi, d_candi_up, hit_noise=0.0, laser_timestep=3.5e-5, laser_fov=80.0):
+        self.W, self.H = int(W), int(H)
+        self.K = np.asarray(K_up, np.float32)
+        self.d_candi = np.asarray(d_candi)
+        self.d_candi_up = np.asarray(d_candi_up)
+        self.r_candi_up = self.d_candi_up
+        lTc = np.eye(4, dtype=np.float32)
+        lTc[0, 3] = 0.2                                             # light_curtain.py:357-362
+        self.dev = lcsim.LCDevice(
+            CAMERA_PARAMS=dict(width=self.W, height=self.H, matrix=self.K, distortion=[0.] * 5,
+                               hit_mode=1, hit_noise=hit_noise),
+            LASER_PARAMS=dict(lTc=lTc, fov=laser_fov, laser_timestep=laser_timestep))
+        self.planner = lcsim.PlannerRT(self.dev, self.r_candi_up, self.W)
+        self.angles = np.array(lcsim.generateCameraAngles(self.K, None, self.W, self.H))
+        self._flow = None
+
+    def flow(self):
+        if self._flow is None:
+            self._flow = polar_flowfield(self.angles, self.d_candi_up, self.r_candi_up)
+        return self._flow
+
+    # ---- plan_default, light_curtain.py:646-739 -------------------------------------------
+    def prepare_field(self, field):
+        """field [D,W] (mutated in place like the reference) -> (field_pre [R,W], field_range [R,W])."""
+        field[:, 0] = field[:, 1]                                    # :654-655
+        field[:, -1] = field[:, -2]
+        for i in range(field.shape[1]):                              # :658-662
+            if torch.isnan(field[:, i]).any():
+                field[:, i] = O.EPS
+                field[-1, i] = 1.0
+        f = F.interpolate(field.unsqueeze(0).unsqueeze(0), size=[len(self.d_candi_up), self.W],
+                          mode="bilinear", align_corners=False)      # preprocess :79-85
+        k = torch.zeros(5, 5)
+        k[:, 2] = 1 / 5.0                                            # create_mean_kernel :213-218
+        f = F.conv2d(f, k.reshape(1, 1, 5, 5), padding=2).squeeze(0).squeeze(0)
+        lo, _ = f.unsqueeze(0).min(1)                                # normalize :207-210
+        hi, _ = f.unsqueeze(0).max(1)
+        f = ((f.unsqueeze(0) - lo) / (hi - lo)).squeeze(0)
+        f[torch.isnan(f)] = O.EPS                                    # :681
+        return f, flow_warp(f, self.flow())                          # :684
+
+    def split_fields(self, frange, steps):
+        """:695-708 -> list of umaps [main, (left_p, right_p) for p in steps], and the argmax row."""
+        left, right = frange.clone(), frange.clone()
+        _, idx = torch.max(frange, 0)
+        R = frange.shape[0]
+        rows = torch.arange(R).unsqueeze(1)
+        left[rows < idx.unsqueeze(0)] = 1.0
+        right[rows >= idx.unsqueeze(0)] = 1.0
+        out = [frange]
+        for p in steps:
+            out.append(invert(left, p=p))
+            out.append(invert(right, p=p))
+        return out, idx
+
+    def plan(self, field, steps, return_indices=False):
+        _, frange = self.prepare_field(field)
+        umaps, idx = self.split_fields(frange, steps)
+        paths = [self.planner.get_design_points(u.numpy(), return_indices) for u in umaps]
+        return paths, umaps, idx
+
+    # ---- sense_high, light_curtain.py:820-910 (rTc = I) -----------------------------------
+    def sense(self, depth_gt, pts, noise=None):
+        img, th = self.dev.get_return(depth_gt, pts, True, noise=noise)
+        img[np.isnan(img[:, :, 0])] = 0                              # :847-848
+        th[np.isnan(th)] = 0
+        return O.curtain_likelihood(self.d_candi, depth_gt, img[:, :, 2], img[:, :, 3], th), img, th
+
+
+def lc_loop(logp, depth_gt, lc, K_up, uf_par, iterations, steps, spread_iter, spread_n, trace=None):
+    """BaseModel.lc_process body for ONE sample, mode='high', planner='default'
+    (models/models.py:1010-1127).  logp [1,D,H,W] log-DPV; depth_gt [H,W] numpy (already x4 nearest).
+    Returns fused log-DPV [1,D,H,W]."""
+    K = torch.as_tensor(K_up).float()
+    start = logp
+    final = logp.detach().clone()
+    if final.shape[1] != len(lc.d_candi):
+        final = O.resample_depth_bins(final, N=len(lc.d_candi), BV_log=True)   # :1015-1016
+    for it in range(iterations):
+        uf, _ = O.ufield(final, lc.d_candi, K, uf_par, BV_log=True)           # :1029
+        paths, umaps, idx = lc.plan(uf.squeeze(0), steps, return_indices=True)  # :1050
+        liks = [lc.sense(depth_gt, p[0])[0] for p in paths]                    # :1066
+        final = O.bayes_fuse(final, liks, spread_iter, spread_n)              # :1097-1122
+        if trace is not None:
+            trace.append(dict(uf=uf, ks=[p[1] for p in paths], umaps=umaps, argmax=idx, logp=final))
+    if final.shape[1] != start.shape[1]:
+        final = O.resample_depth_bins(final, N=start.shape[1], BV_log=True)   # :1124
+    return final

@@ -1,0 +1,208 @@
+"""Generate tests/golden/*.npz by running the UNMODIFIED reference (imported from /root/reference,
+CPU) on seeded inputs.  Run in the build container only:  python tests/golden/make_golden.py
+
+Each case stores the inputs and the reference's outputs; tests/test_oracle_golden.py replays the
+inputs through oracle/ and compares (no /root/reference needed there).  The lcsim C++ cannot be
+built here, so for the light-curtain cases the reference's lc/light_curtain.py and
+BaseModel.lc_process run on top of oracle/lcsim.py's restated LCDevice/PlannerRT: those goldens
+pin the Python half of the LC path, not lcsim itself.
+"""
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, HERE)
+sys.path.insert(0, ROOT)
+
+import ref_shim  # noqa: E402
+
+H_, IU = ref_shim.load()
+from oracle import lcsim  # noqa: E402
+
+torch.set_num_threads(1)
+
+
+def intrinsics(w, h, hfov=80.4, vfov=27.0):
+    """kittiloader/kitti.py:367-379 style low-res K + unit rays (warping/view.py:32-62)."""
+    fx = (w / 2) / np.tan(np.radians(hfov / 2))
+    fy = (h / 2) / np.tan(np.radians(vfov / 2))
+    K = np.array([[fx, 0, w / 2], [0, fy, h / 2], [0, 0, 1]], np.float32)
+    xs = np.tan(np.radians(hfov / 2)) * (2 * (np.arange(w) + 0.5) / w - 1)
+    ys = np.tan(np.radians(vfov / 2)) * (2 * (np.arange(h) + 0.5) / h - 1)
+    rays = np.stack([np.tile(xs, h), np.repeat(ys, w), np.ones(h * w)], 0).astype(np.float32)
+    return K, rays
+
+
+def rot(rx, ry, rz):
+    cx, sx, cy, sy, cz, sz = np.cos(rx), np.sin(rx), np.cos(ry), np.sin(ry), np.cos(rz), np.sin(rz)
+    Rx = np.array([[1, 0, 0], [0, cx, -sx], [0, sx, cx]])
+    Ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+    Rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]])
+    return (Rz @ Ry @ Rx).astype(np.float32)
+
+
+def save(name, **kw):
+    np.savez_compressed(os.path.join(HERE, name + ".npz"),
+                        **{k: (v.numpy() if torch.is_tensor(v) else np.asarray(v)) for k, v in kw.items()})
+    print("wrote", name, {k: tuple(np.shape(v)) for k, v in kw.items()})
+
+
+def case_sweep():
+    g = torch.Generator().manual_seed(1)
+    C, h, w, D, V = 7, 12, 16, 8, 2
+    K, rays = intrinsics(w, h)
+    ref = torch.randn(1, C, h, w, generator=g)
+    src = torch.randn(1, V, C, h, w, generator=g)
+    R = torch.tensor(np.stack([rot(0.002, 0.015, -0.003), rot(-0.003, -0.01, 0.002)]))
+    t = torch.tensor([[0.04, -0.015, -0.9], [-0.54, 0.0, 0.0]], dtype=torch.float32)
+    d = IU.powerf(5., 40., D, 1.0)
+    cam = {"intrinsic_M_cuda": torch.tensor(K), "intrinsic_M": K, "unit_ray_array_2D": torch.tensor(rays)}
+    l2 = H_.est_swp_volume_v4(ref, src, d, R, t, cam, 10.0, feat_dist="L2")
+    l1 = H_.est_swp_volume_v4(ref, src, d, R, t, cam, 10.0, feat_dist="L1")
+    fsrc = torch.randn(1, 3, D, h, w, generator=g)
+    R3 = torch.cat([R, torch.eye(3).unsqueeze(0)])
+    t3 = torch.cat([t, torch.zeros(1, 3)])
+    wf = H_.warp_feature(fsrc, d, R3, t3, cam)
+    save("sweep", ref=ref, src=src, R=R, t=t, K=K, rays=rays, d_candi=d, sigma=10.0, cost_l2=l2, cost_l1=l1,
+         fsrc=fsrc, R3=R3, t3=t3, warped=wf)
+
+
+def case_dpv_utils():
+    g = torch.Generator().manual_seed(2)
+    D, H, W = 8, 32, 48
+    d = IU.powerf(5., 40., D, 1.0)
+    K = np.array([[28.4, 0, 24], [0, 66.6, 16], [0, 0, 1]], np.float32)
+    # peaky DPV whose expected depth falls in the road band for part of the image
+    depth = torch.linspace(6, 38, H).unsqueeze(1).repeat(1, W).flip(0) + torch.rand(H, W, generator=g)
+    logits = -((torch.tensor(d).float().reshape(D, 1, 1) - depth) ** 2) / 8.0 + 0.3 * torch.randn(D, H, W, generator=g)
+    logp = torch.log_softmax(logits, 0).unsqueeze(0)
+    out = {}
+    for key in ("kitti", "sweep"):
+        cfg = ref_shim.AttrDict({"data": {"dataset_path": "/data/%s/x" % key}})
+        uf, dz = IU.gen_ufield(logp.clone(), d, torch.tensor(K), cfg=cfg, BV_log=True)
+        out["uf_" + key], out["dz_" + key] = uf, dz
+    mask = (torch.rand(1, H, W, generator=g) > 0.3).float()
+    cfg = ref_shim.AttrDict({"data": {"dataset_path": "kitti"}})
+    ufm, _ = IU.gen_ufield(torch.exp(logp), d, torch.tensor(K), cfg=cfg, BV_log=False, mask=mask)
+    mean = IU.dpv_to_depthmap(logp, d, BV_log=True)
+    p = torch.exp(logp)
+    IU.spread_kernel = None
+    sp5 = IU.spread_dpv_hack(p, 5)
+    IU.spread_kernel = None
+    sp3 = IU.spread_dpv_hack(p, 3)
+    IU.spread_kernel = None
+    up = IU.upsample_dpv(logp, N=16, BV_log=True)
+    dn = IU.upsample_dpv(up, N=D, BV_log=True)
+    save("dpv_utils", logp=logp, d_candi=d, K=K, mask=mask, uf_masked=ufm, mean=mean, spread5=sp5, spread3=sp3,
+         up16=up, down8=dn, **out)
+
+
+def case_likelihood():
+    g = torch.Generator().manual_seed(3)
+    D, H, W = 16, 6, 10
+    d = IU.powerf(5., 40., D, 1.0)
+    z = 5 + 35 * torch.rand(H, W, generator=g)
+    z[0, :3] = 0.0                                # un-sensed pixels
+    var = (0.05 + 1.5 * torch.rand(H, W, generator=g)) ** 2
+    var[0, :3] = 0.0
+    x = torch.rand(H, W, generator=g)
+    x[0, :3] = 0.0
+    _install_lcsim_stubs()
+    import lc.light_curtain as LC
+    A = LC.mapping(x)
+    mix = LC.mixed_model(d, z, var, A, 1. - A)
+    dm = 5 + 35 * torch.rand(2, H, W, generator=g)
+    mk = (torch.rand(2, 1, H, W, generator=g) > 0.4).float()
+    tdpv = IU.gen_dpv_withmask(dm, mk, d, 0.3)
+    dc = torch.tensor(d).float()
+    mean_i, lik = IU.lc_intensities_to_dist(dc, z.unsqueeze(-1), x.unsqueeze(-1), torch.sqrt(var).unsqueeze(-1) + 0.1,
+                                            0.1, torch.ones(H, W, 1) * 0.2)
+    save("likelihood", d_candi=d, z=z, var=var, x=x, A=A, mixed=mix, dmaps=dm, masks=mk, truth_dpv=tdpv,
+         true_mean=mean_i, true_lik=lik)
+
+
+def _install_lcsim_stubs():
+    sim = types.ModuleType("sim")
+    sim.LCDevice = lcsim.LCDevice
+    pl = types.ModuleType("planner")
+    pl.PlannerRT = lcsim.PlannerRT
+    py = types.ModuleType("pylc_lib")
+    py.generateCameraAngles = lcsim.generateCameraAngles
+    py.transformPoints = lcsim.transformPoints
+    sys.modules["sim"], sys.modules["planner"], sys.modules["pylc_lib"] = sim, pl, py
+
+
+def case_light_curtain():
+    _install_lcsim_stubs()
+    import lc.light_curtain as LC
+    import models.models as MM
+    g = torch.Generator().manual_seed(4)
+    B, D, H, W = 1, 16, 32, 64
+    h, w = H // 4, W // 4
+    cfg = ref_shim.AttrDict({"data": {"dataset_path": "kitti", "exp_name": "golden"},
+                             "var": {"d_min": 5., "d_max": 40., "qpower": 1.0}})
+    d = IU.powerf(5., 40., D, 1.0)
+    d_up = IU.powerf(5., 40., 32, 1.0)
+    Klow, _ = intrinsics(w, h, hfov=16.0, vfov=10.0)   # 0.25 deg/column so the galvo limit leaves edges
+    Kup = Klow * 4
+    Kup[2, 2] = 1
+    # GT: sloped road + a box
+    yy = torch.arange(h).float().unsqueeze(1).repeat(1, w)
+    dm = torch.clamp(0.75 * Klow[1, 1] / torch.clamp(yy - Klow[1, 2] + 0.5, min=0.05), 5.5, 38.0)
+    dm[2:5, 4:8] = 12.0
+    dm = dm + 0.2 * torch.rand(h, w, generator=g)
+    model_input = {"intrinsics_up": torch.tensor(Kup).unsqueeze(0), "intrinsics": torch.tensor(Klow).unsqueeze(0),
+                   "rgb": torch.zeros(B, 2, 3, H, W), "dmaps": dm.unsqueeze(0), "masks": torch.ones(B, 1, h, w),
+                   "d_candi": d, "d_candi_up": d_up}
+    lc = LC.LightCurtain()
+    params = lc.gen_params_from_model_input(model_input)
+    params = lc.expand_params(params, cfg, D, 32)
+    lc.init(params)
+    # initial DPV: broad around a biased depth
+    dmap_up = torch.nn.functional.interpolate(dm.unsqueeze(0).unsqueeze(0), scale_factor=4, mode="nearest")[0, 0]
+    logits = -((torch.tensor(d).float().reshape(D, 1, 1) - (dmap_up * 1.1 + 1.0)) ** 2) / 30.0 \
+        + 0.2 * torch.randn(D, H, W, generator=g)
+    logp = torch.log_softmax(logits, 0).unsqueeze(0)
+    prm = ref_shim.AttrDict({"step": [0.5], "spread_iter": 2, "spread_n": 5})
+
+    # one plan + sense by hand (records intermediates)
+    uf, _ = IU.gen_ufield(logp.clone(), d, torch.tensor(Kup), cfg=cfg, BV_log=True)
+    paths, _ = lc.plan_default_high(uf.squeeze(0).clone(), prm)
+    flow = lc.fw_large.flowfields["z2rwarp_high"].clone()
+    liks = [lc.sense_high(dmap_up.numpy(), p, False)[0] for p in paths]
+
+    class _Self:
+        pass
+    me = _Self()
+    me.cfg = cfg
+    me.viz = None
+    IU.spread_kernel = None
+    fused, _ = MM.BaseModel.lc_process(me, logp.clone(), model_input, lc, mode="high", iterations=3,
+                                       planner="default", params=prm)
+    IU.spread_kernel = None
+    save("light_curtain", logp=logp, d_candi=d, d_candi_up=d_up, Kup=Kup, dmaps=dm, uf0=uf, flow=flow,
+         path0=paths[0], path1=paths[1], path2=paths[2], lik0=liks[0], lik1=liks[1], lik2=liks[2], fused=fused,
+         angles=np.array(lc.fw_large.angles_output, np.float32))
+
+
+def case_lcsim_fixture():
+    """The one known-answer vector the reference ships for lcsim: example/dpv.npy['angles']."""
+    d = np.load("/root/reference/external/lcsim/python/example/dpv.npy", allow_pickle=True, encoding="bytes")[()]
+    fld = d[b"field"]
+    fld = fld.numpy() if hasattr(fld, "numpy") else np.asarray(fld)
+    save("lcsim_dpv_fixture", intrinsics=np.asarray(d[b"intrinsics"], np.float32), size=np.asarray(d[b"size"]),
+         angles=np.asarray(d[b"angles"], np.float32), r_candi=np.asarray(d[b"r_candi"], np.float32),
+         field=fld.astype(np.float16).astype(np.float32))
+
+
+if __name__ == "__main__":
+    case_sweep()
+    case_dpv_utils()
+    case_likelihood()
+    case_light_curtain()
+    case_lcsim_fixture()

@@ -1,0 +1,110 @@
+"""CPU: the oracle restatement (oracle/) against vectors produced by the UNMODIFIED reference
+(tests/golden/make_golden.py, run in the build container) and against the one known-answer
+fixture the reference ships for lcsim (example/dpv.npy['angles'])."""
+import os
+
+import numpy as np
+import torch
+
+from oracle import dpv_oracle as O
+from oracle import lc_oracle as LO
+from oracle import lcsim
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load(name):
+    return {k: v for k, v in np.load(os.path.join(G, name + ".npz")).items()}
+
+
+def T(a):
+    return torch.tensor(a)
+
+
+def close(a, b, rtol=1e-6, atol=1e-7):
+    a = a.numpy() if torch.is_tensor(a) else np.asarray(a)
+    np.testing.assert_allclose(a, b, rtol=rtol, atol=atol, equal_nan=True)
+
+
+def test_plane_sweep_and_warp_feature():
+    g = load("sweep")
+    for metric, key in (("L2", "cost_l2"), ("L1", "cost_l1")):
+        c = O.plane_sweep_cost(T(g["ref"]), T(g["src"]), g["d_candi"], T(g["R"]), T(g["t"]), T(g["K"]),
+                               T(g["rays"]), float(g["sigma"]), metric)
+        close(c, g[key], rtol=1e-6, atol=1e-6)
+    w = O.warp_feature_diag(T(g["fsrc"]), g["d_candi"], T(g["R3"]), T(g["t3"]), T(g["K"]), T(g["rays"]))
+    close(w, g["warped"], rtol=1e-6, atol=1e-6)
+    # identity pose samples pixel centres exactly
+    close(w[0, 2], g["fsrc"][0, 2], rtol=0, atol=1e-5)
+
+
+def test_dpv_utils():
+    g = load("dpv_utils")
+    logp, d, K = T(g["logp"]), g["d_candi"], T(g["K"])
+    for key in ("kitti", "sweep"):
+        uf, dz = O.ufield(logp.clone(), d, K, O.uf_params("/data/%s/x" % key), BV_log=True)
+        close(uf, g["uf_" + key])
+        close(dz, g["dz_" + key])
+    ufm, _ = O.ufield(torch.exp(logp), d, K, O.uf_params("kitti"), BV_log=False, mask=T(g["mask"]))
+    close(ufm, g["uf_masked"])
+    close(O.dpv_expectation(logp, d, BV_log=True), g["mean"])
+    close(O.spread_depth(torch.exp(logp), 5), g["spread5"])
+    close(O.spread_depth(torch.exp(logp), 3), g["spread3"])
+    up = O.resample_depth_bins(logp, 16, BV_log=True)
+    close(up, g["up16"])
+    close(O.resample_depth_bins(up, 8, BV_log=True), g["down8"])
+    _, mean, _, _ = O.logsoftmax_stats(logp, d)
+    close(mean, g["mean"], rtol=1e-5)
+
+
+def test_nearest_index_tables_match_grid_sample():
+    for H, W, ps in ((32, 48, 5), (256, 768, 5), (64, 192, 3)):
+        rf, ri, cs = O.nearest_index_tables(H, W, ps)
+        x = torch.arange(H * W).float().reshape(1, 1, H, W) + 1
+        y = torch.nn.functional.grid_sample(x, O._shift_grid(H, W, ps), mode="nearest", align_corners=False)[0, 0]
+        exp = torch.zeros(H, W)
+        for r in range(H):
+            for c in range(W):
+                if rf[r] >= 0 and cs[c] >= 0:
+                    exp[r, c] = x[0, 0, rf[r], cs[c]]
+        assert torch.equal(y, exp)
+        if (H, W) == (256, 768):
+            assert rf[5] == 0 and rf[4] == -1 and cs[-1] == -1 and cs[-2] == W - 2 and ri[0] == 5
+
+
+def test_likelihood():
+    g = load("likelihood")
+    d = g["d_candi"]
+    A = O.intensity_to_weight(T(g["x"]))
+    close(A, g["A"])
+    close(O.mixed_likelihood(d, T(g["z"]), T(g["var"]), A, 1.0 - A), g["mixed"])
+    close(O.masked_truth_dpv(T(g["dmaps"]), T(g["masks"]), d, 0.3), g["truth_dpv"])
+    m, l = O.intensity_model_likelihood(T(d).float(), T(g["z"]).unsqueeze(-1), T(g["x"]).unsqueeze(-1),
+                                        torch.sqrt(T(g["var"])).unsqueeze(-1) + 0.1, 0.1,
+                                        torch.ones(*g["z"].shape, 1) * 0.2)
+    close(m, g["true_mean"])
+    close(l, g["true_lik"])
+
+
+def test_lcsim_camera_angles_known_answer():
+    g = load("lcsim_dpv_fixture")
+    ang = np.array(lcsim.generateCameraAngles(g["intrinsics"], None, int(g["size"][0]), int(g["size"][1])))
+    np.testing.assert_allclose(ang, g["angles"], rtol=0, atol=2e-5)
+
+
+def test_light_curtain_python_half():
+    g = load("light_curtain")
+    H, W = g["logp"].shape[2:]
+    lc = LO.LightCurtainOracle(g["Kup"], W, H, g["d_candi"], g["d_candi_up"])
+    np.testing.assert_allclose(lc.angles, g["angles"], rtol=0, atol=0)
+    close(lc.flow(), g["flow"], rtol=0, atol=0)
+    uf, _ = O.ufield(T(g["logp"]), g["d_candi"], T(g["Kup"]), O.uf_params("kitti"))
+    close(uf, g["uf0"])
+    paths, _, _ = lc.plan(uf.squeeze(0).clone(), [0.5])
+    depth = np.repeat(np.repeat(g["dmaps"], 4, 0), 4, 1)
+    for i, p in enumerate(paths):
+        np.testing.assert_array_equal(p, g["path%d" % i])
+        lik, _, _ = lc.sense(depth, p)
+        close(lik, g["lik%d" % i])
+    fused = LO.lc_loop(T(g["logp"]), depth, lc, g["Kup"], O.uf_params("kitti"), 3, [0.5], 2, 5)
+    close(fused, g["fused"], rtol=1e-6, atol=1e-6)
