@@ -1,0 +1,55 @@
+// Shared helpers for libdpvb200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdarg>
+#include <cstdio>
+
+#include "dpv_b200.h"
+
+namespace dpv {
+
+void set_error(const char* fmt, ...);
+void count_launch(int n = 1);
+
+// utils/img_utils.py:13 — torch.finfo(float).eps (double eps) used as the fp32 clamp floor
+__host__ __device__ constexpr float eps_floor() { return 2.220446049250313e-16f; }
+
+inline int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return DPV_ECUDA;
+  }
+  count_launch();
+  return DPV_OK;
+}
+
+#define DPV_REQUIRE(cond, ...)      \
+  do {                              \
+    if (!(cond)) {                  \
+      dpv::set_error(__VA_ARGS__);  \
+      return DPV_EINVAL;            \
+    }                               \
+  } while (0)
+
+#define DPV_CUDA(expr)                                              \
+  do {                                                              \
+    cudaError_t e__ = (expr);                                       \
+    if (e__ != cudaSuccess) {                                       \
+      dpv::set_error("%s: %s", #expr, cudaGetErrorString(e__));     \
+      return DPV_ECUDA;                                             \
+    }                                                               \
+  } while (0)
+
+// Streaming (read-once / write-once) accesses: keep the 126 MB L2 for data that is re-read.
+__device__ __forceinline__ float ld_stream(const float* p) { return __ldcs(p); }
+__device__ __forceinline__ void st_stream(float* p, float v) { __stcs(p, v); }
+
+// grid_sample(align_corners=False) un-normalisation, ATen grid_sampler_unnormalize: ((g+1)*N-1)/2
+__device__ __forceinline__ float gs_unnormalize(float g, int n) {
+  return __fdiv_rn(__fsub_rn(__fmul_rn(__fadd_rn(g, 1.f), (float)n), 1.f), 2.f);
+}
+
+}  // namespace dpv

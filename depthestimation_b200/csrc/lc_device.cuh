@@ -1,0 +1,41 @@
+// Light-curtain device model shared by the planner (lc_plan.cu) and the sensing kernels (lc_sense.cu).
+// Host part mirrors DatumProcessor::setSensors (external/lcsim/lcsim/src/dprocessor.cpp:41-235);
+// the per-geometry tables are computed once on the host and kept in HBM.
+#pragma once
+#include <vector>
+
+#include "common.cuh"
+
+struct LcMat4 {
+  float m[4][4];
+};
+
+// Plain-old-data view passed to kernels by value.
+struct LcDeviceView {
+  int W, H;
+  const float* nn_x;        // [W] un-normalised ray x per column ((u+1-cx)/fx, 1-based pixel grid)
+  const float* nn_y;        // [H]
+  const float* ztoramap;    // [H*W]
+  const float* mid_x;       // [W] normalised mid-row ray
+  const float* mid_z;       // [W]
+  const float* angles;      // [W] camera angle per column, degrees
+  const float* hit_lut;     // [hit_N]
+  int hit_N, hit_mode;
+  float limit, thickness, divergence;
+  float cam_origin[2], p_left_cam[2], p_right_cam[2], laser_origin[2], p_left_laser[2], p_right_laser[2];
+  LcMat4 cam_to_laser, laser_to_cam_inv;
+};
+
+struct LcDevice {
+  int W = 0, H = 0;
+  float K[9];
+  LcMat4 cam_to_laser, laser_to_cam, laser_to_cam_inv;
+  float fov = 80.f, laser_timestep = 1.5e-5f, laser_limit = 14000.f;
+  float thickness = 0.00055f, divergence = 0.055f, limit = 1.0f;
+  int hit_mode = 0, hit_N = 1000;
+  float hit_std = 0.3f, hit_pow = 2.f;
+  std::vector<float> nn_x, nn_y, ztoramap, mid_x, mid_z, angles, hit_lut;
+  float t_max = 0.f;
+  float* d_tables = nullptr;   // one device allocation holding all tables
+  LcDeviceView view;
+};

@@ -1,0 +1,208 @@
+// (d2) planner input preparation and (d3) the dynamic-programming curtain planner.
+//   lc/light_curtain.py:646-708 plan_default (up to the planner calls)
+//   external/lcsim/lcsim/src/planning.cpp:14-126, 162-217, 255-264
+#include <cmath>
+#include <vector>
+
+#include "lc_device.cuh"
+
+namespace dpv {
+
+constexpr int kPrepCols = 32;
+constexpr int kPrepWarps = 4;
+
+// ---------------------------------------------------------------------------------------------
+// P1 (column-local): side fix -> NaN columns -> bilinear row upsample D->R -> 5-tap depth mean ->
+// per-column min-max normalise -> NaN->eps.   light_curtain.py:654-681, 79-85, 207-218
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kPrepCols* kPrepWarps)
+plan_prep_columns_kernel(const float* __restrict__ uf, int D, int W, int R, float* __restrict__ field_pre) {
+  extern __shared__ float sm[];
+  float* u = sm;                        // [D][32]
+  float* f0 = sm + (size_t)D * kPrepCols;        // [R][32]
+  float* f1 = f0 + (size_t)R * kPrepCols;        // [R][32]
+  __shared__ int has_nan[kPrepCols];
+  __shared__ float lo_s[kPrepWarps][kPrepCols], hi_s[kPrepWarps][kPrepCols];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int b = blockIdx.y;
+  const int x = blockIdx.x * kPrepCols + lane;
+  const bool xin = x < W;
+  // field[:,0] = field[:,1]; field[:,-1] = field[:,-2]   (:654-655)
+  int sx = x;
+  if (x == 0) sx = 1;
+  if (x == W - 1) sx = W - 2;
+  if (W == 2) sx = 1;
+  if (threadIdx.x < kPrepCols) has_nan[threadIdx.x] = 0;
+  __syncthreads();
+  bool nan_here = false;
+  for (int d = warp; d < D; d += kPrepWarps) {
+    float v = xin ? uf[((size_t)b * D + d) * W + sx] : 0.f;
+    u[d * kPrepCols + lane] = v;
+    nan_here |= (v != v);
+  }
+  if (nan_here) has_nan[lane] = 1;
+  __syncthreads();
+  if (has_nan[lane]) {                                          // :658-662
+    for (int d = warp; d < D; d += kPrepWarps) u[d * kPrepCols + lane] = (d == D - 1) ? 1.0f : eps_floor();
+  }
+  __syncthreads();
+  // F.interpolate(size=[R,W], bilinear, align_corners=False): rows only (W keeps its size)
+  const float scale = (float)D / (float)R;
+  for (int r = warp; r < R; r += kPrepWarps) {
+    float s = fmaxf(scale * ((float)r + 0.5f) - 0.5f, 0.f);
+    int i0 = (int)s;
+    int i1 = i0 + (i0 < D - 1 ? 1 : 0);
+    float l1 = s - (float)i0, l0 = 1.f - l1;
+    f0[r * kPrepCols + lane] = l0 * u[i0 * kPrepCols + lane] + l1 * u[i1 * kPrepCols + lane];
+  }
+  __syncthreads();
+  // conv2d with a 5x5 kernel whose middle COLUMN is 1/5 => 5-tap mean along the range axis, zero pad
+  float lo = INFINITY, hi = -INFINITY;
+  bool any_nan = false;
+  for (int r = warp; r < R; r += kPrepWarps) {
+    float s = 0.f;
+#pragma unroll
+    for (int j = -2; j <= 2; j++) {
+      int rr = r + j;
+      if (rr >= 0 && rr < R) s += 0.2f * f0[rr * kPrepCols + lane];
+    }
+    f1[r * kPrepCols + lane] = s;
+    lo = fminf(lo, s);
+    hi = fmaxf(hi, s);
+    any_nan |= (s != s);
+  }
+  if (any_nan) lo = hi = NAN;                                    // torch.min/max propagate NaN
+  lo_s[warp][lane] = lo;
+  hi_s[warp][lane] = hi;
+  __syncthreads();
+  lo = lo_s[0][lane];
+  hi = hi_s[0][lane];
+#pragma unroll
+  for (int k = 1; k < kPrepWarps; k++) {
+    float a = lo_s[k][lane], c = hi_s[k][lane];
+    lo = (a != a || lo != lo) ? NAN : fminf(lo, a);
+    hi = (c != c || hi != hi) ? NAN : fmaxf(hi, c);
+  }
+  const float span = hi - lo;
+  for (int r = warp; r < R; r += kPrepWarps) {
+    float v = (f1[r * kPrepCols + lane] - lo) / span;            // normalize :207-210
+    if (v != v) v = eps_floor();                                  // :681
+    if (xin) field_pre[((size_t)b * R + r) * W + x] = v;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// P2: polar z->range warp (FieldWarp.warp :47-58, bilinear grid_sample, zeros, align_corners=False)
+// -> per-column argmax (:698) -> left / right peak split (:700-703) -> invert(x,p) (:221-225).
+// ---------------------------------------------------------------------------------------------
+struct InvertSteps {
+  int n;
+  float p[8];
+  float den[8];   // (float)(p^p (1-p)^(1-p)) evaluated in double like the Python expression
+};
+
+__device__ __forceinline__ float pow_like_torch(float x, float e) {
+  if (e == 0.5f) return sqrtf(x);          // ATen pow(tensor, scalar) specialisations
+  if (e == 1.0f) return x;
+  if (e == 2.0f) return x * x;
+  if (e == 0.0f) return 1.f;
+  return powf(x, e);
+}
+
+__global__ void __launch_bounds__(kPrepCols* kPrepWarps)
+plan_prep_warp_kernel(const float* __restrict__ field_pre, const float* __restrict__ flow, int W, int R,
+                      InvertSteps steps, float* __restrict__ umaps, int32_t* __restrict__ argmax_out) {
+  extern __shared__ float sm[];
+  float* fr = sm;                      // [R][32] warped field
+  __shared__ int amax[kPrepCols];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int b = blockIdx.y;
+  const int x = blockIdx.x * kPrepCols + lane;
+  const bool xin = x < W;
+  const float* f = field_pre + (size_t)b * R * W;
+  const float ystep = (float)(2.0 / (double)(R - 1)), xstep = (float)(2.0 / (double)(W - 1));
+  for (int r = warp; r < R; r += kPrepWarps) {
+    float val = 0.f;
+    if (xin) {
+      const float fx = flow[((size_t)r * W + x) * 2 + 0], fy = flow[((size_t)r * W + x) * 2 + 1];
+      float gx = __fsub_rn(__fadd_rn(-1.f, __fmul_rn((float)x, xstep)), __fmul_rn(fx, xstep));
+      float gy = __fsub_rn(__fadd_rn(-1.f, __fmul_rn((float)r, ystep)), __fmul_rn(fy, ystep));
+      float ix = gs_unnormalize(gx, W), iy = gs_unnormalize(gy, R);
+      if (ix > -2.f && ix < (float)(W + 1) && iy > -2.f && iy < (float)(R + 1)) {
+        float fx0 = floorf(ix), fy0 = floorf(iy);
+        int x0 = (int)fx0, y0 = (int)fy0;
+        float tx = ix - fx0, ty = iy - fy0;
+        float ux = (fx0 + 1.f) - ix, uy = (fy0 + 1.f) - iy;
+        bool vx0 = x0 >= 0 && x0 < W, vx1 = x0 + 1 >= 0 && x0 + 1 < W;
+        bool vy0 = y0 >= 0 && y0 < R, vy1 = y0 + 1 >= 0 && y0 + 1 < R;
+        if (vx0 && vy0) val += f[(size_t)y0 * W + x0] * (ux * uy);
+        if (vx1 && vy0) val += f[(size_t)y0 * W + x0 + 1] * (tx * uy);
+        if (vx0 && vy1) val += f[(size_t)(y0 + 1) * W + x0] * (ux * ty);
+        if (vx1 && vy1) val += f[(size_t)(y0 + 1) * W + x0 + 1] * (tx * ty);
+      }
+    }
+    fr[r * kPrepCols + lane] = val;
+  }
+  __syncthreads();
+  if (warp == 0) {                     // torch.max(dim=0): first index of the maximum
+    float best = fr[lane];
+    int bi = 0;
+    for (int r = 1; r < R; r++) {
+      float v = fr[r * kPrepCols + lane];
+      if (v > best || (v != v && best == best)) { best = v; bi = r; }
+    }
+    amax[lane] = bi;
+    if (xin && argmax_out) argmax_out[(size_t)b * W + x] = bi;
+  }
+  __syncthreads();
+  if (!xin) return;
+  const int pk = amax[lane];
+  const int nmaps = 1 + 2 * steps.n;
+  float* out = umaps + (size_t)b * nmaps * R * W;
+  for (int r = warp; r < R; r += kPrepWarps) {
+    const float v = fr[r * kPrepCols + lane];
+    out[(size_t)r * W + x] = v;
+    const float left = (r < pk) ? 1.f : v;        // left_field[rows < idx] = 1
+    const float right = (r >= pk) ? 1.f : v;      // right_field[rows >= idx] = 1
+    for (int s = 0; s < steps.n; s++) {
+      const float p = steps.p[s], q = 1.f - p;
+      float il = (pow_like_torch(left, p) * pow_like_torch(1.f - left, q)) / steps.den[s];
+      float ir = (pow_like_torch(right, p) * pow_like_torch(1.f - right, q)) / steps.den[s];
+      out[((size_t)(1 + 2 * s) * R + r) * W + x] = il;
+      out[((size_t)(2 + 2 * s) * R + r) * W + x] = ir;
+    }
+  }
+}
+
+}  // namespace dpv
+
+using namespace dpv;
+
+extern "C" int lc_plan_prepare(const float* uf, int B, int D, int W, int R, const float* flow, const float* steps,
+                               int nsteps, float* umaps, int32_t* argmax, float* field_pre, void* stream) {
+  DPV_REQUIRE(uf && flow && umaps && field_pre, "lc_plan_prepare: null pointer (field_pre scratch is required)");
+  DPV_REQUIRE(B > 0 && D > 1 && W >= 4 && R > 1, "lc_plan_prepare: bad shape");
+  DPV_REQUIRE(nsteps >= 0 && nsteps <= 8 && (nsteps == 0 || steps), "lc_plan_prepare: nsteps=%d not in [0,8]", nsteps);
+  DPV_REQUIRE(B <= 65535, "lc_plan_prepare: B too large");
+  cudaStream_t st = (cudaStream_t)stream;
+  InvertSteps is;
+  is.n = nsteps;
+  for (int i = 0; i < nsteps; i++) {
+    double p = (double)steps[i];
+    is.p[i] = (float)p;
+    is.den[i] = (float)(std::pow(p, p) * std::pow(1.0 - p, 1.0 - p));
+  }
+  dim3 grid((W + kPrepCols - 1) / kPrepCols, B);
+  size_t sm1 = (size_t)(D + 2 * R) * kPrepCols * sizeof(float);
+  size_t sm2 = (size_t)R * kPrepCols * sizeof(float);
+  DPV_REQUIRE(sm1 <= 200 * 1024, "lc_plan_prepare: D + 2R too large for shared memory");
+  if (sm1 > 48 * 1024)
+    DPV_CUDA(cudaFuncSetAttribute(plan_prep_columns_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
+  if (sm2 > 48 * 1024)
+    DPV_CUDA(cudaFuncSetAttribute(plan_prep_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
+  plan_prep_columns_kernel<<<grid, kPrepCols * kPrepWarps, sm1, st>>>(uf, D, W, R, field_pre);
+  int rc = check_launch("lc_plan_prepare/columns");
+  if (rc) return rc;
+  plan_prep_warp_kernel<<<grid, kPrepCols * kPrepWarps, sm2, st>>>(field_pre, flow, W, R, is, umaps, argmax);
+  return check_launch("lc_plan_prepare/warp");
+}

@@ -1,0 +1,134 @@
+"""The DPV operations that sit between the CNN blocks of the reference's BaseModel
+(models/models.py) and its light-curtain loop, batched and fused for B200:
+
+  cost_volume()        models.py:617-636  (loop over batch of est_swp_volume_v4)
+  warped_features()    models.py:648-661  (loop over batch of warp_feature)
+  dpv_logsoftmax()     models.py:351,671,777 F.log_softmax(dim=1) [+ residual addend] with stats / carry
+  uniform_log_prior()  models.py:756-772
+  lc_process()         models.py:980-1129 BaseModel.lc_process (mode high/low, planner "default")
+
+The CNN blocks themselves (encoder / Base3D / decoder) stay cuDNN library calls in the caller.
+"""
+import numpy as np
+import torch
+
+from . import ops
+from .utils import img_utils
+
+
+def _center_from(K_np_or_tensor, device):
+    K = K_np_or_tensor
+    if torch.is_tensor(K):
+        return K[:, :2, 2].to(device=device, dtype=torch.float32).contiguous()
+    K = np.asarray(K, np.float32)
+    return torch.from_numpy(np.ascontiguousarray(K[:, :2, 2])).to(device)
+
+
+def cost_volume(feat_ref, feat_src, K, R, t, rays, d_candi, sigma, feat_dist="L2", K_np=None):
+    """feat_ref [B,C,h,w], feat_src [B,V,C,h,w], K [B,3,3], R [B,V,3,3], t [B,V,3], rays [B|1,3,h*w]."""
+    center = _center_from(K if K_np is None else K_np, feat_ref.device)
+    return ops.plane_sweep(feat_ref, feat_src, K, R, t, rays, center, d_candi, sigma, feat_dist)
+
+
+def warped_features(feat_raw, K, R, t, rays, d_candi, K_np=None):
+    """feat_raw [B,T,C,h,w] -> [B,T,D,h,w] (diagonal feature warp of every view incl. the reference)."""
+    center = _center_from(K if K_np is None else K_np, feat_raw.device)
+    return ops.warp_feature(feat_raw, K, R, t, rays, center, d_candi)
+
+
+def dpv_logsoftmax(x, d_candi, add=None, stats=True, carry=False):
+    """log_softmax over depth (+ addend) -> dict(logp, mean, var, entropy, carry)."""
+    return ops.logsoftmax_stats(x, d_candi, add=add, want_var=stats, want_entropy=stats, want_carry=carry)
+
+
+def uniform_log_prior(shape, D, device):
+    return torch.log(torch.zeros(shape, device=device) + 1.0 / float(D))
+
+
+class LcLoopState:
+    """Pre-allocated buffers of one LC loop (so the loop can be captured in a CUDA graph)."""
+
+    def __init__(self, B, D, H, W, R, nc, device):
+        f = dict(device=device, dtype=torch.float32)
+        self.logp = torch.empty(B, D, H, W, **f)
+        self.mean = torch.empty(B, H, W, **f)
+        self.uf = torch.empty(B, D, W, **f)
+        self.umaps = torch.empty(B, nc, R, W, **f)
+        self.argmax = torch.empty(B, W, device=device, dtype=torch.int32)
+        self.field_pre = torch.empty(B, R, W, **f)
+        self.ks = torch.empty(B * nc, W, device=device, dtype=torch.int32)
+        self.xz = torch.empty(B * nc, W, 2, **f)
+        self.counts = torch.empty(B * nc, device=device, dtype=torch.int32)
+        self.planes = torch.empty(B * nc, W, 12, **f)
+        self.shape = (B, D, H, W, R, nc)
+
+
+def lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n, noise=None, trace=None):
+    """One Bayesian iteration (models.py:1027-1122) for the whole batch: 6 kernel launches, no host sync."""
+    from ._lib import check, lib, ptr, stream_ptr
+    B, D, H, W, R, nc = state.shape
+    dev = rig.dev
+    ops.ufield(state.logp, state.mean, K, lc.d_candi, uf_par, bv_log=True, want_depth=False, out=state.uf)
+    ops.plan_prepare(state.uf, rig.flow, steps, R, state.umaps, state.argmax, state.field_pre)
+    rig.planner.solve(state.umaps.view(B * nc, R, W), state.ks, state.xz, state.counts)
+    check(lib().lc_curtain_planes(dev._h, ptr(state.xz), ptr(state.counts), B * nc, W, ptr(state.planes), None,
+                                  stream_ptr(dev.device)))
+    if trace is not None:
+        trace.append(dict(uf=state.uf.clone(), ks=state.ks.clone().view(B, nc, W), counts=state.counts.clone(),
+                          umaps=state.umaps.clone(), argmax=state.argmax.clone()))
+    dev.sense_fuse(state.logp, depth, state.planes, nc, lc.d_candi, spread_iter, spread_n, noise=noise,
+                   out=state.logp, mean=state.mean)
+    if trace is not None:
+        trace[-1]["logp"] = state.logp.clone()
+
+
+def lc_process(BV_cur_all, model_input, lc, mode="low", iterations=5, viz=False, score=False, planner="default",
+               params=None, cfg=None, noise=None, trace=None, state=None):
+    """BaseModel.lc_process (models/models.py:980-1129) for the whole batch at once.
+
+    BV_cur_all [B,D,H,W] log-DPV; model_input needs "dmaps" [B,h,w], "intrinsics_up"/"intrinsics" [B,3,3];
+    params has .step / ["step"], spread_iter, spread_n.  noise: optional [iterations, B*nc, H, W] intensity noise
+    (the reference draws unseeded N(0, 0.01)); None uses the device's hit_noise setting.
+    Returns (fused log-DPV [B,D,H,W], unc_scores list) like the reference."""
+    if planner != "default":
+        raise NotImplementedError("planner %r: only 'default' is on the B200 path (plan_m1 / plan_sweep are next)"
+                                  % planner)
+    get = (lambda k: params[k]) if isinstance(params, dict) else (lambda k: getattr(params, k))
+    steps, spread_iter, spread_n = list(get("step")), int(get("spread_iter")), int(get("spread_n"))
+    dev = BV_cur_all.device
+    B = BV_cur_all.shape[0]
+    if mode == "high":                                                        # models.py:985-989
+        K = model_input["intrinsics_up"].to(dev).float().reshape(B, 3, 3)
+        depth = torch.nn.functional.interpolate(model_input["dmaps"].to(dev).float().unsqueeze(1), scale_factor=4,
+                                                mode="nearest").squeeze(1).contiguous()
+    elif mode == "low":                                                       # :997-1001
+        K = model_input["intrinsics"].to(dev).float().reshape(B, 3, 3)
+        depth = model_input["dmaps"].to(dev).float().contiguous()
+    else:
+        raise Exception("lc_process: unknown mode " + str(mode))
+    rig = lc.rig(mode)
+    uf_par = img_utils.uf_params(cfg if cfg is not None else "kitti")
+    final = BV_cur_all.detach()
+    D_in = final.shape[1]
+    if D_in != lc.expand_A:                                                   # :1015-1016
+        final = ops.resample_depth(final, lc.expand_A, bv_log=True)
+    D, H, W = final.shape[1:]
+    R, nc = len(lc.r_candi_up), 1 + 2 * len(steps)
+    if state is None:
+        state = LcLoopState(B, D, H, W, R, nc, dev)
+    state.logp.copy_(final)
+    ops.expectation(state.logp, lc.d_candi, True, out=state.mean)
+    unc_scores = [[] for _ in range(B)]
+    for i in range(iterations):
+        nz = None
+        if noise is not None:
+            nz = noise[i]
+        elif rig.dev.hit_noise > 0:
+            nz = rig.dev.noise_like(B * nc)
+        lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n, noise=nz, trace=trace)
+    out = state.logp
+    if D != D_in:                                                             # :1124
+        out = ops.resample_depth(out, D_in, bv_log=True)
+    else:
+        out = out.clone()
+    return out, unc_scores

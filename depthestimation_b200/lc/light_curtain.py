@@ -1,0 +1,176 @@
+"""Drop-in for the planning / sensing surface of the reference's lc/light_curtain.py:
+LightCurtain.{init, expand_params, gen_params_from_model_input, plan_default_high/low,
+sense_high/low} (light_curtain.py:255-373, 646-739, 741-910) plus the module helpers
+(normalize, create_mean_kernel, invert, mapping, mixed_model :207-252 are folded into kernels).
+
+Planning and sensing stay on the GPU end to end: no .cpu().numpy() round trip (the reference has
+six per LC iteration), design points / likelihood volumes are CUDA tensors.
+"""
+import numpy as np
+import torch
+
+from .. import lcsim, ops
+from ..utils import img_utils
+
+
+def intr_scale_unit(intr, scale):
+    """utils/img_utils.py intr_scale_unit: scale fx, fy, cx, cy."""
+    out = np.array(intr, dtype=np.float32).copy()
+    out[0, 0] *= scale
+    out[1, 1] *= scale
+    out[0, 2] *= scale
+    out[1, 2] *= scale
+    return out
+
+
+def digitize_soft(values, array):
+    """FieldWarp.digitize_soft (light_curtain.py:60-77), vectorised over `values` (float64)."""
+    array = np.asarray(array, dtype=np.float64)
+    values = np.asarray(values, dtype=np.float64)
+    n = len(array)
+    pos = np.digitize(values, array) - 1
+    inside = (pos >= 0) & (pos < n - 1)
+    p = np.clip(pos, 0, n - 2)
+    soft = p + 1.0 * ((values - array[p]) / (array[p + 1] - array[p]))
+    out = np.where(inside, soft, 0.0)
+    out = np.where(pos == n - 1, 100000000.0, out)
+    out = np.where(pos == -1, -100000000.0, out)
+    out = np.where(np.abs(values - array[0]) < 1e-7, 0.0, out)
+    out = np.where(np.abs(values - array[-1]) < 1e-7, float(n - 1), out)
+    return out
+
+
+def polar_flowfield(angles, d_candi, r_candi):
+    """FieldWarp._ztheta2zrange (light_curtain.py:87-116) without the Python double loop:
+    flow[r,c] = (c - thetabin, r - zbin), stored fp32 like the reference's torch.zeros tensor."""
+    angles = np.asarray(angles, dtype=np.float64)        # float32 list in the reference -> float64 math in numpy
+    r_candi = np.asarray(r_candi, dtype=np.float64)
+    R, W = len(r_candi), len(angles)
+    zval = r_candi[:, None] * np.cos(np.radians(angles))[None, :]
+    zbin = digitize_soft(zval.reshape(-1), d_candi).reshape(R, W)
+    thetabin = digitize_soft(angles, angles)
+    flow = np.zeros((R, W, 2), np.float32)
+    flow[:, :, 0] = (np.arange(W, dtype=np.float64)[None, :] - thetabin[None, :]).astype(np.float32)
+    flow[:, :, 1] = (np.arange(R, dtype=np.float64)[:, None] - zbin).astype(np.float32)
+    return flow
+
+
+class _Rig:
+    """One (device, planner, polar flow) triple: the reference's *_large or *_small members."""
+
+    def __init__(self, width, height, K, lTc, fov, timestep, d_candi_up, r_candi_up, device):
+        self.dev = lcsim.LCDevice(
+            CAMERA_PARAMS=dict(width=width, height=height, matrix=K, distortion=[0.] * 5, hit_mode=1, hit_noise=0.01),
+            LASER_PARAMS=dict(lTc=lTc, fov=fov, laser_timestep=timestep), device=device)
+        self.planner = lcsim.PlannerRT(self.dev, r_candi_up, width)
+        self.angles = np.array(lcsim.generateCameraAngles(K, None, width, height), np.float32)
+        self.flow = torch.from_numpy(polar_flowfield(self.angles, d_candi_up, r_candi_up)).to(device)
+
+
+class LightCurtain:
+    def __init__(self):
+        self.lightcurtain = None
+        self.initialized = False
+        self._rigs = {}
+
+    def init(self, PARAMS):
+        self.PARAMS = PARAMS
+        if not np.all(np.equal(np.asarray(PARAMS["rTc"]), np.eye(4))) or \
+                PARAMS["size_rgb"][0] != PARAMS["size_lc"][0] or PARAMS["size_rgb"][1] != PARAMS["size_lc"][1]:
+            raise NotImplementedError("rTc != I / differing LC camera (transformPoints path) is a 'next' row")
+        if np.any(np.asarray(PARAMS["dist_lc"]) != 0) or np.any(np.asarray(PARAMS["dist_rgb"]) != 0):
+            raise NotImplementedError("lens distortion is out of scope")
+        self.d_candi = PARAMS["d_candi"]
+        self.r_candi = PARAMS["r_candi"]
+        self.d_candi_up = PARAMS["d_candi_up"]
+        self.r_candi_up = PARAMS["r_candi_up"]
+        self.PARAMS['cTr'] = np.linalg.inv(PARAMS["rTc"])
+        self.expand_A = PARAMS["expand_A"]
+        self.expand_B = PARAMS["expand_B"]
+        self.device = torch.device(PARAMS["device"])
+        self.transform_needed = False
+        self.hit_noise = PARAMS.get("hit_noise", 0.01)             # light_curtain.py:275-276
+        self._rigs = {}
+        self.initialized = True
+        self.rig("high")
+
+    def rig(self, mode):
+        r = self._rigs.get(mode)
+        if r is None:
+            P = self.PARAMS
+            if mode == "high":
+                r = _Rig(int(P["size_lc"][0]), int(P["size_lc"][1]), np.asarray(P["intr_lc"], np.float32), P["lTc"],
+                         P["laser_fov"], P["laser_timestep"], self.d_candi_up, self.r_candi_up, self.device)
+            else:                                                   # light_curtain.py:279-297 (*_SMALL)
+                r = _Rig(int(P["size_lc"][0] / 4), int(P["size_lc"][1] / 4), intr_scale_unit(P["intr_lc"], 1 / 4.),
+                         P["lTc"], P["laser_fov"], P["laser_timestep"] * 4, self.d_candi_up, self.r_candi_up,
+                         self.device)
+            r.dev.hit_noise = float(self.hit_noise)
+            self._rigs[mode] = r
+        return r
+
+    def expand_params(self, PARAMS, cfg, expand_A, expand_B, add_name=""):      # light_curtain.py:331-341
+        PARAMS["d_candi"] = img_utils.powerf(cfg.var.d_min, cfg.var.d_max, expand_A, cfg.var.qpower)
+        PARAMS["r_candi"] = PARAMS["d_candi"]
+        PARAMS["d_candi_up"] = img_utils.powerf(cfg.var.d_min, cfg.var.d_max, expand_B, cfg.var.qpower)
+        PARAMS["r_candi_up"] = PARAMS["d_candi_up"]
+        PARAMS["expand_A"] = expand_A
+        PARAMS["expand_B"] = expand_B
+        PARAMS["name"] = cfg.data.exp_name + add_name
+        return PARAMS
+
+    def gen_params_from_model_input(self, model_input):                           # light_curtain.py:343-373
+        eye = np.eye(4, dtype=np.float32)
+        lTc = eye.copy()
+        lTc[0, 3] = 0.2
+        K = model_input["intrinsics_up"][0, :, :].cpu().numpy()
+        size = [model_input["rgb"].shape[4], model_input["rgb"].shape[3]]
+        return {"intr_rgb": K, "dist_rgb": [0.] * 5, "size_rgb": size, "intr_lc": K, "dist_lc": [0.] * 5,
+                "size_lc": list(size), "rTc": eye, "lTc": lTc, "laser_fov": 80.,
+                "d_candi": model_input["d_candi"], "r_candi": model_input["d_candi"],
+                "d_candi_up": model_input["d_candi_up"], "r_candi_up": model_input["d_candi_up"],
+                "name": "default", "laser_timestep": 3.5e-5, "device": model_input["intrinsics"].device}
+
+    # ---- planning (light_curtain.py:646-739) --------------------------------------------------
+    def plan_batched(self, uf, steps, mode="high"):
+        """uf [B,D,W] -> dict(xz [B,nc,W,2], ks [B,nc,W] int32, counts [B,nc] int32, umaps, argmax, field_pre)."""
+        r = self.rig(mode)
+        R = len(self.r_candi_up)
+        umaps, amax, pre = ops.plan_prepare(uf, r.flow, steps, R)
+        B, nc = umaps.shape[0], umaps.shape[1]
+        ks, xz, counts = r.planner.solve(umaps.reshape(B * nc, R, -1))
+        W = uf.shape[2]
+        return dict(xz=xz.reshape(B, nc, W, 2), ks=ks.reshape(B, nc, W), counts=counts.reshape(B, nc), umaps=umaps,
+                    argmax=amax, field_pre=pre)
+
+    def _plan_default(self, field, cfg, mode):
+        out = self.plan_batched(field.unsqueeze(0), list(cfg["step"]), mode)
+        counts = out["counts"][0].tolist()
+        pts = [out["xz"][0, i, :counts[i]] for i in range(len(counts))]
+        self.field_visual = out["field_pre"][0]
+        return pts, self.field_visual
+
+    def plan_default_high(self, field, cfg):
+        """-> (list of design-point tensors [n_i,2] (x,z), field_visual).  `field` is not modified."""
+        return self._plan_default(field, cfg, "high")
+
+    def plan_default_low(self, field, cfg):
+        return self._plan_default(field, cfg, "low")
+
+    # ---- sensing (light_curtain.py:741-910) ---------------------------------------------------
+    def _sense(self, depth_rgb, design_pts_lc, mode, noise=None):
+        r = self.rig(mode)
+        depth = ops.f32(depth_rgb, self.device).reshape(1, r.dev.H, r.dev.W)
+        pts = ops.f32(design_pts_lc, self.device)[:, :2].contiguous().unsqueeze(0)
+        planes = r.dev.curtain_planes(pts)
+        if noise is None:
+            noise = r.dev.noise_like(1)
+        lik = r.dev.sense_likelihood(planes, depth, 1, self.d_candi, noise)
+        return lik[0], None, {}
+
+    def sense_high(self, depth_rgb, design_pts_lc, visualizer=None, noise=None):
+        """-> (DPV [D,H,W], None, {}): the per-pixel LC likelihood of one curtain (:820-910)."""
+        return self._sense(depth_rgb, design_pts_lc, "high", noise)
+
+    def sense_low(self, depth_rgb, design_pts_lc, visualizer=None, noise=None):
+        return self._sense(depth_rgb, design_pts_lc, "low", noise)

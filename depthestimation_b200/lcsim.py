@@ -1,0 +1,191 @@
+"""B200-native stand-in for the lcsim Python surface the DPV path uses:
+external/lcsim/python/sim.py:29-211 (LCDevice), planner.py:162-189 (PlannerRT) and the two
+pylc_lib functions bound at pylc_lib.cpp:114-251 (generateCameraAngles; transformPoints is only
+reached for rTc != I sensors and is a "next" row).  Same constructor dictionaries, same method
+names; arrays may be numpy (copied to the GPU) or CUDA tensors (used in place).
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import check, f32, lib, ptr, stream_ptr
+
+
+def _host_f32(a):
+    return np.ascontiguousarray(np.asarray(a, dtype=np.float32))
+
+
+def _hp(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def generateCameraAngles(K, dist, w, h):
+    """pylc_lib.generateCameraAngles (algo.cpp:696-741).  Zero distortion only (the KITTI-sim set-up,
+    lc/light_curtain.py:346-349)."""
+    if dist is not None and np.any(np.asarray(dist) != 0):
+        raise NotImplementedError("generateCameraAngles: non-zero distortion is out of scope (SURVEY 7, hard part 3)")
+    K = _host_f32(K)
+    out = np.zeros(int(w), np.float32)
+    check(lib().lc_camera_angles(_hp(K), int(w), int(h), _hp(out)))
+    return list(out)
+
+
+class LCDevice:
+    """sim.LCDevice for an explicit lTc + camera matrix (what lc/light_curtain.py:270-304 builds)."""
+
+    def __init__(self, LASER_PARAMS=None, CAMERA_PARAMS=None, device=None):
+        lp = dict(fov=80, thickness=0.00055, divergence=0.11 / 2., laser_limit=14000, laser_timestep=1.5e-5,
+                  lTc=None)                                                  # sim.py:42-56
+        cp = dict(width=512, height=512, limit=1.0, distortion=[0.] * 5, matrix=None, hit_mode=0, hit_noise=0.)
+        for k in lp:
+            if LASER_PARAMS and k in LASER_PARAMS:
+                lp[k] = LASER_PARAMS[k]
+        for k in cp:
+            if CAMERA_PARAMS and k in CAMERA_PARAMS:
+                cp[k] = CAMERA_PARAMS[k]
+        if lp["lTc"] is None or cp["matrix"] is None:
+            raise NotImplementedError("LCDevice needs explicit lTc and camera matrix")
+        if np.any(np.asarray(cp["distortion"]) != 0):
+            raise NotImplementedError("LCDevice: non-zero distortion is out of scope")
+        self.LASER_PARAMS, self.CAMERA_PARAMS = lp, cp
+        self.W, self.H = int(cp["width"]), int(cp["height"])
+        self.hit_noise = float(cp["hit_noise"])
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        K, T = _host_f32(cp["matrix"]), _host_f32(lp["lTc"])
+        h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            check(lib().lc_device_create(self.W, self.H, _hp(K), _hp(T), float(lp["fov"]), float(lp["laser_timestep"]),
+                                         float(lp["laser_limit"]), float(lp["thickness"]), float(lp["divergence"]),
+                                         int(cp["hit_mode"]), float(cp["limit"]), ctypes.byref(h)))
+        self._h = h
+        self.datum_processor = self
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h and _lib._lib is not None:
+            _lib._lib.lc_device_destroy(h)
+            self._h = None
+
+    def valid_angles(self):
+        out = np.zeros(self.W, np.float32)
+        check(lib().lc_device_angles(self._h, _hp(out)))
+        return out
+
+    def hit_lut(self):
+        out = np.zeros(1000, np.float32)
+        check(lib().lc_device_hit_lut(self._h, _hp(out)))
+        return out
+
+    # ---- tensor-level API (batched) -----------------------------------------------------------
+    def curtain_planes(self, xz, counts=None, want_design=False):
+        """xz [n,npts,2] (CUDA) -> planes [n,W,12] (+ design [n,W,4])."""
+        xz = f32(xz, self.device)
+        n, npts = xz.shape[0], xz.shape[1]
+        planes = torch.empty(n, self.W, 12, device=self.device, dtype=torch.float32)
+        design = torch.empty(n, self.W, 4, device=self.device, dtype=torch.float32) if want_design else None
+        if counts is not None:
+            counts = counts.to(device=self.device, dtype=torch.int32).contiguous()
+        check(lib().lc_curtain_planes(self._h, ptr(xz), ptr(counts), n, npts, ptr(planes), ptr(design),
+                                      stream_ptr(self.device)))
+        return (planes, design) if want_design else planes
+
+    def noise_like(self, n):
+        """Explicit stand-in for lcsim's unseeded N(0, hit_noise) draw (dprocessor.cpp:984-989)."""
+        if self.hit_noise <= 0:
+            return None
+        return torch.randn(n, self.H, self.W, device=self.device) * self.hit_noise
+
+    def sense_image(self, planes, depth, nc, noise=None):
+        """planes [B*nc,W,12], depth [B,H,W] -> image [B*nc,H,W,4], thick [B*nc,H,W]."""
+        depth = f32(depth, self.device)
+        B = depth.shape[0]
+        img = torch.empty(B * nc, self.H, self.W, 4, device=self.device, dtype=torch.float32)
+        th = torch.empty(B * nc, self.H, self.W, device=self.device, dtype=torch.float32)
+        check(lib().lc_sense_image(self._h, ptr(planes), ptr(depth), ptr(noise), B, nc, ptr(img), ptr(th),
+                                   stream_ptr(self.device)))
+        return img, th
+
+    def sense_likelihood(self, planes, depth, nc, d_candi, noise=None):
+        from .ops import d_candi_tensor
+        depth = f32(depth, self.device)
+        B = depth.shape[0]
+        dc = d_candi_tensor(d_candi, self.device)
+        lik = torch.empty(B * nc, dc.numel(), self.H, self.W, device=self.device, dtype=torch.float32)
+        check(lib().lc_sense_likelihood(self._h, ptr(planes), ptr(depth), ptr(noise), B, nc, ptr(dc), dc.numel(),
+                                        ptr(lik), stream_ptr(self.device)))
+        return lik
+
+    def sense_fuse(self, logp, depth, planes, nc, d_candi, spread_iter, spread_n, noise=None, out=None, mean=None):
+        """One LC iteration's sensing + Bayesian update (models/models.py:1064-1122), in place if out is logp."""
+        from .ops import d_candi_tensor
+        B, D = logp.shape[0], logp.shape[1]
+        dc = d_candi_tensor(d_candi, self.device)
+        out = torch.empty_like(logp) if out is None else out
+        mean = torch.empty(B, self.H, self.W, device=self.device, dtype=torch.float32) if mean is None else mean
+        check(lib().lc_sense_fuse(self._h, ptr(logp), ptr(depth), ptr(planes), ptr(noise), B, nc, ptr(dc), D,
+                                  int(spread_iter), int(spread_n), ptr(out), ptr(mean), stream_ptr(self.device)))
+        return out, mean
+
+    # ---- sim.LCDevice.get_return (sim.py:168-211) -----------------------------------------------
+    def get_return(self, np_depth_image, np_design_pts, get_thickness=False, noise=None):
+        depth = f32(np_depth_image, self.device).reshape(1, self.H, self.W)
+        pts = f32(np_design_pts, self.device)[:, :2].contiguous().unsqueeze(0)
+        planes = self.curtain_planes(pts)
+        if noise is None:
+            noise = self.noise_like(1)
+        else:
+            noise = f32(noise, self.device).reshape(1, self.H, self.W)
+        img, th = self.sense_image(planes, depth, 1, noise)
+        if isinstance(np_depth_image, np.ndarray):
+            img, th = img[0].cpu().numpy(), th[0].cpu().numpy()
+        else:
+            img, th = img[0], th[0]
+        return (img, th) if get_thickness else img
+
+
+class PlannerRT:
+    """planner.PlannerRT (planner.py:162-189): ranges x camera rays graph, DP over an uncertainty map."""
+
+    def __init__(self, lc_device, ranges, num_camera_angles, debug=False):
+        if int(num_camera_angles) != lc_device.W:
+            raise ValueError("PlannerRT: num_camera_angles must equal the device width")
+        self._dev = lc_device
+        self.device = lc_device.device
+        self.ranges = _host_f32(ranges)
+        self.R, self.W = len(self.ranges), lc_device.W
+        h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            check(lib().lc_planner_create(lc_device._h, _hp(self.ranges), self.R, ctypes.byref(h)))
+        self._h = h
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h and _lib._lib is not None:
+            _lib._lib.lc_planner_destroy(h)
+            self._h = None
+
+    def edge_count(self):
+        return int(lib().lc_planner_edge_count(self._h))
+
+    def solve(self, umaps, ks=None, xz=None, counts=None):
+        """umaps [n,R,W] CUDA -> (ks [n,W] int32, xz [n,W,2], counts [n] int32)."""
+        umaps = f32(umaps, self.device)
+        n = umaps.shape[0]
+        if tuple(umaps.shape[1:]) != (self.R, self.W):
+            raise ValueError("PYLC_PLANNER: Unexpected umap shape (%d)." % umaps[0].numel())   # planning.cpp:77-80
+        ks = torch.empty(n, self.W, device=self.device, dtype=torch.int32) if ks is None else ks
+        xz = torch.empty(n, self.W, 2, device=self.device, dtype=torch.float32) if xz is None else xz
+        counts = torch.empty(n, device=self.device, dtype=torch.int32) if counts is None else counts
+        check(lib().lc_planner_solve(self._h, ptr(umaps), n, ptr(ks), ptr(xz), ptr(counts), stream_ptr(self.device)))
+        return ks, xz, counts
+
+    def get_design_points(self, umap, return_indices=False):
+        as_numpy = isinstance(umap, np.ndarray)
+        ks, xz, counts = self.solve(f32(umap, self.device).unsqueeze(0))
+        n = int(counts[0].item())
+        xz, ks = xz[0, :n], ks[0, :n]
+        if as_numpy:
+            xz, ks = xz.cpu().numpy(), ks.cpu().numpy()
+        return (xz, ks) if return_indices else xz

@@ -1,0 +1,163 @@
+/* dpv_b200.h — C ABI of libdpvb200.so: the B200-native (sm_100a) depth-probability-volume (DPV)
+ * + light-curtain (LC) hot path of CMU-Light-Curtains/DepthEstimation.
+ *
+ * Conventions:
+ *   - every `const float*` / `float*` / `int32_t*` argument is a DEVICE pointer owned by the caller
+ *     unless its comment says "host"; tensors are dense, row-major, fp32;
+ *   - `stream` is a cudaStream_t passed as void*; every function is asynchronous on it and never
+ *     synchronises (CUDA-graph capturable) except the *_create functions;
+ *   - return 0 on success, a DPV_E* code otherwise; dpv_last_error() gives the thread-local text;
+ *   - the library allocates only inside the opaque handles (LcDevice, LcPlanner).
+ * File:line citations name the reference function each entry point replaces
+ * (paths relative to the reference repository root).
+ */
+#ifndef DPV_B200_H_
+#define DPV_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DPV_OK 0
+#define DPV_EINVAL 1   /* bad shape / argument (reference: Python Exception / std::invalid_argument) */
+#define DPV_ECUDA 2    /* CUDA runtime error */
+#define DPV_EUNSUPPORTED 3
+
+int dpv_version(void);
+const char* dpv_last_error(void);
+/* Number of kernels this library has launched in the calling process (bench.py: gpu_launches). */
+long long dpv_launch_count(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * (a) Plane sweep.  warping/homography.py:98-135 est_swp_volume_v4 (+ _back_warp_homo_parallel
+ * :170-198, img_dis_L2_pard :80-86), batched over B frames (the reference loops, models/models.py:617).
+ *   ref [B,C,h,w]  src [B,V,C,h,w]  K [B,3,3]  R [B,V,3,3]  t [B,V,3]  rays [B,3,h*w] (or [1,3,h*w]
+ *   with rays_batch_stride = 0)  center [B,2] = (cx,cy) of the numpy intrinsics (homography.py:194)
+ *   d_candi [D]  ->  cost [B,D,h,w] = sum_v sum_c dist(bilinear(src_v, H_d p), ref) / sigma
+ *   metric: 0 = 'L2', 1 = 'L1'.
+ */
+int dpv_plane_sweep(const float* ref, const float* src, int B, int V, int C, int h, int w,
+                    const float* K, const float* R, const float* t, const float* rays,
+                    long long rays_batch_stride, const float* center, const float* d_candi, int D,
+                    float sigma, int metric, float* cost, void* stream);
+
+/* warping/homography.py:137-168 warp_feature: out[b,v,i] = warp of channel i of view v onto plane i.
+ *   src [B,T,C,h,w] with C >= D  ->  out [B,T,D,h,w]   (reference requires C == D) */
+int dpv_warp_feature(const float* src, int B, int T, int C, int h, int w, const float* K,
+                     const float* R, const float* t, const float* rays, long long rays_batch_stride,
+                     const float* center, const float* d_candi, int D, float* out, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * (b) DPV normalisation + statistics in one pass.  F.log_softmax(x [+ add], dim=1) at
+ * models/models.py:351,435,590,671,743,777,816; expectation utils/img_utils.py:197-215
+ * (dpv_to_depthmap); variance trainer/default_trainer.py:446-450; entropy (north_star);
+ * temporal carry F.interpolate(.., 0.25, 'nearest') trainer/default_trainer.py:284,289.
+ *   x, add(nullable) [B,D,H,W] -> logp [B,D,H,W]; mean,var,entropy [B,H,W] (each nullable);
+ *   carry (nullable) [B,D,H/4,W/4].
+ */
+int dpv_logsoftmax_stats(const float* x, const float* add, int B, int D, int H, int W,
+                         const float* d_candi, float* logp, float* mean, float* var, float* entropy,
+                         float* carry, void* stream);
+
+/* utils/img_utils.py:197-215 dpv_to_depthmap, batched: mean[b,y,x] = sum_d d_candi[d] * p. */
+int dpv_expectation(const float* dpv, int B, int D, int H, int W, const float* d_candi, int bv_log,
+                    float* mean, void* stream);
+
+/* utils/img_utils.py:408-436 spread_dpv_hack: N-tap box SUM along D (zero pad) then / sum_d. */
+int dpv_spread(const float* p, int B, int D, int H, int W, int N, float* out, void* stream);
+
+/* utils/img_utils.py:438-449 upsample_dpv: bilinear along D (align_corners=False) + renormalise. */
+int dpv_resample_depth(const float* dpv, int B, int D, int H, int W, int Dout, int bv_log, float* out,
+                       void* stream);
+
+/* models/models.py:1096-1122 (and ros/ros_all.py:169-203): clamp(exp(logp)) -> for each likelihood
+ * volume: NaN->0, clamp, multiply, renormalise -> spread x spread_iter -> clamp -> log.
+ *   logp_in [B,D,H,W]; liks [B,nlik,D,H,W]; -> logp_out [B,D,H,W], mean_out (nullable) [B,H,W]. */
+int dpv_bayes_fuse(const float* logp_in, const float* liks, int nlik, int B, int D, int H, int W,
+                   const float* d_candi, int spread_iter, int spread_n, float* logp_out, float* mean_out,
+                   void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * (d1) DPV -> top-down uncertainty field.  utils/img_utils.py:475-565 gen_ufield
+ * (+ convert_flowfield :343-349, depth_to_pts :269-293).
+ *   dpv [B,D,H,W], mean [B,H,W] (= dpv_expectation of the same dpv), K_up [B,3,3]
+ *   mask (nullable) [B,H,W]  ->  uf [B,D,W] (NaN where a column has no band pixel),
+ *   depth_zero (nullable) [B,H,W].
+ */
+typedef struct DpvUfieldParams {
+  int pshift;          /* img_utils.py:485/491 */
+  float ystart, yend;  /* camera-Y band ("zstart","zend" in the reference) */
+  float maxd, mind;
+  int quash;           /* img_utils.py:532-539 */
+  int bv_log;
+} DpvUfieldParams;
+int dpv_ufield(const float* dpv, const float* mean, const float* mask, int B, int D, int H, int W,
+               const float* d_candi, const float* K_up, const DpvUfieldParams* prm /*host*/, float* uf,
+               float* depth_zero, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * (d2) Planner input.  lc/light_curtain.py:646-708 plan_default up to the planner calls
+ * (FieldWarp.preprocess :79-85, create_mean_kernel :213-218, normalize :207-210, FieldWarp.warp
+ * :47-58, invert :221-225).
+ *   uf [B,D,W] (not modified; the reference edits it in place), flow [R,W,2] (polar z->range flow),
+ *   steps host [nsteps]  ->  umaps [B,1+2*nsteps,R,W], argmax [B,W], field_pre (nullable) [B,R,W].
+ */
+int lc_plan_prepare(const float* uf, int B, int D, int W, int R, const float* flow, const float* steps,
+                    int nsteps, float* umaps, int32_t* argmax, float* field_pre, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * lcsim device model.  external/lcsim/python/sim.py:29-211 LCDevice,
+ * external/lcsim/lcsim/src/dprocessor.cpp:41-235 (setSensors, createNormalMap, computeLaserParams).
+ * All arguments host; K row-major 3x3, lTc row-major 4x4 (camera -> laser).
+ */
+typedef struct LcDevice LcDevice;
+int lc_device_create(int W, int H, const float* K, const float* lTc, float fov, float laser_timestep,
+                     float laser_limit, float thickness, float divergence, int hit_mode, float limit,
+                     LcDevice** out);
+void lc_device_destroy(LcDevice* dev);
+/* host copies of per-column camera angles [W] (degrees) and the 1000-entry hit LUT */
+int lc_device_angles(const LcDevice* dev, float* out_host);
+int lc_device_hit_lut(const LcDevice* dev, float* out_host);
+
+/* external/lcsim/lcsim/src/algo.cpp:696-741 Algo::generateCameraAngles (zero distortion). host in/out */
+int lc_camera_angles(const float* K, int W, int H, float* out_host);
+
+/* (d3) DP planner.  external/lcsim/lcsim/src/planning.cpp:14-126 (+ Trajectory :162-217),
+ * python/planner.py:162-189 PlannerRT.  ranges host [R]. */
+typedef struct LcPlanner LcPlanner;
+int lc_planner_create(const LcDevice* dev, const float* ranges, int R, LcPlanner** out);
+void lc_planner_destroy(LcPlanner* pl);
+long long lc_planner_edge_count(const LcPlanner* pl);
+/* umaps [n,R,W] -> ks [n,W] (range index per ray, -1 past the end), xz [n,W,2], counts [n] */
+int lc_planner_solve(LcPlanner* pl, const float* umaps, int n, int32_t* ks, float* xz, int32_t* counts,
+                     void* stream);
+
+/* (d4) Curtain image formation.  dprocessor.cpp:995-1067 processPointsT = checkPoints :238-280 ->
+ * findCameraIntersectionsOpt :514-634 -> calculateSurface :735-925 -> computeDepthHits :942-993.
+ *   xz [n,npts,2] design points, counts [n] (valid points per curtain; nullable = all npts)
+ *   -> planes [n,W,12] camera-frame plane coefficients (main, +divergence, -divergence),
+ *      design (nullable) [n,W,4].
+ */
+int lc_curtain_planes(const LcDevice* dev, const float* xz, const int32_t* counts, int n, int npts,
+                      float* planes, float* design, void* stream);
+/* LCDevice.get_return (sim.py:168-211): curtains n = B*nc, depth [B,H,W], noise (nullable) [n,H,W]
+ *   -> image [n,H,W,4] (x,y,z,intensity 0..255; NaN = no return), thick [n,H,W]. */
+int lc_sense_image(const LcDevice* dev, const float* planes, const float* depth, const float* noise,
+                   int B, int nc, float* image, float* thick, void* stream);
+/* LightCurtain.sense_high tail (lc/light_curtain.py:847-888: mapping :228-244, mixed_model :247-252,
+ * utils/img_utils.py:176-195)  -> lik [n,D,H,W]. */
+int lc_sense_likelihood(const LcDevice* dev, const float* planes, const float* depth, const float* noise,
+                        int B, int nc, const float* d_candi, int D, float* lik, void* stream);
+/* One LC iteration's sensing + Bayesian update fused (models/models.py:1064-1122): no likelihood
+ * volume is materialised.  logp_in [B,D,H,W], depth [B,H,W], planes [B,nc,W,12]
+ *   -> logp_out [B,D,H,W] (may alias logp_in), mean_out (nullable) [B,H,W]. */
+int lc_sense_fuse(const LcDevice* dev, const float* logp_in, const float* depth, const float* planes,
+                  const float* noise, int B, int nc, const float* d_candi, int D, int spread_iter,
+                  int spread_n, float* logp_out, float* mean_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DPV_B200_H_ */

@@ -71,7 +71,7 @@ def generateCameraAngles(K, dist, w, h):
     K = _f32(K)
     out = np.zeros(int(w), np.float32)
     lib().lco_camera_angles(_p(K), int(w), int(h), _p(out))
-    return list(out)
+    return [float(v) for v in out]      # pybind11 returns std::vector<float> as Python floats
 
 
 def transformPoints(pts, thick, intr, M, width, height, params):

@@ -1,0 +1,182 @@
+"""GPU parity of the light-curtain half of the path (planner input, DP planner, curtain image
+formation, likelihood, fused sense+update, whole lc_process loop) against the CPU oracle and the
+goldens generated from the unmodified reference Python (tests/golden/make_golden.py)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import dpv_oracle as O
+from oracle import lc_oracle as LO
+from oracle import lcsim as olcsim
+
+pytestmark = pytest.mark.gpu
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def load(name):
+    return {k: v for k, v in np.load(os.path.join(G, name + ".npz")).items()}
+
+
+def cu(a):
+    return torch.as_tensor(np.asarray(a)).cuda()
+
+
+def close(a, b, rtol=1e-4, atol=1e-6, what=""):
+    a = a.detach().cpu().numpy() if torch.is_tensor(a) else np.asarray(a)
+    b = b.detach().cpu().numpy() if torch.is_tensor(b) else np.asarray(b)
+    np.testing.assert_allclose(a, b, rtol=rtol, atol=atol, equal_nan=True, err_msg=what)
+
+
+def _lTc():
+    T = np.eye(4, dtype=np.float32)
+    T[0, 3] = 0.2
+    return T
+
+
+def _devices(K, W, H, timestep=3.5e-5):
+    from depthestimation_b200 import lcsim
+    cp = dict(width=W, height=H, matrix=np.asarray(K, np.float32), distortion=[0.] * 5, hit_mode=1, hit_noise=0.)
+    lp = dict(lTc=_lTc(), fov=80., laser_timestep=timestep)
+    return lcsim.LCDevice(CAMERA_PARAMS=dict(cp), LASER_PARAMS=dict(lp)), \
+        olcsim.LCDevice(CAMERA_PARAMS=dict(cp), LASER_PARAMS=dict(lp))
+
+
+def _golden_lc(g):
+    from depthestimation_b200.lc.light_curtain import LightCurtain
+    H, W = g["logp"].shape[2:]
+    eye = np.eye(4, dtype=np.float32)
+    P = {"intr_rgb": g["Kup"], "dist_rgb": [0.] * 5, "size_rgb": [W, H], "intr_lc": g["Kup"], "dist_lc": [0.] * 5,
+         "size_lc": [W, H], "rTc": eye, "lTc": _lTc(), "laser_fov": 80., "d_candi": g["d_candi"],
+         "r_candi": g["d_candi"], "d_candi_up": g["d_candi_up"], "r_candi_up": g["d_candi_up"], "name": "golden",
+         "laser_timestep": 3.5e-5, "device": torch.device("cuda", 0), "expand_A": len(g["d_candi"]),
+         "expand_B": len(g["d_candi_up"]), "hit_noise": 0.0}
+    lc = LightCurtain()
+    lc.init(P)
+    return lc
+
+
+def test_camera_angles_and_device_tables():
+    from depthestimation_b200 import lcsim
+    g = load("lcsim_dpv_fixture")
+    W, H = int(g["size"][0]), int(g["size"][1])
+    ang = np.array(lcsim.generateCameraAngles(g["intrinsics"], None, W, H))
+    np.testing.assert_allclose(ang, g["angles"], rtol=0, atol=2e-5)       # the reference's own known answer
+    dev, odev = _devices(g["intrinsics"], W, H)
+    np.testing.assert_array_equal(dev.valid_angles(), odev.valid_angles())
+    np.testing.assert_array_equal(dev.hit_lut(), odev.hit_lut())
+
+
+def test_planner_bit_exact_on_reference_fixture():
+    """example/dpv.npy field (128 x 400): DP indices and design points identical to the oracle planner."""
+    from depthestimation_b200 import lcsim
+    g = load("lcsim_dpv_fixture")
+    W, H = int(g["size"][0]), int(g["size"][1])
+    for timestep in (3.5e-5, 1.0e-4):
+        dev, odev = _devices(g["intrinsics"], W, H, timestep)
+        pl, opl = lcsim.PlannerRT(dev, g["r_candi"], W), olcsim.PlannerRT(odev, g["r_candi"], W)
+        assert pl.edge_count() == opl.edge_count()
+        gen = np.random.default_rng(3)
+        fields = [g["field"], gen.random((128, W), dtype=np.float32), np.round(gen.random((128, W)) * 4).astype(np.float32) / 4,
+                  np.zeros((128, W), np.float32)]
+        ks, xz, counts = pl.solve(cu(np.stack(fields)))
+        for i, f in enumerate(fields):
+            exz, eks = opl.get_design_points(f, return_indices=True)
+            n = int(counts[i])
+            assert n == len(eks), "field %d: path length %d vs %d" % (i, n, len(eks))
+            np.testing.assert_array_equal(ks[i, :n].cpu().numpy(), eks)
+            np.testing.assert_array_equal(xz[i, :n].cpu().numpy(), exz)
+            assert (ks[i, n:] == -1).all()
+        xz1 = pl.get_design_points(fields[0])
+        np.testing.assert_array_equal(xz1, opl.get_design_points(fields[0]))
+        with pytest.raises(ValueError):
+            pl.get_design_points(np.zeros((5, 5), np.float32))
+
+
+def test_curtain_image_bit_exact():
+    """LCDevice.get_return: design points, plane coefficients, surface, thickness and the quantised
+    intensity are bit-identical to the oracle simulator (noise off and with an explicit noise image)."""
+    g = load("light_curtain")
+    H, W = g["logp"].shape[2:]
+    dev, odev = _devices(g["Kup"], W, H)
+    depth = np.repeat(np.repeat(g["dmaps"], 4, 0), 4, 1).astype(np.float32)
+    rng = np.random.default_rng(1)
+    flat = np.stack([np.arange(-10., 10., 0.05), np.full(400, 9.0)], 1).astype(np.float32)   # sim.py get_flat
+    for pts in (g["path0"], g["path1"], g["path2"], flat, g["path0"][:1], g["path0"][5:40]):
+        for noise in (None, (0.05 * rng.standard_normal((H, W))).astype(np.float32)):
+            img, th = dev.get_return(depth, pts, True, noise=noise)
+            eimg, eth, edes, epl = odev.get_return(depth, pts, True, noise=noise, debug=True)
+            planes, design = dev.curtain_planes(cu(pts[:, :2]).unsqueeze(0), want_design=True)
+            np.testing.assert_array_equal(design[0].cpu().numpy(), edes)
+            np.testing.assert_array_equal(planes[0].cpu().numpy(), epl)
+            np.testing.assert_array_equal(th, eth)
+            np.testing.assert_array_equal(img, eimg)
+
+
+def test_sense_likelihood_golden():
+    g = load("light_curtain")
+    lc = _golden_lc(g)
+    depth = np.repeat(np.repeat(g["dmaps"], 4, 0), 4, 1).astype(np.float32)
+    for i in range(3):
+        lik, _, _ = lc.sense_high(depth, cu(g["path%d" % i]))
+        close(lik, g["lik%d" % i], what="curtain %d" % i)
+
+
+def test_plan_prepare_and_paths_golden():
+    from depthestimation_b200 import ops
+    g = load("light_curtain")
+    lc = _golden_lc(g)
+    np.testing.assert_array_equal(lc.rig("high").angles, g["angles"])
+    close(lc.rig("high").flow, g["flow"][0], rtol=0, atol=0)
+    olc = LO.LightCurtainOracle(g["Kup"], g["logp"].shape[3], g["logp"].shape[2], g["d_candi"], g["d_candi_up"])
+    uf = torch.tensor(g["uf0"])
+    pre, frange = olc.prepare_field(uf[0].clone())
+    umaps_o, idx_o = olc.split_fields(frange, [0.5])
+    out = lc.plan_batched(cu(g["uf0"]), [0.5])
+    close(out["field_pre"][0], pre, rtol=1e-5, atol=1e-7)
+    for i in range(3):
+        close(out["umaps"][0, i], umaps_o[i], rtol=1e-5, atol=1e-6, what="umap %d" % i)
+    np.testing.assert_array_equal(out["argmax"][0].cpu().numpy(), idx_o.numpy())
+    paths, _ = lc.plan_default_high(cu(g["uf0"])[0], {"step": [0.5]})
+    for i in range(3):
+        np.testing.assert_array_equal(paths[i].cpu().numpy(), g["path%d" % i])
+    # a column of NaNs / p = 0.75 (default_318_lc_sweep step) against the oracle
+    uf2 = uf.clone()
+    uf2[0, :, 7] = float("nan")
+    pre2, fr2 = olc.prepare_field(uf2[0].clone())
+    um2, idx2 = olc.split_fields(fr2, [0.75])
+    out2 = lc.plan_batched(uf2.cuda(), [0.75])
+    for i in range(3):
+        close(out2["umaps"][0, i], um2[i], rtol=2e-5, atol=1e-6, what="p=0.75 umap %d" % i)
+
+
+def test_lc_process_golden_and_oracle_trace():
+    from depthestimation_b200 import dpv_head
+    g = load("light_curtain")
+    lc = _golden_lc(g)
+    H, W = g["logp"].shape[2:]
+    mi = {"dmaps": cu(g["dmaps"]).unsqueeze(0), "intrinsics_up": cu(g["Kup"]).unsqueeze(0)}
+    prm = {"step": [0.5], "spread_iter": 2, "spread_n": 5}
+    trace = []
+    fused, _ = dpv_head.lc_process(cu(g["logp"]), mi, lc, mode="high", iterations=3, params=prm, cfg="kitti",
+                                   trace=trace)
+    olc = LO.LightCurtainOracle(g["Kup"], W, H, g["d_candi"], g["d_candi_up"])
+    otrace = []
+    depth = np.repeat(np.repeat(g["dmaps"], 4, 0), 4, 1).astype(np.float32)
+    LO.lc_loop(torch.tensor(g["logp"]), depth, olc, g["Kup"], O.uf_params("kitti"), 3, [0.5], 2, 5, trace=otrace)
+    for it in range(3):
+        close(trace[it]["uf"], otrace[it]["uf"], what="uf it %d" % it)
+        for c in range(3):
+            n = int(trace[it]["counts"][c])
+            np.testing.assert_array_equal(trace[it]["ks"][0, c, :n].cpu().numpy(), otrace[it]["ks"][c],
+                                          err_msg="planner indices it %d curtain %d" % (it, c))
+        close(trace[it]["logp"], otrace[it]["logp"], atol=1e-5, what="logp it %d" % it)
+    close(fused, g["fused"], atol=1e-5)
+    assert torch.equal(fused.argmax(1).cpu(), torch.tensor(g["fused"]).argmax(1))
+    # batched call == per-sample calls
+    both, _ = dpv_head.lc_process(cu(g["logp"]).repeat(2, 1, 1, 1), {k: v.repeat(2, 1, 1) for k, v in mi.items()},
+                                  lc, mode="high", iterations=2, params=prm, cfg="kitti")
+    one, _ = dpv_head.lc_process(cu(g["logp"]), mi, lc, mode="high", iterations=2, params=prm, cfg="kitti")
+    assert torch.equal(both[0], one[0]) and torch.equal(both[1], one[0])

@@ -1,0 +1,77 @@
+"""CPU-side checks: the C-ABI library loads and exports every symbol include/dpv_b200.h declares, host
+logic of the Python mirrors (polar flow field, parameter plumbing), and loud failure without a GPU."""
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+G = os.path.join(ROOT, "tests", "golden")
+
+
+def test_library_exports_every_declared_symbol():
+    from depthestimation_b200 import _lib, build
+    build.build()
+    L = _lib.lib()
+    hdr = open(os.path.join(ROOT, "include", "dpv_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b((?:dpv|lc)_[a-z_0-9]+)\s*\(", hdr))
+    assert declared, "no declarations parsed"
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+    for name in declared:
+        assert hasattr(L, name), name
+    assert L.dpv_version() >= 100
+    assert L.dpv_launch_count() == 0
+
+
+def test_host_only_entry_points_match_oracle():
+    """lc_camera_angles is pure host code: check it against the reference's known-answer vector."""
+    from depthestimation_b200 import lcsim
+    g = np.load(os.path.join(G, "lcsim_dpv_fixture.npz"))
+    ang = np.array(lcsim.generateCameraAngles(g["intrinsics"], None, int(g["size"][0]), int(g["size"][1])))
+    np.testing.assert_allclose(ang, g["angles"], rtol=0, atol=2e-5)
+    with pytest.raises(NotImplementedError):
+        lcsim.generateCameraAngles(g["intrinsics"], [0.1, 0, 0, 0, 0], 10, 10)
+
+
+def test_polar_flowfield_matches_reference_golden():
+    from depthestimation_b200.lc.light_curtain import polar_flowfield
+    g = np.load(os.path.join(G, "light_curtain.npz"))
+    flow = polar_flowfield(g["angles"], g["d_candi_up"], g["d_candi_up"])
+    np.testing.assert_array_equal(flow, g["flow"][0])
+
+
+def test_no_cpu_fallback():
+    """The product path refuses CPU tensors instead of silently computing somewhere else."""
+    from depthestimation_b200 import _lib, ops
+    with pytest.raises(_lib.DpvError):
+        ops.expectation(torch.zeros(1, 4, 2, 2), np.linspace(1, 2, 4))
+    with pytest.raises(_lib.DpvError):
+        ops.spread(torch.zeros(1, 4, 2, 2))
+
+
+def test_argument_validation_without_gpu():
+    """Shape / argument errors are raised by the C ABI before any launch."""
+    import ctypes
+    from depthestimation_b200 import _lib
+    L = _lib.lib()
+    rc = L.dpv_spread(ctypes.c_void_p(16), 1, 8, 4, 4, 4, ctypes.c_void_p(16), None)      # N = 4 is not odd
+    assert rc == 1 and b"kernel size" in L.dpv_last_error()
+    rc = L.dpv_logsoftmax_stats(None, None, 1, 8, 4, 4, None, None, None, None, None, None, None)
+    assert rc == 1 and b"null pointer" in L.dpv_last_error()
+    rc = L.dpv_plane_sweep(ctypes.c_void_p(16), ctypes.c_void_p(16), 1, 1, 4, 4, 4, ctypes.c_void_p(16),
+                           ctypes.c_void_p(16), ctypes.c_void_p(16), ctypes.c_void_p(16), 0, ctypes.c_void_p(16),
+                           ctypes.c_void_p(16), 4, 10.0, 7, ctypes.c_void_p(16), None)
+    assert rc == 1 and b"undefined metric" in L.dpv_last_error()
+
+
+def test_uf_params_follow_dataset_path():
+    from depthestimation_b200.utils import img_utils as IU
+    from oracle import dpv_oracle as O
+    for k in ("kitti", "ilim", "sweep"):
+        assert IU.uf_params("/x/%s/y" % k) == O.uf_params("/x/%s/y" % k)
+    cfgx = {"unc_ang": 2, "unc_shift": 0.5, "unc_span": 0.2}
+    assert IU.uf_params(None, cfgx) == O.uf_params(None, cfgx)
+    np.testing.assert_array_equal(IU.powerf(5., 40., 64, 1.0), O.powerf(5., 40., 64, 1.0))
