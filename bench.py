@@ -1,0 +1,306 @@
+#!/usr/bin/env python
+"""bench.py — DPV + light-curtain-fusion hot path throughput (frames/sec) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--impl b200|reference]
+
+One "step" = one pass of the whole hot path (plane sweep -> log-softmax -> warp_feature -> log-softmax(+resi) ->
+full-res log-softmax+stats+carry -> 5 x [UF collapse, plan, DP, curtain planes, sense+fuse]) over one batch of
+synthetic KITTI-shaped frames per GPU (BASELINE.json configs[1]: default_exp7_lc --lc, batch 8 per GPU).
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every field.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+METRIC = "DPV+LC-fusion frames/sec"
+UNIT = "frames/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="C2_mono_lc_b8")
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the same step (reference Python restated in oracle/, lcsim restated in C++)
+# --------------------------------------------------------------------------------------------------
+def oracle_step(batch, meta, lc_cache={}):
+    """One frame-batch through the CPU oracle; returns the fused log-DPV.  Same inputs as DpvLcPipeline.step."""
+    from oracle import dpv_oracle as O
+    from oracle import lc_oracle as LO
+    d = meta["d_candi"]
+    B = batch["feat_all"].shape[0]
+    outs = []
+    for b in range(B):                                    # the reference is serial over the batch (models.py:617,984)
+        K, rays = batch["K"][b], batch["rays"][0]
+        cost = O.plane_sweep_cost(batch["feat_all"][b:b + 1, -1], batch["feat_all"][b:b + 1, :-1], d,
+                                  batch["R"][b, :-1], batch["t"][b, :-1], K, rays, 10.0, "L2")
+        bv = O.logsoftmax_stats(cost, d)[0]
+        O.warp_feature_diag(batch["feat_raw"][b:b + 1], d, batch["R"][b], batch["t"][b], K, rays)
+        O.logsoftmax_stats(bv, d, batch["bv_resi"][b:b + 1])
+        logp, mean, var, ent = O.logsoftmax_stats(batch["dec_logits"][b:b + 1], d)
+        O.carry_quarter(logp)
+        if meta["iterations"] > 0:
+            key = (meta["H"], meta["W"], meta["D"], meta["R"])
+            if key not in lc_cache:
+                lc_cache[key] = LO.LightCurtainOracle(meta["K_up"], meta["W"], meta["H"], d, meta["d_candi_up"])
+                lc_cache[key].flow()
+            depth = np.repeat(np.repeat(batch["dmaps"][b].numpy(), 4, 0), 4, 1).astype(np.float32)
+            logp = LO.lc_loop(logp, depth, lc_cache[key], meta["K_up"], O.uf_params(meta["dataset"]),
+                              meta["iterations"], meta["step"], meta["spread_iter"], meta["spread_n"])
+        outs.append(logp)
+    return torch.cat(outs)
+
+
+def time_cpu(workload, steps, warmup, frames_per_step=1):
+    from depthestimation_b200.pipeline import synthetic_batch
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    batch, meta = synthetic_batch(workload, seed=0, B=frames_per_step)
+    for _ in range(max(warmup, 0)):
+        oracle_step(batch, meta)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        oracle_step(batch, meta)
+    dt = (time.perf_counter() - t0) / steps
+    return frames_per_step / dt, dt, cores, meta
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.p = index, [], None
+
+    def __enter__(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                       "-lms", "200", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.p = None
+        return self
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.p:
+            time.sleep(0.25)
+            self.p.terminate()
+            self.t.join(timeout=2)
+
+    def summary(self):
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 9:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------------
+# GPU arm
+# --------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch.distributed as dist
+    from depthestimation_b200 import _lib, sharding
+    from depthestimation_b200.pipeline import STREAMED_KEYS, DpvLcPipeline, synthetic_batch
+    rank, world, local = sharding.init_from_env(args.gpus)
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    host, meta = synthetic_batch(args.workload, seed=rank)
+    B = meta["B"]
+    pipe = DpvLcPipeline(meta, dev)
+    x = {k: v.to(dev) for k, v in host.items()}
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    peak_gbs, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+
+    def sync():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    # ---- value: inputs resident in HBM --------------------------------------------------------
+    for _ in range(args.warmup):
+        out = pipe.step(x)
+        sharding.gather_frame_outputs(out, world)
+    sync()
+    pipe.fuse_events = []
+    n0 = _lib.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clk:
+        sync()
+        e0.record()
+        for _ in range(args.steps):
+            out = pipe.step(x)
+            sharding.gather_frame_outputs(out, world)
+        e1.record()
+        sync()
+    ms = e0.elapsed_time(e1)
+    launches = _lib.launch_count() - n0
+    fuse_ms = [a.elapsed_time(b) for a, b in pipe.fuse_events]
+    pipe.fuse_events = None
+    ms_t = torch.tensor([ms], device=dev)
+    if world > 1:
+        dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
+    ms = float(ms_t.item())
+    ms_per_step = ms / args.steps
+    value = world * B * args.steps / (ms / 1e3)
+
+    # ---- e2e: host buffers in, host results out, copies inside the timed region ------------------
+    e2e = None
+    if not args.no_e2e:
+        e2e = run_e2e(args, pipe, host, x, dev, world, B, STREAMED_KEYS, sync, sharding)
+
+    # ---- roofline of the dominant kernel (sense+fuse: one read + one write of the volume) --------
+    alg = pipe.algorithmic_bytes()
+    roof = None
+    if fuse_ms:
+        t = statistics.mean(fuse_ms) / 1e3
+        ach = alg["sense_fuse"] / t / 1e9
+        roof = {"kernel": "sense_fuse_kernel", "bound": "hbm", "achieved": round(ach, 1), "peak": peak_gbs,
+                "peak_source": peak_src, "unit": "GB/s", "frac": round(ach / peak_gbs, 4), "traffic": None,
+                "launch_ms": round(t * 1e3, 4), "launches_timed": len(fuse_ms),
+                "algorithmic_bytes_per_launch": alg["sense_fuse"],
+                "share_of_step": round(sum(fuse_ms) / ms if ms else 0.0, 4)}
+        tr = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tr):
+            roof["traffic"] = json.load(open(tr)).get("sense_fuse_kernel")
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, dt, cores, _ = time_cpu(args.workload, 1, 0)
+        cpu = {"value": round(v, 5), "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": "1 frame of the same workload through oracle/ (torch-CPU restatement + restated lcsim C++), "
+                         "%.1f s" % dt}
+    if rank == 0:
+        line = {"metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": args.workload, "frames_per_gpu": B, "H": meta["H"], "W": meta["W"],
+                           "D": meta["D"], "C": meta["C"], "T": meta["T"], "lc_iterations": meta["iterations"],
+                           "curtains_per_iteration": 1 + 2 * len(meta["step"]), "parallelism": "batch-shard x%d" % world,
+                           "l2_policy": "inputs larger than L2 (0.9 GB streamed per frame)"},
+                "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
+                "ms_per_frame": round(ms_per_step / B, 4)}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_e2e(args, pipe, host, x, dev, world, B, keys, sync, sharding):
+    """Same step through the public API with HOST buffers: pinned H2D of the step's inputs (double-buffered on a
+    copy stream so the copy of step i+1 overlaps step i) and a D2H read of depth / variance / LC depth."""
+    pin = {k: host[k].pin_memory() for k in keys}
+    bufs = [{k: torch.empty_like(x[k]) for k in keys} for _ in range(2)]
+    res_host = {k: torch.empty(B, pipe.m["H"], pipe.m["W"]).pin_memory() for k in ("depth", "var", "depth_lc")}
+    copy = torch.cuda.Stream(dev)
+    main = torch.cuda.current_stream(dev)
+    ready = [torch.cuda.Event() for _ in range(2)]
+    free = [torch.cuda.Event() for _ in range(2)]
+    h2d = sum(pin[k].numel() * 4 for k in keys)
+    d2h = sum(v.numel() * 4 for v in res_host.values())
+
+    def issue_copy(i):
+        s = i % 2
+        with torch.cuda.stream(copy):
+            copy.wait_event(free[s])
+            for k in keys:
+                bufs[s][k].copy_(pin[k], non_blocking=True)
+            ready[s].record(copy)
+
+    def loop(n):
+        for s in range(2):
+            free[s].record(main)
+        issue_copy(0)
+        for i in range(n):
+            s = i % 2
+            if i + 1 < n:
+                issue_copy(i + 1)
+            main.wait_event(ready[s])
+            xin = dict(x)
+            xin.update(bufs[s])
+            out = pipe.step(xin)
+            sharding.gather_frame_outputs(out, world)
+            for k in res_host:
+                if k in out:
+                    res_host[k].copy_(out[k], non_blocking=True)
+            free[s].record(main)
+        torch.cuda.synchronize(dev)
+
+    loop(max(args.warmup, 1))
+    sync()
+    t0 = time.perf_counter()
+    loop(args.steps)
+    sync()
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt], device=dev)
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dt = float(t.item())
+    return {"value": round(world * B * args.steps / dt, 2), "unit": UNIT, "h2d_bytes_per_step": h2d,
+            "d2h_bytes_per_step": d2h, "ms_per_step": round(dt / args.steps * 1e3, 4)}
+
+
+def run_reference(args):
+    """Reference arm: the reference's own CPU algorithm for this path (oracle port; lcsim cannot be compiled here,
+    DESIGN.md) on all host cores.  Each step = 1 frame of the workload.  Rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    from depthestimation_b200.pipeline import WORKLOADS
+    v, dt, cores, meta = time_cpu(args.workload, args.steps, min(args.warmup, 1))
+    w = WORKLOADS[args.workload]
+    line = {"impl": "reference", "metric": METRIC, "value": round(v, 5), "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(dt * 1e3, 2), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "frames_per_gpu": w["B"], "H": w["H"], "W": w["W"], "D": w["D"],
+                       "C": w["C"], "T": w["T"], "lc_iterations": w["iterations"],
+                       "curtains_per_iteration": 1 + 2 * len(w["step"])},
+            "cpu_baseline": {"value": round(v, 5), "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": "each step = 1 frame of the workload through oracle/ (serial over batch like the "
+                                       "reference, models.py:984)"},
+            "e2e": {"value": round(v, 5), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

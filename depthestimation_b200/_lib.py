@@ -55,7 +55,7 @@ SIGNATURES = {
     "lc_curtain_planes": (c_int, [c_vp, c_fp, c_ip, c_int, c_int, c_fp, c_fp, c_vp]),
     "lc_sense_image": (c_int, [c_vp, c_fp, c_fp, c_fp, c_int, c_int, c_fp, c_fp, c_vp]),
     "lc_sense_likelihood": (c_int, [c_vp, c_fp, c_fp, c_fp, c_int, c_int, c_fp, c_int, c_fp, c_vp]),
-    "lc_sense_fuse": (c_int, [c_vp, c_fp, c_fp, c_fp, c_fp, c_int, c_int, c_fp, c_int, c_int, c_int, c_fp, c_fp,
+    "lc_sense_fuse": (c_int, [c_vp, c_fp, c_fp, c_fp, c_fp, c_int, c_int, c_fp, c_int, c_int, c_int, c_int, c_fp, c_fp,
                               c_vp]),
 }
 

@@ -8,7 +8,7 @@ namespace dpv {
 // utils/img_utils.py:408-436 spread_dpv_hack on one pixel: q[d] = sum_{|j|<=HALF} p[d+j] (zero pad),
 // then q /= sum_d q.  In place, sliding window (no second register array).
 template <int DPT, int HALF>
-__device__ __forceinline__ void spread_renorm(float (&p)[DPT], int D) {
+__device__ __forceinline__ float spread_sum(float (&p)[DPT], int D) {
   float prev[HALF > 0 ? HALF : 1];
 #pragma unroll
   for (int j = 0; j < HALF; j++) prev[j] = 0.f;
@@ -31,6 +31,12 @@ __device__ __forceinline__ void spread_renorm(float (&p)[DPT], int D) {
       total += q;
     }
   }
+  return total;
+}
+
+template <int DPT, int HALF>
+__device__ __forceinline__ void spread_renorm(float (&p)[DPT], int D) {
+  const float total = spread_sum<DPT, HALF>(p, D);
 #pragma unroll
   for (int d = 0; d < DPT; d++)
     if (d < D) p[d] = p[d] / total;

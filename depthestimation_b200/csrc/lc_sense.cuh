@@ -1,0 +1,139 @@
+// Per-pixel light-curtain image formation and likelihood parameters shared by lc_sense_nofma.cu and
+// lc_fuse_nofma.cu (both compiled with -fmad=false: fp32 expressions round exactly as written).
+//   external/lcsim/lcsim/src/dprocessor.cpp:806-887, :942-993 ; util.cpp:47-52
+//   lc/light_curtain.py:847-888, :228-252 ; utils/img_utils.py:176-195
+#pragma once
+#include "dpv_pixel.cuh"
+#include "lc_device.cuh"
+
+namespace dpv {
+
+constexpr int kSenseThreads = 128;
+
+struct Ret {          // one pixel of LCDevice.get_return
+  float x, y, z, inten;   // NaN x => no return
+  float thick;
+};
+
+// util.cpp:47-52
+__device__ __forceinline__ void intersect(const float* P, float rx, float ry, float rz, float out[3]) {
+  float t = -P[3] / (P[0] * rx + P[1] * ry + P[2]);
+  out[0] = rx * t;
+  out[1] = ry * t;
+  out[2] = rz * t;
+}
+
+__device__ __forceinline__ Ret sense_pixel(const LcDeviceView& dv, const float* __restrict__ P, int u, int v,
+                                           float zval, const float* noise) {
+  Ret r;
+  const float rx = dv.nn_x[u], ry = dv.nn_y[v];
+  float c[3], bot[3], top[3];
+  intersect(P, rx, ry, 1.0f, c);
+  float c3 = 0.f;
+  if (c[2] < 0 || fabs((double)c[1]) > 3.0) { c[0] = c[1] = c[2] = c3 = NAN; }      // :818-823
+  intersect(P + 4, rx, ry, 1.0f, bot);
+  intersect(P + 8, rx, ry, 1.0f, top);
+  double dx = (double)(bot[0] - top[0]), dy = (double)(bot[1] - top[1]), dz = (double)(bot[2] - top[2]);
+  const float unc = (float)sqrt(dx * dx + dy * dy + dz * dz);                        // :884-887
+  r.thick = unc;
+  if (!(c[0] != c[0]) && !(unc != unc) && !(zval != zval)) {                         // computeDepthHits
+    float srange = sqrtf(c[0] * c[0] + c[1] * c[1] + c[2] * c[2]);
+    float drange = zval / dv.ztoramap[(size_t)v * dv.W + u];
+    float inten = 0.f;
+    if (dv.hit_mode == 0) {
+      float err = fabsf(drange - srange);
+      float color = 0;
+      if (err >= 0) color = (float)(1. - 1. * (err / (unc / 2.)));
+      if (err < unc / 2.) inten = color;
+    } else {
+      float err = drange - srange;
+      float scale = (float)(err / (unc / 2.));
+      if (fabsf(err) > unc / 2.) scale = (float)(((0.f < err) - (err < 0.f)) * 1.);
+      int idx = (int)(((scale + 1.) / 2.) * (dv.hit_N - 1));
+      idx = min(max(idx, 0), dv.hit_N - 1);
+      inten = dv.hit_lut[idx];
+    }
+    if (noise) {
+      inten += *noise;
+      inten = fmaxf(0.f, fminf(inten, 1.f));
+    }
+    c3 = (float)(int)(255 * inten);
+  }
+  r.x = c[0]; r.y = c[1]; r.z = c[2]; r.inten = c3;
+  return r;
+}
+
+// Per-pixel, per-curtain parameters of the likelihood (sense_high tail + mixed_model)
+struct Lik {
+  float z;      // sensed z * mask
+  float den;    // 2 * sigma^2
+  float A, Bu;  // mixture weight, (1-A) * (1/D)
+};
+
+__device__ __forceinline__ Lik lik_params(const Ret& r, float gt, int D) {
+  float z = r.z, th = r.thick, it = r.inten;
+  if (r.x != r.x) { z = 0.f; it = 0.f; }            // light_curtain.py:847 (whole pixel -> 0)
+  if (th != th) th = 0.f;                           // :848 (only where the thickness itself is NaN)
+  const float mask = gt > 0.f ? 1.f : 0.f;          // :870
+  z = z * mask;
+  th = th * mask;
+  it = it * mask;
+  const float x = it / 255.0f;
+  // mapping(), light_curtain.py:228-244 (m = 20, f = 0.5)
+  float A;
+  if (x > 0.5f) {
+    const float cc = (float)(20.0 / ((20.0 * 0.5 + 0.5) * (20.0 * 0.5 + 0.5)));
+    const float c1 = (float)(1.0 - 20.0 / ((20.0 * 0.5 + 0.5) * (20.0 * 0.5 + 0.5)));
+    A = cc * x + c1;
+  } else {
+    A = (1.0f / (20.f * (0.025f + x))) * -1.0f + 1.0f;
+  }
+  Lik L;
+  L.z = z;
+  const float t10 = th / 10.0f;
+  const float var = t10 * t10;
+  const float sg = sqrtf(var);
+  L.den = 2.f * (sg * sg);
+  L.A = A;
+  L.Bu = (1.0f / (float)D) * (1.f - A);
+  return L;
+}
+
+// exp(-|dc - z|^2 / (2 sigma^2)); exact 0 once the argument is below fp32 exp underflow
+__device__ __forceinline__ float soft_g(float dc, const Lik& L) {
+  float a = fabsf(dc - L.z);
+  a = a * a;
+  if (a > 105.f * L.den) return 0.f;      // (-a)/den < -104.9: expf rounds to +0
+  return expf((-a) / L.den);
+}
+
+__device__ __forceinline__ float clamp0_keepnan(float v) { return (v != v) ? v : fmaxf(v, 0.f); }
+
+// mix[d] before the final normalisation: clamp(g/sg * A + (1/D)*(1-A), 0, inf) with NaN -> -1 first
+__device__ __forceinline__ float mix_value(float g, float sg, const Lik& L) {
+  float n = g / sg;
+  if (n != n) n = -1.f;                   // zero_invalid (img_utils.py:189-190)
+  return clamp0_keepnan(n * L.A + L.Bu);
+}
+
+template <int DPT>
+__device__ __forceinline__ void lik_sums(const float* dc, int D, const Lik& L, float& sg, float& sm) {
+  sg = 0.f;
+#pragma unroll
+  for (int d = 0; d < DPT; d++)
+    if (d < D) sg += soft_g(dc[d], L);
+  sm = 0.f;
+  if (sg > 0.f) {
+#pragma unroll
+    for (int d = 0; d < DPT; d++)
+      if (d < D) sm += mix_value(soft_g(dc[d], L), sg, L);
+  } else {
+    // every bin is 0/0 -> -1 (or NaN sum): the mixture is the same constant in every bin
+    float m = mix_value(0.f, sg, L);
+#pragma unroll
+    for (int d = 0; d < DPT; d++)
+      if (d < D) sm += m;
+  }
+}
+
+}  // namespace dpv

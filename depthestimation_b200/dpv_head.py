@@ -63,12 +63,13 @@ class LcLoopState:
         self.shape = (B, D, H, W, R, nc)
 
 
-def lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n, noise=None, trace=None):
+def lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n, noise=None, trace=None, events=None,
+                 in_prob=False, out_prob=False):
     """One Bayesian iteration (models.py:1027-1122) for the whole batch: 6 kernel launches, no host sync."""
     from ._lib import check, lib, ptr, stream_ptr
     B, D, H, W, R, nc = state.shape
     dev = rig.dev
-    ops.ufield(state.logp, state.mean, K, lc.d_candi, uf_par, bv_log=True, want_depth=False, out=state.uf)
+    ops.ufield(state.logp, state.mean, K, lc.d_candi, uf_par, bv_log=not in_prob, want_depth=False, out=state.uf)
     ops.plan_prepare(state.uf, rig.flow, steps, R, state.umaps, state.argmax, state.field_pre)
     rig.planner.solve(state.umaps.view(B * nc, R, W), state.ks, state.xz, state.counts)
     check(lib().lc_curtain_planes(dev._h, ptr(state.xz), ptr(state.counts), B * nc, W, ptr(state.planes), None,
@@ -76,10 +77,16 @@ def lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n,
     if trace is not None:
         trace.append(dict(uf=state.uf.clone(), ks=state.ks.clone().view(B, nc, W), counts=state.counts.clone(),
                           umaps=state.umaps.clone(), argmax=state.argmax.clone()))
+    if events is not None:                       # bench.py: CUDA-event bracket of the dominant kernel
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
     dev.sense_fuse(state.logp, depth, state.planes, nc, lc.d_candi, spread_iter, spread_n, noise=noise,
-                   out=state.logp, mean=state.mean)
+                   out=state.logp, mean=state.mean, in_prob=in_prob, out_prob=out_prob)
+    if events is not None:
+        e1.record()
+        events.append((e0, e1))
     if trace is not None:
-        trace[-1]["logp"] = state.logp.clone()
+        trace[-1]["logp"] = torch.log(state.logp) if out_prob else state.logp.clone()
 
 
 def lc_process(BV_cur_all, model_input, lc, mode="low", iterations=5, viz=False, score=False, planner="default",
@@ -125,7 +132,9 @@ def lc_process(BV_cur_all, model_input, lc, mode="low", iterations=5, viz=False,
             nz = noise[i]
         elif rig.dev.hit_noise > 0:
             nz = rig.dev.noise_like(B * nc)
-        lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n, noise=nz, trace=trace)
+        # between iterations the volume stays clamped probability (no exp/log per bin); log only in and out
+        lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n, noise=nz, trace=trace,
+                     in_prob=i > 0, out_prob=i < iterations - 1)
     out = state.logp
     if D != D_in:                                                             # :1124
         out = ops.resample_depth(out, D_in, bv_log=True)

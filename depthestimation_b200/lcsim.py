@@ -29,7 +29,7 @@ def generateCameraAngles(K, dist, w, h):
     K = _host_f32(K)
     out = np.zeros(int(w), np.float32)
     check(lib().lc_camera_angles(_hp(K), int(w), int(h), _hp(out)))
-    return list(out)
+    return [float(v) for v in out]        # pybind11 hands std::vector<float> back as Python floats
 
 
 class LCDevice:
@@ -117,7 +117,8 @@ class LCDevice:
                                         ptr(lik), stream_ptr(self.device)))
         return lik
 
-    def sense_fuse(self, logp, depth, planes, nc, d_candi, spread_iter, spread_n, noise=None, out=None, mean=None):
+    def sense_fuse(self, logp, depth, planes, nc, d_candi, spread_iter, spread_n, noise=None, out=None, mean=None,
+                   in_prob=False, out_prob=False):
         """One LC iteration's sensing + Bayesian update (models/models.py:1064-1122), in place if out is logp."""
         from .ops import d_candi_tensor
         B, D = logp.shape[0], logp.shape[1]
@@ -125,7 +126,8 @@ class LCDevice:
         out = torch.empty_like(logp) if out is None else out
         mean = torch.empty(B, self.H, self.W, device=self.device, dtype=torch.float32) if mean is None else mean
         check(lib().lc_sense_fuse(self._h, ptr(logp), ptr(depth), ptr(planes), ptr(noise), B, nc, ptr(dc), D,
-                                  int(spread_iter), int(spread_n), ptr(out), ptr(mean), stream_ptr(self.device)))
+                                  int(spread_iter), int(spread_n), (1 if in_prob else 0) | (2 if out_prob else 0),
+                                  ptr(out), ptr(mean), stream_ptr(self.device)))
         return out, mean
 
     # ---- sim.LCDevice.get_return (sim.py:168-211) -----------------------------------------------

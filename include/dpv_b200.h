@@ -152,10 +152,14 @@ int lc_sense_likelihood(const LcDevice* dev, const float* planes, const float* d
                         int B, int nc, const float* d_candi, int D, float* lik, void* stream);
 /* One LC iteration's sensing + Bayesian update fused (models/models.py:1064-1122): no likelihood
  * volume is materialised.  logp_in [B,D,H,W], depth [B,H,W], planes [B,nc,W,12]
- *   -> logp_out [B,D,H,W] (may alias logp_in), mean_out (nullable) [B,H,W]. */
+ *   -> logp_out [B,D,H,W] (may alias logp_in), mean_out (nullable) [B,H,W].
+ * flags: 0 = log-probability in and out (the reference's format); LC_FUSE_IN_PROB / LC_FUSE_OUT_PROB keep the
+ * volume as clamped probability between the iterations of one lc_process call (no exp/log per bin). */
+#define LC_FUSE_IN_PROB 1
+#define LC_FUSE_OUT_PROB 2
 int lc_sense_fuse(const LcDevice* dev, const float* logp_in, const float* depth, const float* planes,
                   const float* noise, int B, int nc, const float* d_candi, int D, int spread_iter,
-                  int spread_n, float* logp_out, float* mean_out, void* stream);
+                  int spread_n, int flags, float* logp_out, float* mean_out, void* stream);
 
 #ifdef __cplusplus
 }

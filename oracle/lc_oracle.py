@@ -146,11 +146,12 @@ def lc_loop(logp, depth_gt, lc, K_up, uf_par, iterations, steps, spread_iter, sp
         final = O.resample_depth_bins(final, N=len(lc.d_candi), BV_log=True)   # :1015-1016
     for it in range(iterations):
         uf, _ = O.ufield(final, lc.d_candi, K, uf_par, BV_log=True)           # :1029
+        uf_rec = uf.clone() if trace is not None else None                    # plan() edits uf in place (:654-662)
         paths, umaps, idx = lc.plan(uf.squeeze(0), steps, return_indices=True)  # :1050
         liks = [lc.sense(depth_gt, p[0])[0] for p in paths]                    # :1066
         final = O.bayes_fuse(final, liks, spread_iter, spread_n)              # :1097-1122
         if trace is not None:
-            trace.append(dict(uf=uf, ks=[p[1] for p in paths], umaps=umaps, argmax=idx, logp=final))
+            trace.append(dict(uf=uf_rec, ks=[p[1] for p in paths], umaps=umaps, argmax=idx, logp=final))
     if final.shape[1] != start.shape[1]:
         final = O.resample_depth_bins(final, N=start.shape[1], BV_log=True)   # :1124
     return final

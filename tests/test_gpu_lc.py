@@ -180,3 +180,18 @@ def test_lc_process_golden_and_oracle_trace():
                                   lc, mode="high", iterations=2, params=prm, cfg="kitti")
     one, _ = dpv_head.lc_process(cu(g["logp"]), mi, lc, mode="high", iterations=2, params=prm, cfg="kitti")
     assert torch.equal(both[0], one[0]) and torch.equal(both[1], one[0])
+
+
+def test_pipeline_tiny_matches_oracle_step():
+    """The whole hot path (DpvLcPipeline.step, what bench.py times) against the CPU oracle's step."""
+    import bench
+    from depthestimation_b200.pipeline import DpvLcPipeline, synthetic_batch
+    host, meta = synthetic_batch("tiny", seed=3)
+    pipe = DpvLcPipeline(meta, torch.device("cuda", 0))
+    out = pipe.step({k: v.cuda() for k, v in host.items()})
+    exp = bench.oracle_step(host, meta)
+    close(out["logp_lc"], exp, atol=1e-5)
+    close(out["depth_lc"], torch.cat([O.dpv_expectation(exp[b:b + 1], meta["d_candi"], True) for b in range(meta["B"])]),
+          atol=1e-5)
+    assert torch.equal(out["logp_lc"].argmax(1).cpu(), exp.argmax(1))
+    assert torch.equal(out["carry_lc"].cpu(), O.carry_quarter(out["logp_lc"].cpu()))

@@ -130,9 +130,14 @@ def test_dpv_utils_golden():
     close(IU.dpv_to_depthmap(logp, d, BV_log=True), g["mean"])
     close(IU.spread_dpv_hack(torch.exp(logp), 5), g["spread5"])
     close(IU.spread_dpv_hack(torch.exp(logp), 3), g["spread3"])
-    up = IU.upsample_dpv(logp, N=16, BV_log=True)
-    close(up, g["up16"], atol=1e-5)
-    close(IU.upsample_dpv(cu(g["up16"]), N=8, BV_log=True), g["down8"], atol=1e-5)
+    # bins whose probability underflows fp32 (log p < -87) are -inf or a denormal's log depending on the exp
+    # implementation: compare those in probability space, the rest in log space
+    up = IU.upsample_dpv(logp, N=16, BV_log=True).cpu()
+    dn = IU.upsample_dpv(cu(g["up16"]), N=8, BV_log=True).cpu()
+    for got, ref in ((up, torch.tensor(g["up16"])), (dn, torch.tensor(g["down8"]))):
+        big = ref > -80
+        close(got[big], ref[big], atol=1e-5)
+        close(torch.exp(got), torch.exp(ref), atol=1e-30)
     for key in ("kitti", "sweep"):
         uf, dz = IU.gen_ufield(logp, d, K, BV_log=True, cfg="/data/%s/x" % key)
         close(uf, g["uf_" + key], what=key)
@@ -165,9 +170,9 @@ def test_ufield_kitti_shape_properties():
     mean = O.dpv_expectation(logp, d, True)[0]
     yf = (torch.arange(H).float().unsqueeze(1) + 5 - Kup[1, 2]) / Kup[1, 1]
     Y = yf * mean
-    near = ((Y - 0.6).abs() < 1e-4) | ((Y - 0.9).abs() < 1e-4)
+    near = ((Y - 0.6).abs() < 1e-5) | ((Y - 0.9).abs() < 1e-5)
     ok = ~near.any(0)
-    assert ok.float().mean() > 0.95
+    assert ok.float().mean() > 0.97
     close(uf[0][:, ok.cuda()], exp_uf[0][:, ok])
     close(dz[0][:, ok.cuda()], exp_dz[0][:, ok])
 
