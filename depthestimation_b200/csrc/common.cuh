@@ -47,6 +47,13 @@ inline int check_launch(const char* what) {
 __device__ __forceinline__ float ld_stream(const float* p) { return __ldcs(p); }
 __device__ __forceinline__ void st_stream(float* p, float v) { __stcs(p, v); }
 
+// 2^x on the MUFU pipe (ex2.approx.ftz: 2 ulp; denormal results flush to 0)
+__device__ __forceinline__ float exp2f_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // grid_sample(align_corners=False) un-normalisation, ATen grid_sampler_unnormalize: ((g+1)*N-1)/2
 __device__ __forceinline__ float gs_unnormalize(float g, int n) {
   return __fdiv_rn(__fsub_rn(__fmul_rn(__fadd_rn(g, 1.f), (float)n), 1.f), 2.f);

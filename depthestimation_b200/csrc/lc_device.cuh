@@ -39,3 +39,13 @@ struct LcDevice {
   float* d_tables = nullptr;   // one device allocation holding all tables
   LcDeviceView view;
 };
+
+// DP planner handle (lc_planner.cu builds it, lc_planner_solve.cu uses it)
+struct LcPlanner {
+  int W = 0, R = 0;
+  float max_d_las = 0.f;
+  long long edges = 0;
+  float* d_theta = nullptr;     // [W,R]
+  float* d_xz = nullptr;        // [W,R,2]
+  uint8_t* d_win = nullptr;     // [W,R,2] lo,hi (lo > hi = no edge); last ray has none
+};

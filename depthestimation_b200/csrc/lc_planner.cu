@@ -19,156 +19,7 @@
 
 #define LCP_PI 3.14159265 /* planning.h:11 (truncated literal) */
 
-struct LcPlanner {
-  int W = 0, R = 0;
-  float max_d_las = 0.f;
-  long long edges = 0;
-  float* d_theta = nullptr;     // [W,R]
-  float* d_xz = nullptr;        // [W,R,2]
-  uint8_t* d_win = nullptr;     // [W,R,2] lo,hi (lo > hi = no edge); last ray has none
-};
 
-namespace dpv {
-
-struct Cand {
-  float u, l;
-  int e;    // -1 = no edge (path ends here)
-};
-
-// reference order (planning.cpp:210-217 + first-in-edge-order on full ties)
-__device__ __forceinline__ bool cand_better(const Cand& a, const Cand& b) {
-  if (a.u > b.u) return true;
-  if (a.u == b.u) {
-    if (a.l < b.l) return true;
-    if (a.l == b.l) return a.e < b.e;
-  }
-  return false;
-}
-
-template <int LANES>
-__global__ void __launch_bounds__(1024)
-planner_solve_kernel(const float* __restrict__ umaps, int W, int R, const float* __restrict__ theta,
-                     const float* __restrict__ node_xz, const uint8_t* __restrict__ win, int32_t* __restrict__ ks,
-                     float* __restrict__ xz, int32_t* __restrict__ counts) {
-  extern __shared__ unsigned char smraw[];
-  float* unc = reinterpret_cast<float*>(smraw);          // [2][R]
-  float* las = unc + 2 * R;                              // [2][R]
-  float* th = las + 2 * R;                               // [2][R]
-  int16_t* path = reinterpret_cast<int16_t*>(th + 2 * R);   // [W]
-  uint8_t* sub = reinterpret_cast<uint8_t*>(path + ((W + 1) & ~1));   // [W][R]
-  __shared__ int s_cnt;
-
-  const int k = threadIdx.x / LANES, s = threadIdx.x % LANES;
-  const bool active = k < R;
-  const float* umap = umaps + (size_t)blockIdx.x * R * W;
-  const unsigned gmask = 0xffffffffu;
-
-  // Rays are processed in groups of LANES: lane s of node k prefetches (u, theta, window) of ray
-  // i0 - s one group ahead; values are handed round with shuffles.
-  float pu = 0.f, pt = 0.f;
-  int plo = 1, phi = 0;
-  auto prefetch = [&](int i0) {
-    int i = i0 - s;
-    if (active && i >= 0) {
-      pu = __ldg(umap + (size_t)k * W + i);
-      pt = __ldg(theta + (size_t)i * R + k);
-      if (i < W - 1) {
-        plo = win[((size_t)i * R + k) * 2];
-        phi = win[((size_t)i * R + k) * 2 + 1];
-      } else {
-        plo = 1; phi = 0;
-      }
-    }
-  };
-  prefetch(W - 1);
-  int buf = 0;
-  for (int i0 = W - 1; i0 >= 0; i0 -= LANES) {
-    const float cu = pu, ct = pt;
-    const int clo = plo, chi = phi;
-    prefetch(i0 - LANES);
-    for (int j = 0; j < LANES && i0 - j >= 0; j++) {
-      const int i = i0 - j;
-      const int src = (threadIdx.x & 31 & ~(LANES - 1)) + j;
-      const float u = __shfl_sync(gmask, cu, src);
-      const float tn = __shfl_sync(gmask, ct, src);
-      const int lo = __shfl_sync(gmask, clo, src);
-      const int hi = __shfl_sync(gmask, chi, src);
-      const float* uncn = unc + (buf ^ 1) * R;
-      const float* lasn = las + (buf ^ 1) * R;
-      const float* thn = th + (buf ^ 1) * R;
-      Cand best;
-      best.u = u; best.l = 0.f; best.e = -1;                  // Trajectory(node): planning.cpp:169-184
-      if (active) {
-        for (int e = lo + s; e <= hi; e += LANES) {
-          Cand c;
-          c.u = __fadd_rn(u, uncn[e]);                        // :194
-          float dth = __fsub_rn(thn[e], tn);
-          c.l = __fadd_rn(__fmul_rn(dth, dth), lasn[e]);      // :197-198
-          c.e = e;
-          if (cand_better(c, best)) best = c;
-        }
-      }
-#pragma unroll
-      for (int off = LANES / 2; off > 0; off >>= 1) {
-        Cand o;
-        o.u = __shfl_xor_sync(gmask, best.u, off);
-        o.l = __shfl_xor_sync(gmask, best.l, off);
-        o.e = __shfl_xor_sync(gmask, best.e, off);
-        if (cand_better(o, best)) best = o;
-      }
-      if (active && s == 0) {
-        unc[buf * R + k] = best.u;
-        las[buf * R + k] = best.l;
-        th[buf * R + k] = tn;
-        sub[(size_t)i * R + k] = best.e < 0 ? 255 : (uint8_t)best.e;
-      }
-      __syncthreads();
-      buf ^= 1;
-    }
-  }
-  // ray 0 results are in buffer buf^1.  Best start against a default (0,0,null) trajectory (:99-104)
-  if (threadIdx.x == 0) {
-    const float* u0 = unc + (buf ^ 1) * R;
-    const float* l0 = las + (buf ^ 1) * R;
-    float bu = 0.f, bl = 0.f;
-    int bk = -1;
-    for (int kk = 0; kk < R; kk++) {
-      float tu = u0[kk], tl = l0[kk];
-      bool gt = (tu > bu) ? true : ((tu == bu) ? (tl < bl) : false);
-      if (gt) { bu = tu; bl = tl; bk = kk; }
-    }
-    int cnt = 0;
-    if (bk >= 0) {                       // the reference dereferences a null node otherwise (:116)
-      int i = 0, kk = bk;
-      while (true) {
-        path[cnt++] = (int16_t)kk;
-        int nx = sub[(size_t)i * R + kk];
-        if (nx == 255 || i == W - 1) break;
-        kk = nx;
-        i++;
-      }
-    }
-    s_cnt = cnt;
-    if (counts) counts[blockIdx.x] = cnt;
-  }
-  __syncthreads();
-  const int cnt = s_cnt;
-  for (int i = threadIdx.x; i < W; i += blockDim.x) {
-    int kk = i < cnt ? path[i] : -1;
-    if (ks) ks[(size_t)blockIdx.x * W + i] = kk;
-    if (xz) {
-      float x = 0.f, z = 0.f;
-      if (kk >= 0) {
-        x = node_xz[((size_t)i * R + kk) * 2];
-        z = node_xz[((size_t)i * R + kk) * 2 + 1];
-      }
-      xz[((size_t)blockIdx.x * W + i) * 2] = x;
-      xz[((size_t)blockIdx.x * W + i) * 2 + 1] = z;
-    }
-  }
-}
-
-}  // namespace dpv
 
 using namespace dpv;
 
@@ -256,30 +107,5 @@ void lc_planner_destroy(LcPlanner* p) {
 }
 
 long long lc_planner_edge_count(const LcPlanner* p) { return p ? p->edges : 0; }
-
-int lc_planner_solve(LcPlanner* p, const float* umaps, int n, int32_t* ks, float* xz, int32_t* counts,
-                     void* stream) {
-  DPV_REQUIRE(p && umaps, "lc_planner_solve: null pointer");
-  DPV_REQUIRE(n > 0, "lc_planner_solve: n=%d", n);
-  const int W = p->W, R = p->R;
-  int lanes = 8;
-  while (lanes > 1 && R * lanes > 1024) lanes >>= 1;
-  int threads = ((R * lanes + 31) / 32) * 32;
-  size_t smem = (size_t)6 * R * 4 + (size_t)((W + 1) & ~1) * 2 + (size_t)W * R;
-  cudaStream_t st = (cudaStream_t)stream;
-#define LAUNCH(L)                                                                                              \
-  do {                                                                                                         \
-    DPV_CUDA(cudaFuncSetAttribute(planner_solve_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize,        \
-                                  (int)smem));                                                                 \
-    planner_solve_kernel<L><<<n, threads, smem, st>>>(umaps, W, R, p->d_theta, p->d_xz, p->d_win, ks, xz,      \
-                                                      counts);                                                 \
-  } while (0)
-  if (lanes == 8) LAUNCH(8);
-  else if (lanes == 4) LAUNCH(4);
-  else if (lanes == 2) LAUNCH(2);
-  else LAUNCH(1);
-#undef LAUNCH
-  return check_launch("lc_planner_solve");
-}
 
 }  // extern "C"
