@@ -261,6 +261,7 @@ int lc_device_hit_lut(const LcDevice* d, float* out) {
 namespace dpv {
 
 constexpr int kPlaneThreads = 256;
+constexpr int kPlaneCols = 128;     // columns per CTA (grid.y splits the image width)
 
 __device__ __forceinline__ float point_angle(float x, float z) {
   // -((atan2f(z, x) * 180 / M_PI) - 90) + 0 + 0   (dprocessor.cpp:528-531, 762)
@@ -322,7 +323,11 @@ curtain_planes_kernel(LcDeviceView dv, const float* __restrict__ xz, const int32
   const bool all_pts = (ngood == 0);            // findCameraIntersectionsOpt :519-523
   if (all_pts) ngood = N;
 
-  for (int i = threadIdx.x; i < dv.W; i += kPlaneThreads) {
+  // Columns of this CTA: [col0, col1).  Each WARP searches one column at a time: its 32 lanes test 32
+  // consecutive segments j, and the lowest hitting lane is exactly the reference's "first j that hits".
+  const int col0 = blockIdx.y * kPlaneCols, col1 = min(col0 + kPlaneCols, dv.W);
+  __shared__ float s_dsg[kPlaneCols][4];
+  for (int i = col0 + warp; i < col1; i += kPlaneThreads / 32) {
     // ---- findCameraIntersectionsOpt (dprocessor.cpp:514-634) for column i
     float dx = dv.mid_x[i], dz = dv.mid_z[i];
     float nrm = sqrtf(dx * dx + dz * dz);
@@ -332,29 +337,51 @@ curtain_planes_kernel(LcDeviceView dv, const float* __restrict__ xz, const int32
     float ix = 0.f, iz = 0.f;
     for (int li = 0; li < 2 && !found; li++) {
       const float lim = li == 0 ? 1.f : 100.f;
-      for (int j = 0; j + 1 < ngood; j++) {
-        const int a = all_pts ? j : good[j], b = all_pts ? j + 1 : good[j + 1];
-        const float pa = ang[a], pb = ang[b];
-        if (pa != pb)
-          if (fabsf(pa - cam_angle) > lim && fabsf(pb - cam_angle) > lim) continue;
-        const float p1x = px[a], p1z = pz[a], p2x = px[b], p2z = pz[b];
-        if (p1x == p2x && p1z == p2z) continue;
-        float ex = p2x - p1x, ez = p2z - p1z;
-        float nx = -ez, nz = ex;
-        float n2 = nx * nx + nz * nz;
-        if (n2 > 0.f) { float s = sqrtf(n2); nx = nx / s; nz = nz / s; }
-        float off = -(p1x * nx + p1z * nz);
-        float t = -(off + (nx * 0.f + nz * 0.f)) / (nx * dx + nz * dz);
-        float qx = 0.f + dx * t, qz = 0.f + dz * t;
-        float kk = ex * ex + ez * ez;
-        float kp = ex * (qx - p1x) + ez * (qz - p1z);
-        if (kp < 0) found = false;
-        else if (kp > kk) found = false;
-        else if (kp == kp && kk == kk) { found = true; ix = qx; iz = qz; }
-        else found = false;
-        if (found) break;
+      for (int j0 = 0; j0 + 1 < ngood && !found; j0 += 32) {
+        const int j = j0 + lane;
+        bool hit = false;
+        float qx = 0.f, qz = 0.f;
+        if (j + 1 < ngood) {
+          const int a = all_pts ? j : good[j], b = all_pts ? j + 1 : good[j + 1];
+          const float pa = ang[a], pb = ang[b];
+          bool gate = true;
+          if (pa != pb)
+            if (fabsf(pa - cam_angle) > lim && fabsf(pb - cam_angle) > lim) gate = false;
+          const float p1x = px[a], p1z = pz[a], p2x = px[b], p2z = pz[b];
+          if (p1x == p2x && p1z == p2z) gate = false;
+          if (gate) {
+            float ex = p2x - p1x, ez = p2z - p1z;
+            float nx = -ez, nz = ex;
+            float n2 = nx * nx + nz * nz;
+            if (n2 > 0.f) { float s = sqrtf(n2); nx = nx / s; nz = nz / s; }
+            float off = -(p1x * nx + p1z * nz);
+            float t = -(off + (nx * 0.f + nz * 0.f)) / (nx * dx + nz * dz);
+            qx = 0.f + dx * t; qz = 0.f + dz * t;
+            float kk = ex * ex + ez * ez;
+            float kp = ex * (qx - p1x) + ez * (qz - p1z);
+            if (kp < 0) hit = false;
+            else if (kp > kk) hit = false;
+            else if (kp == kp && kk == kk) hit = true;
+            else hit = false;
+          }
+        }
+        const unsigned mask = __ballot_sync(0xffffffffu, hit);
+        if (mask) {
+          const int srcl = __ffs(mask) - 1;
+          ix = __shfl_sync(0xffffffffu, qx, srcl);
+          iz = __shfl_sync(0xffffffffu, qz, srcl);
+          found = true;
+        }
       }
     }
+    if (lane == 0) {
+      s_dsg[i - col0][0] = ix; s_dsg[i - col0][1] = iz; s_dsg[i - col0][2] = found ? 1.f : 0.f;
+    }
+  }
+  __syncthreads();
+  for (int i = col0 + threadIdx.x; i < col1; i += kPlaneThreads) {
+    bool found = s_dsg[i - col0][2] != 0.f;
+    const float ix = s_dsg[i - col0][0], iz = s_dsg[i - col0][1];
     float cp = (float)i / float(dv.W);
     if (dv.limit > 0) if (cp > dv.limit) found = false;
     if (dv.limit < 0) if (cp < fabsf(dv.limit)) found = false;
@@ -407,7 +434,8 @@ extern "C" int lc_curtain_planes(const LcDevice* dev, const float* xz, const int
   DPV_REQUIRE(smem <= 200 * 1024, "lc_curtain_planes: npts=%d too large", npts);
   if (smem > 48 * 1024)
     DPV_CUDA(cudaFuncSetAttribute(dpv::curtain_planes_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dpv::curtain_planes_kernel<<<n, dpv::kPlaneThreads, smem, (cudaStream_t)stream>>>(dev->view, xz, counts, npts,
-                                                                                    planes, design);
+  dim3 grid(n, (dev->W + dpv::kPlaneCols - 1) / dpv::kPlaneCols);
+  dpv::curtain_planes_kernel<<<grid, dpv::kPlaneThreads, smem, (cudaStream_t)stream>>>(dev->view, xz, counts, npts,
+                                                                                       planes, design);
   return dpv::check_launch("lc_curtain_planes");
 }
