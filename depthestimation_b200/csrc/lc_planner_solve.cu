@@ -4,14 +4,18 @@
 // dp(i,k) = umap(k,i) + best over the edge window [lo,hi] of ray i+1, rays processed right to left.
 // The reference's total order over a node's edges is
 //   (unc = fl(u + unc[e]) larger) > (las = dth^2 + las[e] smaller) > (first in edge order), "no edge" first,
-// and max-propagation through zero regions of the map makes exact ties in the first key COMMON, so the
-// second key decides real paths and must be evaluated exactly.  Here LANES threads share one node and
-// scan its window in two cheap vectorised passes over shared memory (LDS.128):
-//   pass 1: m = max unc[e]  (fl(u + x) is monotone in x, so fl(u + m) is the winning first key);
-//   pass 2: among the e with fl(u + unc[e]) == fl(u + m), the lexicographic minimum of (las, e).
-// Both passes are plain associative reductions, so the selected index is exactly the one the reference's
-// sequential strict-'>' scan selects: results are bit-exact.  One CTA = one umap; back-pointers for all
-// W x R nodes stay in shared memory (W*R bytes) for the final path unroll.
+// and max-propagation through zero regions of the map makes exact ties in the first key COMMON (5-20 % of the
+// nodes), so the second key decides real paths and must be evaluated exactly.  The kernel is bound by
+// instruction issue on the ~W*R*|window| edge visits, so the scan is organised to touch most edges at a
+// quarter instruction each:
+//   * the ray just finished keeps, next to unc[], the maxima of its aligned groups of four (qm[]);
+//   * pass 1: window max m from qm[] (interior) + the two boundary groups entry by entry;
+//     fl(u + x) is monotone in x, so fl(u + m) is the winning first key;
+//   * pass 2: a group can hold a first-key tie only if fl(u + qm) == fl(u + m); only those groups are
+//     opened and their entries compared exactly on (las, e).
+// Both passes are associative reductions under the reference's order, so the selected index is exactly the
+// one its sequential strict-'>' scan selects: results are bit-exact.  One CTA = one umap, LANES threads per
+// node; back-pointers for all W x R nodes stay in shared memory (W*R bytes) for the final path unroll.
 #include <cstdlib>
 
 #include "lc_device.cuh"
@@ -23,113 +27,153 @@ struct RayIn {
   int lo, hi;
 };
 
+struct Best {          // running minimum of (las, e) among first-key ties
+  float l;
+  int e;
+};
+
 template <int LANES>
 __global__ void __launch_bounds__(1024)
 planner_solve_kernel(const float* __restrict__ umaps, int W, int R, int RP, const float* __restrict__ theta,
                      const float* __restrict__ node_xz, const uint8_t* __restrict__ win, int32_t* __restrict__ ks,
                      float* __restrict__ xz, int32_t* __restrict__ counts) {
   extern __shared__ __align__(16) unsigned char smraw[];
+  const int NQ = RP / 4;
   float* unc = reinterpret_cast<float*>(smraw);            // [2][RP]   RP = R rounded up to 4 (pad = -inf)
   float* las = unc + 2 * RP;                               // [2][RP]
   float* th = las + 2 * RP;                                // [2][RP]
-  int16_t* path = reinterpret_cast<int16_t*>(th + 2 * RP); // [W rounded to even]
-  uint8_t* sub = reinterpret_cast<uint8_t*>(path + ((W + 1) & ~1));     // [W][R]
+  float* qm = th + 2 * RP;                                 // [2][NQ]   max of unc[4q..4q+3]
+  int16_t* path = reinterpret_cast<int16_t*>(qm + 2 * NQ + (NQ & 1) * 2);   // [W rounded to even]
+  uint8_t* sub = reinterpret_cast<uint8_t*>(path + ((W + 1) & ~1));         // [W][R]
   __shared__ int s_cnt;
 
   const int k = threadIdx.x / LANES, s = threadIdx.x % LANES;
   const bool active = k < R;
   const float* umap = umaps + (size_t)blockIdx.x * R * W;
   const unsigned full = 0xffffffffu;
-  // shuffles inside per-node branches name only the node's own lane group (branches differ between nodes of a warp)
-  const unsigned gmask = (LANES == 32 ? 0xffffffffu : ((1u << LANES) - 1u)) << ((threadIdx.x & 31) & ~(LANES - 1));
-  for (int i = threadIdx.x; i < 6 * RP; i += blockDim.x) unc[i] = -INFINITY;   // padding lanes never win a max
+  // shuffles inside per-node branches name only the node's own lanes (branches differ between nodes of a warp)
+  const unsigned gmask = ((1u << LANES) - 1u) << ((threadIdx.x & 31) & ~(LANES - 1));
+  for (int i = threadIdx.x; i < 6 * RP + 2 * NQ; i += blockDim.x) unc[i] = -INFINITY;   // pads never win a max
   __syncthreads();
 
-  // lane s of a node prefetches (u, theta, window) of ray i0 - s one group of LANES rays ahead
-  RayIn pre;
-  auto fetch = [&](int i0) {
-    const int i = i0 - s;
-    pre.u = 0.f; pre.th = 0.f; pre.lo = 1; pre.hi = 0;
+  auto fetch = [&](int i) {
+    RayIn r;
+    r.u = 0.f; r.th = 0.f; r.lo = 1; r.hi = 0;
     if (active && i >= 0) {
-      pre.u = __ldg(umap + (size_t)k * W + i);
-      pre.th = __ldg(theta + (size_t)i * R + k);
+      r.u = __ldg(umap + (size_t)k * W + i);
+      r.th = __ldg(theta + (size_t)i * R + k);
       if (i < W - 1) {
         const uchar2 w2 = *reinterpret_cast<const uchar2*>(win + ((size_t)i * R + k) * 2);
-        pre.lo = w2.x; pre.hi = w2.y;
+        r.lo = w2.x; r.hi = w2.y;
       }
     }
+    return r;
   };
-  fetch(W - 1);
+  // software pipeline: inputs of ray i-3 are requested while ray i is processed
+  RayIn cur = fetch(W - 1), n1 = fetch(W - 2), n2 = fetch(W - 3);
   int buf = 0;
-  for (int i0 = W - 1; i0 >= 0; i0 -= LANES) {
-    const RayIn grp = pre;
-    fetch(i0 - LANES);
-    for (int j = 0; j < LANES && i0 - j >= 0; j++) {
-      const int i = i0 - j;
-      const int src = (threadIdx.x & 31 & ~(LANES - 1)) + j;
-      const float u = __shfl_sync(full, grp.u, src);
-      const float tn = __shfl_sync(full, grp.th, src);
-      const int lo = __shfl_sync(full, grp.lo, src);
-      const int hi = __shfl_sync(full, grp.hi, src);
-      const float4* unc4 = reinterpret_cast<const float4*>(unc + (buf ^ 1) * RP);
-      const float4* las4 = reinterpret_cast<const float4*>(las + (buf ^ 1) * RP);
-      const float4* th4 = reinterpret_cast<const float4*>(th + (buf ^ 1) * RP);
-      float bu = u, bl = 0.f;                                   // Trajectory(node): planning.cpp:169-184
-      int be = -1;
-      if (lo <= hi) {                                           // uniform within the node's lane group
-        const int q0 = lo >> 2, q1 = hi >> 2;
-        // ---- pass 1: window maximum of unc[] (entries outside [lo,hi] masked) ----
-        float m = -INFINITY;
-        for (int q = q0 + s; q <= q1; q += LANES) {
-          const float4 v = unc4[q];
-          const int e = q << 2;
-          float a = (e >= lo && e <= hi) ? v.x : -INFINITY;
-          float b = (e + 1 >= lo && e + 1 <= hi) ? v.y : -INFINITY;
-          float c = (e + 2 >= lo && e + 2 <= hi) ? v.z : -INFINITY;
-          float d = (e + 3 >= lo && e + 3 <= hi) ? v.w : -INFINITY;
-          m = fmaxf(fmaxf(m, fmaxf(a, b)), fmaxf(c, d));
-        }
-#pragma unroll
-        for (int off = LANES / 2; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(gmask, m, off));
-        const float tmax = __fadd_rn(u, m);                     // :194
-        if (tmax > u) {                                         // strict '>' against the bare node
-          // ---- pass 2: among first-key ties, min (las, e) ----
-          float cl = INFINITY;
-          int ce = 0x7fffffff;
-          for (int q = q0 + s; q <= q1; q += LANES) {
-            const float4 v = unc4[q];
-            const int e = q << 2;
-            const bool ha = (e >= lo && e <= hi) && __fadd_rn(u, v.x) == tmax;
-            const bool hb = (e + 1 >= lo && e + 1 <= hi) && __fadd_rn(u, v.y) == tmax;
-            const bool hc = (e + 2 >= lo && e + 2 <= hi) && __fadd_rn(u, v.z) == tmax;
-            const bool hd = (e + 3 >= lo && e + 3 <= hi) && __fadd_rn(u, v.w) == tmax;
-            if (ha | hb | hc | hd) {
-              const float4 t4 = th4[q], l4 = las4[q];
-              float dth, tl;
-              if (ha) { dth = __fsub_rn(t4.x, tn); tl = __fadd_rn(__fmul_rn(dth, dth), l4.x); if (tl < cl) { cl = tl; ce = e; } }
-              if (hb) { dth = __fsub_rn(t4.y, tn); tl = __fadd_rn(__fmul_rn(dth, dth), l4.y); if (tl < cl) { cl = tl; ce = e + 1; } }
-              if (hc) { dth = __fsub_rn(t4.z, tn); tl = __fadd_rn(__fmul_rn(dth, dth), l4.z); if (tl < cl) { cl = tl; ce = e + 2; } }
-              if (hd) { dth = __fsub_rn(t4.w, tn); tl = __fadd_rn(__fmul_rn(dth, dth), l4.w); if (tl < cl) { cl = tl; ce = e + 3; } }
-            }
-          }
-#pragma unroll
-          for (int off = LANES / 2; off > 0; off >>= 1) {
-            const float ol = __shfl_xor_sync(gmask, cl, off);
-            const int oe = __shfl_xor_sync(gmask, ce, off);
-            if (ol < cl || (ol == cl && oe < ce)) { cl = ol; ce = oe; }
-          }
-          bu = tmax; bl = cl; be = ce;                          // :197-198, :210-217
-        }
+  for (int i = W - 1; i >= 0; i--) {
+    const RayIn in = cur;
+    cur = n1; n1 = n2; n2 = fetch(i - 3);
+    const float* uncn = unc + (buf ^ 1) * RP;
+    const float* lasn = las + (buf ^ 1) * RP;
+    const float* thn = th + (buf ^ 1) * RP;
+    const float* qmn = qm + (buf ^ 1) * NQ;
+    const float u = in.u, tn = in.th;
+    const int lo = in.lo, hi = in.hi;
+    float bu = u, bl = 0.f;                                     // Trajectory(node): planning.cpp:169-184
+    int be = -1;
+    if (lo <= hi) {                                             // same for the LANES threads of a node
+      const int qlo = lo >> 2, qhi = hi >> 2;
+      // ---- pass 1: window maximum --------------------------------------------------------
+      float m = -INFINITY, mb = -INFINITY;                      // mb: this lane's boundary-group maximum
+      if (s == 0) {                                             // boundary groups, entry by entry
+        const float4 a = reinterpret_cast<const float4*>(uncn)[qlo];
+        const int e = qlo << 2;
+        if (e >= lo && e <= hi) m = fmaxf(m, a.x);
+        if (e + 1 >= lo && e + 1 <= hi) m = fmaxf(m, a.y);
+        if (e + 2 >= lo && e + 2 <= hi) m = fmaxf(m, a.z);
+        if (e + 3 >= lo && e + 3 <= hi) m = fmaxf(m, a.w);
+        mb = m;
       }
-      if (active && s == 0) {
+      float mb2 = -INFINITY;
+      if (s == LANES - 1 && qhi != qlo) {
+        const float4 a = reinterpret_cast<const float4*>(uncn)[qhi];
+        const int e = qhi << 2;
+        if (e <= hi) mb2 = fmaxf(mb2, a.x);
+        if (e + 1 <= hi) mb2 = fmaxf(mb2, a.y);
+        if (e + 2 <= hi) mb2 = fmaxf(mb2, a.z);
+        if (e + 3 <= hi) mb2 = fmaxf(mb2, a.w);
+        m = fmaxf(m, mb2);
+      }
+      {
+        float m1 = -INFINITY;
+        int q = qlo + 1 + s;
+        for (; q + LANES < qhi; q += 2 * LANES) {               // interior groups: one value per four edges
+          m = fmaxf(m, qmn[q]);
+          m1 = fmaxf(m1, qmn[q + LANES]);
+        }
+        if (q < qhi) m = fmaxf(m, qmn[q]);
+        m = fmaxf(m, m1);
+      }
+#pragma unroll
+      for (int off = LANES / 2; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(gmask, m, off));
+      const float tmax = __fadd_rn(u, m);                       // :194
+      if (tmax > u) {                                           // strict '>' against the bare node
+        // ---- pass 2: among first-key ties, min (las, e) ---------------------------------
+        Best bb;
+        bb.l = INFINITY; bb.e = 0x7fffffff;
+        auto open_group = [&](int q) {
+          const float4 v = reinterpret_cast<const float4*>(uncn)[q];
+          const float4 t4 = reinterpret_cast<const float4*>(thn)[q];
+          const float4 l4 = reinterpret_cast<const float4*>(lasn)[q];
+          const int e = q << 2;
+          float dth, tl;
+          if (e >= lo && e <= hi && __fadd_rn(u, v.x) == tmax) {
+            dth = __fsub_rn(t4.x, tn); tl = __fadd_rn(__fmul_rn(dth, dth), l4.x);          // :197-198
+            if (tl < bb.l || (tl == bb.l && e < bb.e)) { bb.l = tl; bb.e = e; }
+          }
+          if (e + 1 >= lo && e + 1 <= hi && __fadd_rn(u, v.y) == tmax) {
+            dth = __fsub_rn(t4.y, tn); tl = __fadd_rn(__fmul_rn(dth, dth), l4.y);
+            if (tl < bb.l || (tl == bb.l && e + 1 < bb.e)) { bb.l = tl; bb.e = e + 1; }
+          }
+          if (e + 2 >= lo && e + 2 <= hi && __fadd_rn(u, v.z) == tmax) {
+            dth = __fsub_rn(t4.z, tn); tl = __fadd_rn(__fmul_rn(dth, dth), l4.z);
+            if (tl < bb.l || (tl == bb.l && e + 2 < bb.e)) { bb.l = tl; bb.e = e + 2; }
+          }
+          if (e + 3 >= lo && e + 3 <= hi && __fadd_rn(u, v.w) == tmax) {
+            dth = __fsub_rn(t4.w, tn); tl = __fadd_rn(__fmul_rn(dth, dth), l4.w);
+            if (tl < bb.l || (tl == bb.l && e + 3 < bb.e)) { bb.l = tl; bb.e = e + 3; }
+          }
+        };
+        if (s == 0 && __fadd_rn(u, mb) == tmax) open_group(qlo);
+        if (s == LANES - 1 && qhi != qlo && __fadd_rn(u, mb2) == tmax) open_group(qhi);
+        for (int q = qlo + 1 + s; q < qhi; q += LANES)
+          if (__fadd_rn(u, qmn[q]) == tmax) open_group(q);
+#pragma unroll
+        for (int off = LANES / 2; off > 0; off >>= 1) {
+          const float ol = __shfl_xor_sync(gmask, bb.l, off);
+          const int oe = __shfl_xor_sync(gmask, bb.e, off);
+          if (ol < bb.l || (ol == bb.l && oe < bb.e)) { bb.l = ol; bb.e = oe; }
+        }
+        bu = tmax; bl = bb.l; be = bb.e;                        // :210-217
+      }
+    }
+    // group-of-four maxima of the new unc[] (nodes 4j..4j+3 are 4*LANES adjacent lanes)
+    float gq = active ? bu : -INFINITY;
+    gq = fmaxf(gq, __shfl_xor_sync(full, gq, LANES));
+    gq = fmaxf(gq, __shfl_xor_sync(full, gq, 2 * LANES));
+    if (s == 0 && k < RP) {
+      if (active) {
         unc[buf * RP + k] = bu;
         las[buf * RP + k] = bl;
         th[buf * RP + k] = tn;
         sub[(size_t)i * R + k] = be < 0 ? 255 : (uint8_t)be;
       }
-      __syncthreads();
-      buf ^= 1;
+      if ((k & 3) == 0) qm[buf * NQ + (k >> 2)] = gq;
     }
+    __syncthreads();
+    buf ^= 1;
   }
   // ray 0 results are in buffer buf^1.  Best start against a default (0,0,null) trajectory (:99-104)
   if (threadIdx.x == 0) {
@@ -183,11 +227,13 @@ extern "C" int lc_planner_solve(LcPlanner* p, const float* umaps, int n, int32_t
   DPV_REQUIRE(n > 0, "lc_planner_solve: n=%d", n);
   const int W = p->W, R = p->R;
   const int RP = ((R + 3) / 4) * 4;
-  int lanes = 8;
-  if (const char* e = getenv("DPV_PLANNER_LANES")) lanes = atoi(e) > 0 ? atoi(e) : lanes;   // tuning aid (1,2,4,8)
-  while (lanes > 1 && R * lanes > 1024) lanes >>= 1;
-  const int threads = ((R * lanes + 31) / 32) * 32;
-  size_t smem = (size_t)6 * RP * 4 + (size_t)((W + 1) & ~1) * 2 + (size_t)W * R;
+  int lanes = 4;
+  if (const char* e = getenv("DPV_PLANNER_LANES")) lanes = atoi(e);                // tuning aid (1,2,4,8)
+  if (lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8) lanes = 4;
+  while (lanes > 1 && RP * lanes > 1024) lanes >>= 1;
+  const int threads = ((RP * lanes + 31) / 32) * 32;
+  const int NQ = RP / 4;
+  size_t smem = (size_t)6 * RP * 4 + (size_t)(2 * NQ + (NQ & 1) * 2) * 4 + (size_t)((W + 1) & ~1) * 2 + (size_t)W * R;
   DPV_REQUIRE(smem <= 227 * 1024, "lc_planner_solve: W*R = %d*%d back-pointers exceed shared memory", W, R);
   cudaStream_t st = (cudaStream_t)stream;
 #define LAUNCH(L)                                                                                               \
