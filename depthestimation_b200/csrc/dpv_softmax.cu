@@ -28,77 +28,108 @@ constexpr int kThreads = 128;
 // log_softmax over D (+ optional addend) with fused expectation / variance / entropy / x0.25 carry.
 // models/models.py:351,671,777 ; utils/img_utils.py:197-215 ; trainer/default_trainer.py:284,446-450
 // ---------------------------------------------------------------------------------------------
-template <int DPT, bool KEEP_E>
-__global__ void __launch_bounds__(kThreads)
+// The depth column of a pixel is split over T adjacent lanes (DPT bins each, lane t owns bins
+// [t*DPT, (t+1)*DPT)): 2 x 32 registers per lane instead of 2 x 64 keeps ~20 warps resident per SM, and the
+// column reductions (max, sum, mean, entropy, variance) finish with log2(T) shuffles.
+template <int T>
+__device__ __forceinline__ float lane_group_sum(float v) {
+#pragma unroll
+  for (int off = T / 2; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+  return v;
+}
+
+template <int DPT, int T>
+__global__ void __launch_bounds__(kThreads, 4)
 lsm_stats_kernel(const float* __restrict__ x, const float* __restrict__ add, int D, int H, int W, long long npix,
                  const float* __restrict__ d_candi, float* __restrict__ logp, float* __restrict__ mean_o,
                  float* __restrict__ var_o, float* __restrict__ ent_o, float* __restrict__ carry) {
-  __shared__ float dc[DPT];
-  for (int i = threadIdx.x; i < DPT; i += blockDim.x) dc[i] = i < D ? d_candi[i] : 0.f;
+  __shared__ float dc[DPT * T];
+  for (int i = threadIdx.x; i < DPT * T; i += blockDim.x) dc[i] = i < D ? d_candi[i] : 0.f;
   __syncthreads();
-  const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (pix >= npix) return;
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  // every lane of a warp stays alive for the shuffles: out-of-range pixels are clamped and not stored
+  const bool live = gid / T < npix;
+  const long long pix = live ? gid / T : npix - 1;
+  const int tl = threadIdx.x & (T - 1);
+  const int d0 = tl * DPT;
+  const float* dcl = dc + d0;
   const size_t HW = (size_t)H * W;
   const int b = (int)(pix / (long long)HW);
   const size_t hw = (size_t)(pix - (long long)b * HW);
-  const size_t base = (size_t)b * D * HW + hw;
+  const size_t base = ((size_t)b * D + d0) * HW + hw;
 
   float t[DPT];
 #pragma unroll
-  for (int d = 0; d < DPT; d++) t[d] = d < D ? ld_stream(x + base + (size_t)d * HW) : -INFINITY;
+  for (int d = 0; d < DPT; d++) t[d] = (d0 + d < D) ? ld_stream(x + base + (size_t)d * HW) : -INFINITY;
   if (add != nullptr) {
 #pragma unroll
     for (int d = 0; d < DPT; d++)
-      if (d < D) t[d] += ld_stream(add + base + (size_t)d * HW);
+      if (d0 + d < D) t[d] += ld_stream(add + base + (size_t)d * HW);
   }
-  float m = t[0];
+  float m0 = t[0], m1 = t[1];
 #pragma unroll
-  for (int d = 1; d < DPT; d++) m = fmaxf(m, t[d]);
-  float e[KEEP_E ? DPT : 1];
-  float s = 0.f;
+  for (int d = 2; d < DPT; d += 2) { m0 = fmaxf(m0, t[d]); m1 = fmaxf(m1, t[d + 1]); }
+  float m = fmaxf(m0, m1);
 #pragma unroll
-  for (int d = 0; d < DPT; d++) {
+  for (int off = T / 2; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, off));
+  float e[DPT];
+  float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+  for (int d = 0; d < DPT; d += 2) {
     t[d] -= m;
-    float ev = d < D ? expf(t[d]) : 0.f;
-    if (KEEP_E) e[d] = ev;
-    s += ev;
+    t[d + 1] -= m;
+    e[d] = expf(t[d]);                 // exp(-inf) = 0 for the padding bins
+    e[d + 1] = expf(t[d + 1]);
+    s0 += e[d];
+    s1 += e[d + 1];
   }
-  const float lse = logf(s);
-  const float inv = 1.f / s;
-  float mean = 0.f, ent = 0.f;
+  const float ssum = lane_group_sum<T>(s0 + s1);
+  const float lse = logf(ssum);
+  const float inv = 1.f / ssum;
+  float mean0 = 0.f, mean1 = 0.f, ent0 = 0.f, ent1 = 0.f;
 #pragma unroll
-  for (int d = 0; d < DPT; d++)
-    if (d < D) {
-      float lp = t[d] - lse;
-      st_stream(logp + base + (size_t)d * HW, lp);
-      float p = KEEP_E ? e[d] * inv : expf(lp);
-      mean += dc[d] * p;
-      ent -= p * lp;
-      t[d] = lp;
-      if (KEEP_E) e[d] = p;
+  for (int d = 0; d < DPT; d += 2) {
+    const float lp0 = t[d] - lse, lp1 = t[d + 1] - lse;
+    e[d] *= inv;
+    e[d + 1] *= inv;
+    if (d0 + d < D) {
+      if (live) st_stream(logp + base + (size_t)d * HW, lp0);
+      mean0 = fmaf(dcl[d], e[d], mean0);
+      ent0 = fmaf(-e[d], lp0, ent0);
     }
-  if (mean_o) mean_o[pix] = mean;
-  if (ent_o) ent_o[pix] = ent;
-  if (var_o) {
-    float var = 0.f;
-#pragma unroll
-    for (int d = 0; d < DPT; d++)
-      if (d < D) {
-        float p = KEEP_E ? e[d] : expf(t[d]);
-        float dd = dc[d] - mean;
-        var += dd * dd * p;
-      }
-    var_o[pix] = var;
+    if (d0 + d + 1 < D) {
+      if (live) st_stream(logp + base + (size_t)(d + 1) * HW, lp1);
+      mean1 = fmaf(dcl[d + 1], e[d + 1], mean1);
+      ent1 = fmaf(-e[d + 1], lp1, ent1);
+    }
+    t[d] = lp0;
+    t[d + 1] = lp1;
   }
-  if (carry) {
+  const float mean = lane_group_sum<T>(mean0 + mean1);
+  const float ent = lane_group_sum<T>(ent0 + ent1);
+  const bool writer = live && tl == 0;
+  if (mean_o && writer) mean_o[pix] = mean;
+  if (ent_o && writer) ent_o[pix] = ent;
+  if (var_o) {
+    float v0 = 0.f, v1 = 0.f;
+#pragma unroll
+    for (int d = 0; d < DPT; d += 2) {
+      const float a0 = dcl[d] - mean, a1 = dcl[d + 1] - mean;
+      v0 = fmaf(a0 * a0, e[d], v0);
+      v1 = fmaf(a1 * a1, e[d + 1], v1);
+    }
+    const float var = lane_group_sum<T>(v0 + v1);
+    if (writer) var_o[pix] = var;
+  }
+  if (carry && live) {
     // F.interpolate(scale_factor=0.25, 'nearest'): dst (j,i) <- src (4j, 4i)
     const int y = (int)(hw / W), xx = (int)(hw % W);
     const int h4 = H / 4, w4 = W / 4;
     if ((y & 3) == 0 && (xx & 3) == 0 && (y >> 2) < h4 && (xx >> 2) < w4) {
-      float* c = carry + (size_t)b * D * h4 * w4 + (size_t)(y >> 2) * w4 + (xx >> 2);
+      float* c = carry + ((size_t)b * D + d0) * h4 * w4 + (size_t)(y >> 2) * w4 + (xx >> 2);
 #pragma unroll
       for (int d = 0; d < DPT; d++)
-        if (d < D) c[(size_t)d * h4 * w4] = t[d];
+        if (d0 + d < D) c[(size_t)d * h4 * w4] = t[d];
     }
   }
 }
@@ -294,12 +325,13 @@ int dpv_logsoftmax_stats(const float* x, const float* add, int B, int D, int H, 
   cudaStream_t st = (cudaStream_t)stream;
   const long long npix = (long long)B * H * W;
   const unsigned g = blocks_for(npix, kThreads);
-#define LAUNCH(DPT, KE) \
-  lsm_stats_kernel<DPT, KE><<<g, kThreads, 0, st>>>(x, add, D, H, W, npix, d_candi, logp, mean, var, entropy, carry)
-  if (D <= 16) LAUNCH(16, true);
-  else if (D <= 32) LAUNCH(32, true);
-  else if (D <= 64) LAUNCH(64, true);
-  else if (D <= 128) LAUNCH(128, false);
+#define LAUNCH(DPT, T)                                                                                       \
+  lsm_stats_kernel<DPT, T><<<blocks_for(npix * T, kThreads), kThreads, 0, st>>>(x, add, D, H, W, npix, d_candi, \
+                                                                                logp, mean, var, entropy, carry)
+  if (D <= 16) LAUNCH(16, 1);
+  else if (D <= 32) LAUNCH(32, 1);
+  else if (D <= 64) LAUNCH(32, 2);
+  else if (D <= 128) LAUNCH(32, 4);
   else
     lsm_stats_generic_kernel<<<g, kThreads, 0, st>>>(x, add, D, H, W, npix, d_candi, logp, mean, var, entropy, carry);
 #undef LAUNCH
