@@ -37,6 +37,8 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--streams", type=int, default=3,
+                    help="independent batches in flight (steps are issued round-robin on this many CUDA streams)")
     return ap.parse_args()
 
 
@@ -139,7 +141,10 @@ def run_b200(args):
     torch.cuda.set_device(dev)
     host, meta = synthetic_batch(args.workload, seed=rank)
     B = meta["B"]
-    pipe = DpvLcPipeline(meta, dev)
+    S = max(1, min(args.streams, args.steps))
+    pipes = [DpvLcPipeline(meta, dev) for _ in range(S)]
+    streams = [torch.cuda.Stream(dev) for _ in range(S)]
+    pipe = pipes[0]
     x = {k: v.to(dev) for k, v in host.items()}
     peaks = {}
     try:
@@ -147,6 +152,7 @@ def run_b200(args):
     except OSError:
         pass
     peak_gbs, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    main = torch.cuda.current_stream(dev)
 
     def sync():
         torch.cuda.synchronize(dev)
@@ -154,26 +160,40 @@ def run_b200(args):
             dist.barrier()
             torch.cuda.synchronize(dev)
 
+    def run_steps(n):
+        """n steps, step i on stream i % S: successive (independent) batches overlap — the latency-bound planner of
+        one batch runs beside the streaming kernels of the next."""
+        start = torch.cuda.Event()
+        start.record(main)
+        for st in streams:
+            st.wait_event(start)
+        for i in range(n):
+            with torch.cuda.stream(streams[i % S]):
+                out = pipes[i % S].step(x)
+                sharding.gather_frame_outputs(out, world)
+        for st in streams:
+            done = torch.cuda.Event()
+            done.record(st)
+            main.wait_event(done)
+
     # ---- value: inputs resident in HBM --------------------------------------------------------
-    for _ in range(args.warmup):
-        out = pipe.step(x)
-        sharding.gather_frame_outputs(out, world)
+    run_steps(max(args.warmup, S))
     sync()
-    pipe.fuse_events = []
+    for p_ in pipes:
+        p_.fuse_events = []
     n0 = _lib.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clk:
         sync()
-        e0.record()
-        for _ in range(args.steps):
-            out = pipe.step(x)
-            sharding.gather_frame_outputs(out, world)
-        e1.record()
+        e0.record(main)
+        run_steps(args.steps)
+        e1.record(main)
         sync()
     ms = e0.elapsed_time(e1)
     launches = _lib.launch_count() - n0
-    fuse_ms = [a.elapsed_time(b) for a, b in pipe.fuse_events]
-    pipe.fuse_events = None
+    fuse_ms = [a.elapsed_time(b) for p_ in pipes for a, b in p_.fuse_events]
+    for p_ in pipes:
+        p_.fuse_events = None
     ms_t = torch.tensor([ms], device=dev)
     if world > 1:
         dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
@@ -184,7 +204,7 @@ def run_b200(args):
     # ---- e2e: host buffers in, host results out, copies inside the timed region ------------------
     e2e = None
     if not args.no_e2e:
-        e2e = run_e2e(args, pipe, host, x, dev, world, B, STREAMED_KEYS, sync, sharding)
+        e2e = run_e2e(args, pipes, streams, host, x, dev, world, B, STREAMED_KEYS, sync, sharding)
 
     # ---- roofline of the dominant kernel (sense+fuse: one read + one write of the volume) --------
     alg = pipe.algorithmic_bytes()
@@ -213,7 +233,7 @@ def run_b200(args):
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": args.workload, "frames_per_gpu": B, "H": meta["H"], "W": meta["W"],
                            "D": meta["D"], "C": meta["C"], "T": meta["T"], "lc_iterations": meta["iterations"],
-                           "curtains_per_iteration": 1 + 2 * len(meta["step"]), "parallelism": "batch-shard x%d" % world,
+                           "curtains_per_iteration": 1 + 2 * len(meta["step"]), "parallelism": "batch-shard x%d" % world, "streams_in_flight": S,
                            "l2_policy": "inputs larger than L2 (0.9 GB streamed per frame)"},
                 "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
                 "ms_per_frame": round(ms_per_step / B, 4)}
@@ -222,47 +242,39 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
-def run_e2e(args, pipe, host, x, dev, world, B, keys, sync, sharding):
-    """Same step through the public API with HOST buffers: pinned H2D of the step's inputs (double-buffered on a
-    copy stream so the copy of step i+1 overlaps step i) and a D2H read of depth / variance / LC depth."""
+def run_e2e(args, pipes, streams, host, x, dev, world, B, keys, sync, sharding):
+    """Same step through the public API with HOST buffers: every step copies its inputs from pinned host memory
+    (H2D) and reads depth / variance / LC depth back (D2H), on the step's own stream, so the copies of one batch
+    overlap the kernels of the others."""
+    S = len(pipes)
+    m = pipes[0].m
     pin = {k: host[k].pin_memory() for k in keys}
-    bufs = [{k: torch.empty_like(x[k]) for k in keys} for _ in range(2)]
-    res_host = {k: torch.empty(B, pipe.m["H"], pipe.m["W"]).pin_memory() for k in ("depth", "var", "depth_lc")}
-    copy = torch.cuda.Stream(dev)
+    bufs = [{k: torch.empty_like(x[k]) for k in keys} for _ in range(S)]
+    res_host = [{k: torch.empty(B, m["H"], m["W"]).pin_memory() for k in ("depth", "var", "depth_lc")} for _ in range(S)]
     main = torch.cuda.current_stream(dev)
-    ready = [torch.cuda.Event() for _ in range(2)]
-    free = [torch.cuda.Event() for _ in range(2)]
     h2d = sum(pin[k].numel() * 4 for k in keys)
-    d2h = sum(v.numel() * 4 for v in res_host.values())
-
-    def issue_copy(i):
-        s = i % 2
-        with torch.cuda.stream(copy):
-            copy.wait_event(free[s])
-            for k in keys:
-                bufs[s][k].copy_(pin[k], non_blocking=True)
-            ready[s].record(copy)
+    d2h = sum(v.numel() * 4 for v in res_host[0].values())
 
     def loop(n):
-        for s in range(2):
-            free[s].record(main)
-        issue_copy(0)
+        start = torch.cuda.Event()
+        start.record(main)
+        for st in streams:
+            st.wait_event(start)
         for i in range(n):
-            s = i % 2
-            if i + 1 < n:
-                issue_copy(i + 1)
-            main.wait_event(ready[s])
-            xin = dict(x)
-            xin.update(bufs[s])
-            out = pipe.step(xin)
-            sharding.gather_frame_outputs(out, world)
-            for k in res_host:
-                if k in out:
-                    res_host[k].copy_(out[k], non_blocking=True)
-            free[s].record(main)
+            sl = i % S
+            with torch.cuda.stream(streams[sl]):
+                for k in keys:
+                    bufs[sl][k].copy_(pin[k], non_blocking=True)
+                xin = dict(x)
+                xin.update(bufs[sl])
+                out = pipes[sl].step(xin)
+                sharding.gather_frame_outputs(out, world)
+                for k in res_host[sl]:
+                    if k in out:
+                        res_host[sl][k].copy_(out[k], non_blocking=True)
         torch.cuda.synchronize(dev)
 
-    loop(max(args.warmup, 1))
+    loop(max(args.warmup, S))
     sync()
     t0 = time.perf_counter()
     loop(args.steps)

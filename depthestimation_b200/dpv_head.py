@@ -48,10 +48,11 @@ def uniform_log_prior(shape, D, device):
 class LcLoopState:
     """Pre-allocated buffers of one LC loop (so the loop can be captured in a CUDA graph)."""
 
-    def __init__(self, B, D, H, W, R, nc, device):
+    def __init__(self, B, D, H, W, R, nc, device, alloc_volume=True):
         f = dict(device=device, dtype=torch.float32)
-        self.logp = torch.empty(B, D, H, W, **f)
-        self.mean = torch.empty(B, H, W, **f)
+        # the pipeline fuses in place on the volume the log-softmax kernel just wrote, so it brings its own
+        self.logp = torch.empty(B, D, H, W, **f) if alloc_volume else None
+        self.mean = torch.empty(B, H, W, **f) if alloc_volume else None
         self.uf = torch.empty(B, D, W, **f)
         self.umaps = torch.empty(B, nc, R, W, **f)
         self.argmax = torch.empty(B, W, device=device, dtype=torch.int32)

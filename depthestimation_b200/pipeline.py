@@ -128,7 +128,7 @@ class DpvLcPipeline:
             self.lc = LightCurtain()
             self.lc.init(P)
             nc = 1 + 2 * len(meta["step"])
-            self.state = dpv_head.LcLoopState(meta["B"], meta["D"], H, W, meta["R"], nc, self.device)
+            self.state = dpv_head.LcLoopState(meta["B"], meta["D"], H, W, meta["R"], nc, self.device, alloc_volume=False)
         self.fuse_events = None          # optional list collecting (start, end) CUDA events of sense+fuse launches
 
     def step(self, x):
