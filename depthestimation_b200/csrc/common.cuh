@@ -54,6 +54,13 @@ __device__ __forceinline__ float exp2f_approx(float x) {
   return y;
 }
 
+// log2(x) on the MUFU pipe (lg2.approx.ftz: callers pass x >= eps_floor(), never a denormal)
+__device__ __forceinline__ float log2f_approx(float x) {
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // grid_sample(align_corners=False) un-normalisation, ATen grid_sampler_unnormalize: ((g+1)*N-1)/2
 __device__ __forceinline__ float gs_unnormalize(float g, int n) {
   return __fdiv_rn(__fsub_rn(__fmul_rn(__fadd_rn(g, 1.f), (float)n), 1.f), 2.f);

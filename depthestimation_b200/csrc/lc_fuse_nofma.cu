@@ -3,8 +3,8 @@
 //   with lc/light_curtain.py:847-888 + :228-252 (likelihood) and dprocessor.cpp:806-993 (image formation)
 //   evaluated per pixel in registers.  Compiled with -fmad=false for the geometry (see lc_sense.cuh).
 //
-// A thread owns one pixel: its DPV column p[D] and the current curtain's likelihood column g[D] live in
-// registers (straight-line code over the bins; at the simulated baseline of 0.2 m the curtain thickness
+// T adjacent lanes own one pixel: its DPV column p[D] and the current curtain's likelihood column g[D] live in
+// registers as f32x2 pairs (straight-line code over the bins; at the simulated baseline of 0.2 m the curtain thickness
 // grows to metres, so the Gaussian really is dense over the bins and is evaluated for every bin with one
 // MUFU ex2 each).  Multiply, box-spread and renormalise are all homogeneous in the DPV, so the
 // per-curtain and per-spread renormalisations of the reference collapse into one scale at the end
@@ -18,11 +18,7 @@ namespace dpv {
 constexpr int kFuseThreads = 128;
 constexpr int kMaxCurtains = 8;
 
-// g[d] = exp(-(dc-z)^2 / den) as ex2((dc-z)^2 * kk), kk = -log2(e)/den  (img_utils.py:183-186)
-__device__ __forceinline__ float gauss_bin(float dcv, float z, float kk) {
-  const float t = dcv - z;
-  return exp2f_approx((t * t) * kk);
-}
+__device__ __forceinline__ float2 splat2(float a) { return make_float2(a, a); }
 
 // sum over the T lanes that share one pixel (T is a power of two; lanes are adjacent)
 template <int T>
@@ -32,172 +28,233 @@ __device__ __forceinline__ float group_sum(float v, unsigned gmask) {
   return v;
 }
 
+// A lane's DPT bins as DPT/2 register pairs (packed f32x2 arithmetic: one FMUL2/FADD2/FFMA2 per two bins).
+template <int NP>
+struct Col {
+  float2 v[NP];
+  __device__ __forceinline__ float get(int d) const { return (d & 1) ? v[d >> 1].y : v[d >> 1].x; }
+  __device__ __forceinline__ void set(int d, float x) {
+    if (d & 1) v[d >> 1].y = x;
+    else v[d >> 1].x = x;
+  }
+};
+
 // One box-sum pass along depth over a column that is split over T lanes (DPT bins each, lane t owns bins
 // [t*DPT, (t+1)*DPT)).  q[d] = sum_{|j|<=HALF} p[d+j], zero outside [0,D).  img_utils.py:408-436.
-template <int DPT, int T, int HALF>
-__device__ __forceinline__ void spread_pass(float (&p)[DPT], int d0, int D, int t, int lane, unsigned gmask) {
-  float lo_h[HALF > 0 ? HALF : 1], hi_h[HALF > 0 ? HALF : 1];     // neighbours' edge bins (before modification)
+// Bins at and beyond D hold 0 on entry and on exit, so the neighbour lane's halo needs no bound check.
+template <int DPT, int T, int HALF, bool FULL>
+__device__ __forceinline__ void spread_pass(Col<DPT / 2>& p, int d0, int D, int t, int lane, unsigned gmask) {
+  constexpr int NH = HALF > 0 ? HALF : 1;
+  float lo_h[NH], hi_h[NH];                                    // lo_h[j] = p[d0-1-j], hi_h[j] = p[d0+DPT+j]
 #pragma unroll
   for (int j = 0; j < HALF; j++) {
     float from_prev = 0.f, from_next = 0.f;
     if (T > 1) {
-      from_prev = __shfl_sync(gmask, p[DPT - 1 - j], (lane - 1) & 31);     // p[d0-1-j]
-      from_next = __shfl_sync(gmask, p[j], (lane + 1) & 31);               // p[d0+DPT+j]
+      from_prev = __shfl_sync(gmask, p.get(DPT - 1 - j), (lane - 1) & 31);
+      from_next = __shfl_sync(gmask, p.get(j), (lane + 1) & 31);
     }
     lo_h[j] = (T > 1 && t > 0) ? from_prev : 0.f;
-    hi_h[j] = (T > 1 && t < T - 1 && d0 + DPT + j < D) ? from_next : 0.f;
+    hi_h[j] = (T > 1 && t < T - 1) ? from_next : 0.f;
   }
-  float prev[HALF > 0 ? HALF : 1];
+  auto at = [&](int i) -> float {                              // i is a compile-time constant after unrolling
+    return i < 0 ? lo_h[(-1 - i) < NH ? (-1 - i) : 0] : (i >= DPT ? hi_h[(i - DPT) < NH ? (i - DPT) : 0] : p.get(i));
+  };
+  Col<DPT / 2> q;
+  if constexpr (HALF == 2) {
+    // pair sums S_k = p[2k] + p[2k+1]:  q[2k] = S_{k-1} + S_k + p[2k+2],  q[2k+1] = p[2k-1] + S_k + S_{k+1}
+    float S[DPT / 2 + 2];
 #pragma unroll
-  for (int j = 0; j < HALF; j++) prev[j] = lo_h[j];                        // prev[j] = p[d-1-j]
+    for (int k = -1; k <= DPT / 2; k++) S[k + 1] = at(2 * k) + at(2 * k + 1);
 #pragma unroll
-  for (int d = 0; d < DPT; d++) {
-    const float c = p[d];
-    float q = 0.f;
-#pragma unroll
-    for (int j = HALF - 1; j >= 0; j--) q += prev[j];
-    q += c;
-#pragma unroll
-    for (int j = 1; j <= HALF; j++) {
-      const float nb = (d + j < DPT) ? ((d0 + d + j < D) ? p[(d + j < DPT) ? d + j : 0] : 0.f) : hi_h[(d + j - DPT) < HALF ? (d + j - DPT) : 0];
-      q += nb;
+    for (int k = 0; k < DPT / 2; k++) {
+      q.v[k].x = (S[k] + S[k + 1]) + at(2 * k + 2);
+      q.v[k].y = (S[k + 1] + S[k + 2]) + at(2 * k - 1);
     }
+  } else {
 #pragma unroll
-    for (int j = HALF - 1; j > 0; j--) prev[j] = prev[j - 1];
-    if (HALF > 0) prev[0] = c;
-    p[d] = (d0 + d < D) ? q : 0.f;
+    for (int d = 0; d < DPT; d++) {
+      float acc = at(d);
+#pragma unroll
+      for (int j = 1; j <= HALF; j++) acc += at(d - j) + at(d + j);
+      q.set(d, acc);
+    }
   }
+#pragma unroll
+  for (int d = 0; d < DPT; d++) p.set(d, (FULL || d0 + d < D) ? q.get(d) : 0.f);
 }
 
-template <int DPT, int T, int HALF>
+template <int DPT, int T, int HALF, bool FULL>
 __global__ void __launch_bounds__(kFuseThreads, 4)
 sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float* __restrict__ depth,
                   const float* __restrict__ planes, const float* __restrict__ noise, int nc, long long npix,
                   const float* __restrict__ d_candi, int D, int spread_iter, int flags,
                   float* __restrict__ vol_out, float* __restrict__ mean_out) {
-  __shared__ float dc[DPT * T];
-  for (int i = threadIdx.x; i < DPT * T; i += blockDim.x) dc[i] = i < D ? d_candi[i] : 0.f;
+  constexpr int NP = DPT / 2;
+  constexpr int STR = DPT + 4;      // lane slices of d_candi, padded: 16-byte aligned and 4 banks apart
+  __shared__ __align__(16) float dc[STR * T];
+  for (int i = threadIdx.x; i < STR * T; i += blockDim.x) {
+    const int tt = i / STR, j = i - tt * STR, d = tt * DPT + j;
+    dc[i] = (j < DPT && d < D) ? d_candi[d] : 0.f;
+  }
   __syncthreads();
   const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long pix = gid / T;
   if (pix >= npix) return;                                   // whole lane groups leave together
   const int lane = threadIdx.x & 31;
   const int t = lane & (T - 1);
-  const unsigned gmask = (T == 32 ? 0xffffffffu : ((1u << T) - 1u)) << (lane & ~(T - 1));
+  const int gbase = lane & ~(T - 1);
+  const unsigned gmask = (T == 32 ? 0xffffffffu : ((1u << T) - 1u)) << gbase;
   const int d0 = t * DPT;
-  const float* dcl = dc + d0;
+  const float4* dc4 = reinterpret_cast<const float4*>(dc + t * STR);
   const size_t HW = (size_t)dv.H * dv.W;
   const int b = (int)(pix / (long long)HW);
   const size_t hw = (size_t)(pix - (long long)b * HW);
   const int v = (int)(hw / dv.W), u = (int)(hw % dv.W);
   const size_t base = ((size_t)b * D + d0) * HW + hw;
-  const bool in_prob = flags & 1, out_prob = flags & 2;
+  auto valid = [&](int d) -> bool { return FULL || d0 + d < D; };
 
   // ---- issue the volume loads first; the curtain geometry below overlaps their latency
-  float p[DPT];
+  Col<NP> p;
+  {
+    const float* src = vol_in + base;
 #pragma unroll
-  for (int d = 0; d < DPT; d++) p[d] = (d0 + d < D) ? ld_stream(vol_in + base + (size_t)d * HW) : 0.f;
+    for (int d = 0; d < DPT; d++) p.set(d, valid(d) ? ld_stream(src + (size_t)d * HW) : 0.f);
+  }
   const float gt = depth[pix];
-  bool first = true;
-  Lik mine;
-  mine.z = 0.f; mine.den = 0.f; mine.A = 0.f; mine.Bu = 0.f;
 
-  for (int c = 0; c < nc; c++) {
-    // ---- sensing: in rounds of T curtains, lane t of the group senses curtain c + t (all lanes busy, same code)
-    if ((c & (T - 1)) == 0) {
-      const int myc = c + t;
-      if (myc < nc) {
-        const int cu = b * nc + myc;
-        float Pl[12];
+  int c0 = 0;
+#pragma unroll 1
+  do {
+    // ---- sensing: in rounds of T curtains, lane t of the group senses curtain c0 + t (all lanes busy, same code)
+    Lik mine;
+    mine.z = 0.f; mine.den = 0.f; mine.A = 0.f; mine.Bu = 0.f;
+    if (c0 + t < nc) {
+      const int cu = b * nc + c0 + t;
+      const float4* P4 = reinterpret_cast<const float4*>(planes + ((size_t)cu * dv.W + u) * 12);
+      float Pl[12];
 #pragma unroll
-        for (int k = 0; k < 12; k++) Pl[k] = __ldg(planes + ((size_t)cu * dv.W + u) * 12 + k);
-        const Ret r = sense_pixel(dv, Pl, u, v, gt, noise ? noise + (size_t)cu * HW + hw : nullptr);
-        mine = lik_params(r, gt, D);
+      for (int k = 0; k < 3; k++) {
+        const float4 q = __ldg(P4 + k);
+        Pl[4 * k] = q.x; Pl[4 * k + 1] = q.y; Pl[4 * k + 2] = q.z; Pl[4 * k + 3] = q.w;
+      }
+      const Ret r = sense_pixel(dv, Pl, u, v, gt, noise ? noise + (size_t)cu * HW + hw : nullptr);
+      mine = lik_params(r, gt, D);
+    }
+    if (c0 == 0) {                                           // models.py:1097 (after the loads have landed)
+      if (flags & 1) {
+#pragma unroll
+        for (int d = 0; d < DPT; d++) p.set(d, valid(d) ? fminf(fmaxf(p.get(d), eps_floor()), 1.f) : 0.f);
+      } else {
+#pragma unroll
+        for (int d = 0; d < DPT; d++) p.set(d, valid(d) ? fminf(fmaxf(exp2f_approx(p.get(d) * 1.4426950408889634f), eps_floor()), 1.f) : 0.f);
       }
     }
-    Lik L;
-    const int owner = (lane & ~(T - 1)) + (c & (T - 1));
-    L.z = __shfl_sync(gmask, mine.z, owner);
-    L.den = __shfl_sync(gmask, mine.den, owner);
-    L.A = __shfl_sync(gmask, mine.A, owner);
-    L.Bu = __shfl_sync(gmask, mine.Bu, owner);
-    if (first) {                                             // models.py:1097 (after the loads have landed)
+    const int jn = min(T, nc - c0);
+#pragma unroll 1
+    for (int j = 0; j < jn; j++) {
+      Lik L = mine;
+      if (T > 1) {
+        L.z = __shfl_sync(gmask, mine.z, gbase + j);
+        L.den = __shfl_sync(gmask, mine.den, gbase + j);
+        L.A = __shfl_sync(gmask, mine.A, gbase + j);
+        L.Bu = __shfl_sync(gmask, mine.Bu, gbase + j);
+      }
+      // ---- likelihood of this curtain over the depth bins (mixed_model, light_curtain.py:247-252):
+      // g[d] = exp(-(dc-z)^2 / den) as ex2((dc-z)^2 * kk), kk = -log2(e)/den  (img_utils.py:183-186);
+      // den = 0 -> kk = -inf: g = 0 (NaN at dc == z), as in the reference
+      const float2 kk2 = splat2(-1.4426950408889634f / L.den), nz2 = splat2(-L.z);
+      Col<NP> g;
+      float2 a0 = splat2(0.f), a1 = splat2(0.f);
 #pragma unroll
-      for (int d = 0; d < DPT; d++) p[d] = fminf(fmaxf(in_prob ? p[d] : __expf(p[d]), eps_floor()), 1.f);
-      first = false;
+      for (int k = 0; k < NP; k += 2) {
+        const float4 q = dc4[k >> 1];
+        float2 e0 = __fadd2_rn(make_float2(q.x, q.y), nz2), e1 = __fadd2_rn(make_float2(q.z, q.w), nz2);
+        e0 = __fmul2_rn(__fmul2_rn(e0, e0), kk2);
+        e1 = __fmul2_rn(__fmul2_rn(e1, e1), kk2);
+        g.v[k] = make_float2(valid(2 * k) ? exp2f_approx(e0.x) : 0.f, valid(2 * k + 1) ? exp2f_approx(e0.y) : 0.f);
+        g.v[k + 1] =
+            make_float2(valid(2 * k + 2) ? exp2f_approx(e1.x) : 0.f, valid(2 * k + 3) ? exp2f_approx(e1.y) : 0.f);
+        a0 = __fadd2_rn(a0, g.v[k]);
+        a1 = __fadd2_rn(a1, g.v[k + 1]);
+      }
+      const float sg = group_sum<T>((a0.x + a0.y) + (a1.x + a1.y), gmask);
+      // sg == 0 or NaN: g/sg is NaN -> -1 in every bin -> constant mixture -> uniform likelihood -> no-op
+      bool ok = sg > 0.f;
+      const float2 As2 = splat2(L.A / sg), Bu2 = splat2(L.Bu);
+      a0 = splat2(0.f); a1 = splat2(0.f);
+#pragma unroll
+      for (int k = 0; k < NP; k += 2) {                      // clamp(soft * A + uni * B, 0, inf)
+        float2 m0 = __ffma2_rn(g.v[k], As2, Bu2), m1 = __ffma2_rn(g.v[k + 1], As2, Bu2);
+        m0 = make_float2(valid(2 * k) ? fmaxf(m0.x, 0.f) : 0.f, valid(2 * k + 1) ? fmaxf(m0.y, 0.f) : 0.f);
+        m1 = make_float2(valid(2 * k + 2) ? fmaxf(m1.x, 0.f) : 0.f, valid(2 * k + 3) ? fmaxf(m1.y, 0.f) : 0.f);
+        g.v[k] = m0;
+        g.v[k + 1] = m1;
+        a0 = __fadd2_rn(a0, m0);
+        a1 = __fadd2_rn(a1, m1);
+      }
+      const float sm = group_sum<T>((a0.x + a0.y) + (a1.x + a1.y), gmask);
+      ok = ok && (sm > 0.f);                                 // 0/0 in every bin -> NaN -> 0 -> eps: uniform again
+      if (ok) {
+        // models.py:1109-1112: p *= clamp(m / sm, eps, 1), renormalise.  Everything here is homogeneous in p,
+        // so the common factor 1/sm is left to the final renormalisation: p *= max(m, eps * sm); m <= sm
+        // already bounds the ratio by 1.
+        const float esm = eps_floor() * sm;
+        a0 = splat2(0.f); a1 = splat2(0.f);
+#pragma unroll
+        for (int k = 0; k < NP; k += 2) {
+          p.v[k] = __fmul2_rn(p.v[k], make_float2(fmaxf(g.v[k].x, esm), fmaxf(g.v[k].y, esm)));
+          p.v[k + 1] = __fmul2_rn(p.v[k + 1], make_float2(fmaxf(g.v[k + 1].x, esm), fmaxf(g.v[k + 1].y, esm)));
+          a0 = __fadd2_rn(a0, p.v[k]);
+          a1 = __fadd2_rn(a1, p.v[k + 1]);
+        }
+        const float s = group_sum<T>((a0.x + a0.y) + (a1.x + a1.y), gmask);
+        if (s < 1e-12f || s > 1e12f) {                       // rescale only to stay inside fp32 range
+          const float2 inv2 = splat2(1.f / s);
+#pragma unroll
+          for (int k = 0; k < NP; k++) p.v[k] = __fmul2_rn(p.v[k], inv2);
+        }
+      }
     }
-    // ---- likelihood of this curtain over the depth bins (mixed_model, light_curtain.py:247-252)
-    const float kk = -1.4426950408889634f / L.den;           // den = 0 -> -inf: g = 0 (NaN at dc == z) like the reference
-    float g[DPT];
-    float s0 = 0.f, s1 = 0.f;
-#pragma unroll
-    for (int d = 0; d < DPT; d += 2) {
-      g[d] = (d0 + d < D) ? gauss_bin(dcl[d], L.z, kk) : 0.f;
-      g[d + 1] = (d0 + d + 1 < D) ? gauss_bin(dcl[d + 1], L.z, kk) : 0.f;
-      s0 += g[d];
-      s1 += g[d + 1];
-    }
-    const float sg = group_sum<T>(s0 + s1, gmask);
-    // sg == 0 or NaN: g/sg is NaN -> -1 in every bin -> constant mixture -> uniform likelihood -> no-op
-    if (!(sg > 0.f)) continue;
-    const float As = L.A / sg;
-    s0 = 0.f; s1 = 0.f;
-#pragma unroll
-    for (int d = 0; d < DPT; d += 2) {
-      g[d] = (d0 + d < D) ? fmaxf(fmaf(g[d], As, L.Bu), 0.f) : 0.f;     // clamp(soft * A + uni * B, 0, inf)
-      g[d + 1] = (d0 + d + 1 < D) ? fmaxf(fmaf(g[d + 1], As, L.Bu), 0.f) : 0.f;
-      s0 += g[d];
-      s1 += g[d + 1];
-    }
-    const float sm = group_sum<T>(s0 + s1, gmask);
-    if (!(sm > 0.f)) continue;                               // 0/0 in every bin -> NaN -> 0 -> eps: uniform again
-    const float inv_sm = 1.f / sm;
-    s0 = 0.f; s1 = 0.f;
-#pragma unroll
-    for (int d = 0; d < DPT; d += 2) {
-      p[d] *= fminf(fmaxf(g[d] * inv_sm, eps_floor()), 1.f);             // models.py:1109-1111
-      p[d + 1] *= fminf(fmaxf(g[d + 1] * inv_sm, eps_floor()), 1.f);
-      s0 += p[d];
-      s1 += p[d + 1];
-    }
-    const float s = group_sum<T>(s0 + s1, gmask);
-    if (s < 1e-12f) {                                        // models.py:1112 — only needed to stay in range
-      const float inv = 1.f / s;
-#pragma unroll
-      for (int d = 0; d < DPT; d++) p[d] *= inv;
-    }
-  }
-  if (first) {
-#pragma unroll
-    for (int d = 0; d < DPT; d++) p[d] = fminf(fmaxf(in_prob ? p[d] : __expf(p[d]), eps_floor()), 1.f);
-  }
-#pragma unroll
-  for (int d = 0; d < DPT; d++)
-    if (d0 + d >= D) p[d] = 0.f;
+    c0 += T;
+  } while (c0 < nc);
 
   // ---- box spread along depth x spread_iter (img_utils.py:408-436), one renormalisation at the end
-  for (int i = 0; i < spread_iter; i++) spread_pass<DPT, T, HALF>(p, d0, D, t, lane, gmask);
-  float s0 = 0.f, s1 = 0.f;
+#pragma unroll 1
+  for (int i = 0; i < spread_iter; i++) spread_pass<DPT, T, HALF, FULL>(p, d0, D, t, lane, gmask);
+  float2 a0 = splat2(0.f), a1 = splat2(0.f);
 #pragma unroll
-  for (int d = 0; d < DPT; d += 2) { s0 += p[d]; s1 += p[d + 1]; }
-  const float inv = 1.f / group_sum<T>(s0 + s1, gmask);
+  for (int k = 0; k < NP; k += 2) {
+    a0 = __fadd2_rn(a0, p.v[k]);
+    a1 = __fadd2_rn(a1, p.v[k + 1]);
+  }
+  const float2 inv2 = splat2(1.f / group_sum<T>((a0.x + a0.y) + (a1.x + a1.y), gmask));
 
   // ---- clamp, (log), expectation, store (models.py:1119-1122) -------------------------------
-  float m0 = 0.f, m1 = 0.f;
+  float2 m0 = splat2(0.f), m1 = splat2(0.f);
 #pragma unroll
-  for (int d = 0; d < DPT; d += 2) {
-    const float c0 = fminf(fmaxf(p[d] * inv, eps_floor()), 1.f);
-    const float c1 = fminf(fmaxf(p[d + 1] * inv, eps_floor()), 1.f);
-    if (d0 + d < D) {
-      m0 = fmaf(dcl[d], c0, m0);
-      st_stream(vol_out + base + (size_t)d * HW, out_prob ? c0 : __logf(c0));
-    }
-    if (d0 + d + 1 < D) {
-      m1 = fmaf(dcl[d + 1], c1, m1);
-      st_stream(vol_out + base + (size_t)(d + 1) * HW, out_prob ? c1 : __logf(c1));
+  for (int k = 0; k < NP; k += 2) {
+    const float4 q = dc4[k >> 1];
+    float2 c0v = __fmul2_rn(p.v[k], inv2), c1v = __fmul2_rn(p.v[k + 1], inv2);
+    c0v = make_float2(fminf(fmaxf(c0v.x, eps_floor()), 1.f), fminf(fmaxf(c0v.y, eps_floor()), 1.f));
+    c1v = make_float2(fminf(fmaxf(c1v.x, eps_floor()), 1.f), fminf(fmaxf(c1v.y, eps_floor()), 1.f));
+    p.v[k] = c0v;
+    p.v[k + 1] = c1v;
+    m0 = __ffma2_rn(make_float2(q.x, q.y), c0v, m0);         // d_candi is 0 in the padding bins
+    m1 = __ffma2_rn(make_float2(q.z, q.w), c1v, m1);
+  }
+  {
+    float* dst = vol_out + base;
+    if (flags & 2) {
+#pragma unroll
+      for (int d = 0; d < DPT; d++)
+        if (valid(d)) st_stream(dst + (size_t)d * HW, p.get(d));
+    } else {
+#pragma unroll
+      for (int d = 0; d < DPT; d++)
+        if (valid(d)) st_stream(dst + (size_t)d * HW, log2f_approx(p.get(d)) * 0.6931471805599453f);
     }
   }
-  const float mean = group_sum<T>(m0 + m1, gmask);
+  const float mean = group_sum<T>((m0.x + m0.y) + (m1.x + m1.y), gmask);
   if (mean_out && t == 0) mean_out[pix] = mean;
 }
 
@@ -214,13 +271,20 @@ extern "C" int lc_sense_fuse(const LcDevice* dev, const float* logp_in, const fl
   DPV_REQUIRE(spread_iter == 0 || spread_n == 1 || spread_n == 3 || spread_n == 5 || spread_n == 7,
               "lc_sense_fuse: spread_n=%d not in {1,3,5,7}", spread_n);
   DPV_REQUIRE(D <= 128, "lc_sense_fuse: D=%d > 128 unsupported", D);
+  DPV_REQUIRE(((uintptr_t)planes & 15) == 0, "lc_sense_fuse: planes must be 16-byte aligned");
   DPV_REQUIRE((flags & ~3) == 0, "lc_sense_fuse: unknown flags %d", flags);
   const long long npix = (long long)B * dev->H * dev->W;
   cudaStream_t st = (cudaStream_t)stream;
   const int half = spread_iter == 0 ? 0 : spread_n / 2;
-#define LAUNCH3(DPT, T, HALF)                                                                                      \
-  sense_fuse_kernel<DPT, T, HALF><<<(unsigned)((npix * T + kFuseThreads - 1) / kFuseThreads), kFuseThreads, 0, st>>>( \
-      dev->view, logp_in, depth, planes, noise, nc, npix, d_candi, D, spread_iter, flags, logp_out, mean_out)
+#define LAUNCH4(DPT, T, HALF, FULL)                                                                                \
+  sense_fuse_kernel<DPT, T, HALF, FULL>                                                                            \
+      <<<(unsigned)((npix * T + kFuseThreads - 1) / kFuseThreads), kFuseThreads, 0, st>>>(                         \
+          dev->view, logp_in, depth, planes, noise, nc, npix, d_candi, D, spread_iter, flags, logp_out, mean_out)
+#define LAUNCH3(DPT, T, HALF)                        \
+  do {                                               \
+    if (D == DPT * T) LAUNCH4(DPT, T, HALF, true);   \
+    else LAUNCH4(DPT, T, HALF, false);               \
+  } while (0)
 #define LAUNCH(DPT, T)                       \
   do {                                       \
     if (half == 0) LAUNCH3(DPT, T, 0);       \
@@ -228,12 +292,14 @@ extern "C" int lc_sense_fuse(const LcDevice* dev, const float* logp_in, const fl
     else if (half == 2) LAUNCH3(DPT, T, 2);  \
     else LAUNCH3(DPT, T, 3);                 \
   } while (0)
-  // each pixel's depth column is split over T adjacent lanes, at most 32 bins per lane (register budget)
+  // each pixel's depth column is split over T adjacent lanes, at most 32 bins per lane (register budget);
+  // D == DPT*T (16, 32, 64, 128) compiles without any per-bin bound check
   if (D <= 16) LAUNCH(16, 1);
   else if (D <= 32) LAUNCH(32, 1);
   else if (D <= 64) LAUNCH(32, 2);
   else LAUNCH(32, 4);
 #undef LAUNCH
 #undef LAUNCH3
+#undef LAUNCH4
   return check_launch("lc_sense_fuse");
 }
