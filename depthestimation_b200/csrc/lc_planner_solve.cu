@@ -4,18 +4,25 @@
 // dp(i,k) = umap(k,i) + best over the edge window [lo,hi] of ray i+1, rays processed right to left.
 // The reference's total order over a node's edges is
 //   (unc = fl(u + unc[e]) larger) > (las = dth^2 + las[e] smaller) > (first in edge order), "no edge" first,
-// and max-propagation through zero regions of the map makes exact ties in the first key COMMON (5-20 % of the
-// nodes), so the second key decides real paths and must be evaluated exactly.  The kernel is bound by
-// instruction issue on the ~W*R*|window| edge visits, so the scan is organised to touch most edges at a
-// quarter instruction each:
-//   * the ray just finished keeps, next to unc[], the maxima of its aligned groups of four (qm[]);
-//   * pass 1: window max m from qm[] (interior) + the two boundary groups entry by entry;
-//     fl(u + x) is monotone in x, so fl(u + m) is the winning first key;
-//   * pass 2: a group can hold a first-key tie only if fl(u + qm) == fl(u + m); only those groups are
-//     opened and their entries compared exactly on (las, e).
-// Both passes are associative reductions under the reference's order, so the selected index is exactly the
-// one its sequential strict-'>' scan selects: results are bit-exact.  One CTA = one umap, LANES threads per
-// node; back-pointers for all W x R nodes stay in shared memory (W*R bytes) for the final path unroll.
+// and max-propagation through zero regions of the map makes exact ties in the first key COMMON (about a fifth
+// of the nodes), so the second key decides real paths and must be evaluated exactly.
+//
+// The rays are a serial chain (W steps) and one CTA works on one umap on an otherwise idle SM, so what counts
+// is the length of the dependent instruction chain per ray, not throughput.  Each ray is done in two phases,
+// both written branch-free with all shared-memory loads issued up front:
+//   A. LANES threads per node.  The finished ray keeps, next to unc[], the maxima of its aligned groups of
+//      four (qm[]).  A lane holds up to NQL interior groups of the node's window in registers; lanes 0 and
+//      LANES-1 also hold the two boundary groups entry by entry.  Window maximum m; fl(u + x) is monotone in
+//      x, so fl(u + m) is the winning first key and the node's new unc.  The groups / boundary entries that
+//      can hold a first-key tie (fl(u + .) == fl(u + m)) are counted.  If exactly one group qualifies, its
+//      lane opens it; if exactly one of its entries ties, the node is finished.  Everything else (several
+//      groups or several entries tie) is queued.
+//   B. one WARP per queued node: the previous ray sits in the warp's registers, four entries per lane; tie
+//      flags, the second key for the tied entries, and two REDUX.min give the exact (las, e) minimum with no
+//      divergence, however many entries tie.
+// Both phases are associative reductions under the reference's order, so the selected edge is exactly the one
+// its sequential strict-'>' scan selects: results are bit-exact.  Back-pointers for all W x R nodes stay in
+// shared memory (W*R bytes) for the final path unroll.
 #include <cstdlib>
 
 #include "lc_device.cuh"
@@ -24,161 +31,222 @@ namespace dpv {
 
 struct RayIn {
   float u, th;
-  int lo, hi;
+  unsigned w;         // lo | hi << 8, unpacked only when used (an early unpack would wait for the load)
 };
 
-struct Best {          // running minimum of (las, e) among first-key ties
-  float l;
-  int e;
+struct __align__(16) TieRec {       // a node queued for phase B
+  int k, lo, hi;
+  float u;
+  float tn, tmax, pad0, pad1;
 };
 
-template <int LANES>
+constexpr unsigned kNoWindow = 1u;  // lo = 1 > hi = 0
+
+// LANES threads per node, NQL interior groups per lane: covers R <= 4 * LANES * NQL range entries
+template <int LANES, int NQL>
 __global__ void __launch_bounds__(1024)
-planner_solve_kernel(const float* __restrict__ umaps, int W, int R, int RP, const float* __restrict__ theta,
+planner_solve_kernel(const float* __restrict__ umaps, int W, int R, const float* __restrict__ theta,
                      const float* __restrict__ node_xz, const uint8_t* __restrict__ win, int32_t* __restrict__ ks,
                      float* __restrict__ xz, int32_t* __restrict__ counts) {
+  constexpr int NQ = LANES * NQL;                                 // groups of four per ray
+  constexpr int RP = 4 * NQ;                                      // padded ray length (multiple of 128)
+  constexpr int NCH = RP / 128;
+  static_assert(RP % 128 == 0, "ray length must fill whole warps in phase B");
   extern __shared__ __align__(16) unsigned char smraw[];
-  const int NQ = RP / 4;
-  float* unc = reinterpret_cast<float*>(smraw);            // [2][RP]   RP = R rounded up to 4 (pad = -inf)
-  float* las = unc + 2 * RP;                               // [2][RP]
-  float* th = las + 2 * RP;                                // [2][RP]
-  float* qm = th + 2 * RP;                                 // [2][NQ]   max of unc[4q..4q+3]
-  int16_t* path = reinterpret_cast<int16_t*>(qm + 2 * NQ + (NQ & 1) * 2);   // [W rounded to even]
-  uint8_t* sub = reinterpret_cast<uint8_t*>(path + ((W + 1) & ~1));         // [W][R]
+  float* state = reinterpret_cast<float*>(smraw);                 // [2][3][RP]: unc (pad -inf), las, th
+  float* qm = state + 6 * RP;                                     // [2][NQ]: max of unc[4q..4q+3]
+  TieRec* rec = reinterpret_cast<TieRec*>(qm + 2 * NQ);           // [R]
+  int16_t* path = reinterpret_cast<int16_t*>(rec + R);            // [W rounded to 8]
+  uint8_t* sub = reinterpret_cast<uint8_t*>(path + ((W + 7) & ~7));   // [W][R]
+  __shared__ int s_ties[2];
   __shared__ int s_cnt;
 
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int k = threadIdx.x / LANES, s = threadIdx.x % LANES;
-  const bool active = k < R;
-  const float* umap = umaps + (size_t)blockIdx.x * R * W;
+  const bool active = k < R;                                      // phase-A thread with a node
+  const bool in_a = (int)threadIdx.x < ((R * LANES + 31) & ~31);  // warps that take part in phase A
   const unsigned full = 0xffffffffu;
-  // shuffles inside per-node branches name only the node's own lanes (branches differ between nodes of a warp)
-  const unsigned gmask = ((1u << LANES) - 1u) << ((threadIdx.x & 31) & ~(LANES - 1));
-  for (int i = threadIdx.x; i < 6 * RP + 2 * NQ; i += blockDim.x) unc[i] = -INFINITY;   // pads never win a max
+
+  for (int i = threadIdx.x; i < 6 * RP; i += blockDim.x) state[i] = ((i % (3 * RP)) < RP) ? -INFINITY : 0.f;
+  for (int i = threadIdx.x; i < 2 * NQ; i += blockDim.x) qm[i] = -INFINITY;
+  if (threadIdx.x < 2) s_ties[threadIdx.x] = 0;
   __syncthreads();
 
-  auto fetch = [&](int i) {
+  // input pointers of this thread's node, walked right to left
+  const int kc = active ? k : 0;
+  const float* pu = umaps + (size_t)blockIdx.x * R * W + (size_t)kc * W + (W - 1);
+  const float* pth = theta + (size_t)(W - 1) * R + kc;
+  const uint16_t* pw = reinterpret_cast<const uint16_t*>(win) + (size_t)(W - 1) * R + kc;
+  auto fetch = [&](int i) {                                       // i = ray the pointers stand on
     RayIn r;
-    r.u = 0.f; r.th = 0.f; r.lo = 1; r.hi = 0;
+    r.u = 0.f; r.th = 0.f; r.w = kNoWindow;
     if (active && i >= 0) {
-      r.u = __ldg(umap + (size_t)k * W + i);
-      r.th = __ldg(theta + (size_t)i * R + k);
-      if (i < W - 1) {
-        const uchar2 w2 = *reinterpret_cast<const uchar2*>(win + ((size_t)i * R + k) * 2);
-        r.lo = w2.x; r.hi = w2.y;
-      }
+      r.u = __ldg(pu);
+      r.th = __ldg(pth);
+      if (i < W - 1) r.w = __ldg(pw);
     }
+    pu -= 1; pth -= R; pw -= R;
     return r;
   };
   // software pipeline: inputs of ray i-3 are requested while ray i is processed
   RayIn cur = fetch(W - 1), n1 = fetch(W - 2), n2 = fetch(W - 3);
-  int buf = 0;
+
   for (int i = W - 1; i >= 0; i--) {
-    const RayIn in = cur;
-    cur = n1; n1 = n2; n2 = fetch(i - 3);
-    const float* uncn = unc + (buf ^ 1) * RP;
-    const float* lasn = las + (buf ^ 1) * RP;
-    const float* thn = th + (buf ^ 1) * RP;
-    const float* qmn = qm + (buf ^ 1) * NQ;
-    const float u = in.u, tn = in.th;
-    const int lo = in.lo, hi = in.hi;
-    float bu = u, bl = 0.f;                                     // Trajectory(node): planning.cpp:169-184
-    int be = -1;
-    if (lo <= hi) {                                             // same for the LANES threads of a node
+    const int par = i & 1;
+    const float* uncn = state + (par ^ 1) * 3 * RP;               // ray i+1
+    const float* lasn = uncn + RP;
+    const float* thn = uncn + 2 * RP;
+    const float* qmn = qm + (par ^ 1) * NQ;
+    float* unco = state + par * 3 * RP;                           // ray i
+    uint8_t* subi = sub + (size_t)i * R;
+    if (threadIdx.x == 0) s_ties[par ^ 1] = 0;                    // last read two barriers ago, next used on ray i-1
+
+    if (in_a) {
+      // ================= phase A =================
+      const RayIn in = cur;
+      cur = n1; n1 = n2; n2 = fetch(i - 3);
+      const float u = in.u, tn = in.th;
+      const int lo = (int)(in.w & 0xffu), hi = (int)(in.w >> 8);
       const int qlo = lo >> 2, qhi = hi >> 2;
-      // ---- pass 1: window maximum --------------------------------------------------------
-      float m = -INFINITY, mb = -INFINITY;                      // mb: this lane's boundary-group maximum
-      if (s == 0) {                                             // boundary groups, entry by entry
-        const float4 a = reinterpret_cast<const float4*>(uncn)[qlo];
-        const int e = qlo << 2;
-        if (e >= lo && e <= hi) m = fmaxf(m, a.x);
-        if (e + 1 >= lo && e + 1 <= hi) m = fmaxf(m, a.y);
-        if (e + 2 >= lo && e + 2 <= hi) m = fmaxf(m, a.z);
-        if (e + 3 >= lo && e + 3 <= hi) m = fmaxf(m, a.w);
-        mb = m;
-      }
-      float mb2 = -INFINITY;
-      if (s == LANES - 1 && qhi != qlo) {
-        const float4 a = reinterpret_cast<const float4*>(uncn)[qhi];
-        const int e = qhi << 2;
-        if (e <= hi) mb2 = fmaxf(mb2, a.x);
-        if (e + 1 <= hi) mb2 = fmaxf(mb2, a.y);
-        if (e + 2 <= hi) mb2 = fmaxf(mb2, a.z);
-        if (e + 3 <= hi) mb2 = fmaxf(mb2, a.w);
-        m = fmaxf(m, mb2);
-      }
-      {
-        float m1 = -INFINITY;
-        int q = qlo + 1 + s;
-        for (; q + LANES < qhi; q += 2 * LANES) {               // interior groups: one value per four edges
-          m = fmaxf(m, qmn[q]);
-          m1 = fmaxf(m1, qmn[q + LANES]);
-        }
-        if (q < qhi) m = fmaxf(m, qmn[q]);
-        m = fmaxf(m, m1);
-      }
+      const bool has_win = lo <= hi;                              // same for the LANES threads of a node
+      // ---- loads: this lane's boundary group (lane 0: group of lo, lane LANES-1: group of hi) and its
+      //      interior groups qlo+1+s, +LANES, ... < qhi
+      const bool is_b = has_win && (s == 0 || (s == LANES - 1 && qhi != qlo));
+      const int qb = s == 0 ? qlo : qhi;
+      const float4 araw = reinterpret_cast<const float4*>(uncn)[qb];
+      float qv[NQL];
 #pragma unroll
-      for (int off = LANES / 2; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(gmask, m, off));
-      const float tmax = __fadd_rn(u, m);                       // :194
-      if (tmax > u) {                                           // strict '>' against the bare node
-        // ---- pass 2: among first-key ties, min (las, e) ---------------------------------
-        Best bb;
-        bb.l = INFINITY; bb.e = 0x7fffffff;
-        auto open_group = [&](int q) {
+      for (int j = 0; j < NQL; j++) {
+        const int q = qlo + 1 + s + j * LANES;
+        qv[j] = qmn[q < NQ ? q : NQ - 1];
+      }
+      const int eb = qb << 2;
+      float4 a;                                                   // boundary entries inside the window, else -inf
+      a.x = (is_b && eb >= lo && eb <= hi) ? araw.x : -INFINITY;
+      a.y = (is_b && eb + 1 >= lo && eb + 1 <= hi) ? araw.y : -INFINITY;
+      a.z = (is_b && eb + 2 >= lo && eb + 2 <= hi) ? araw.z : -INFINITY;
+      a.w = (is_b && eb + 3 >= lo && eb + 3 <= hi) ? araw.w : -INFINITY;
+      float m = fmaxf(fmaxf(a.x, a.y), fmaxf(a.z, a.w)), m1 = -INFINITY;
+#pragma unroll
+      for (int j = 0; j < NQL; j++) {
+        if (!(has_win && qlo + 1 + s + j * LANES < qhi)) qv[j] = -INFINITY;
+        if (j & 1) m1 = fmaxf(m1, qv[j]);
+        else m = fmaxf(m, qv[j]);
+      }
+      m = fmaxf(m, m1);
+#pragma unroll
+      for (int off = LANES / 2; off > 0; off >>= 1) m = fmaxf(m, __shfl_xor_sync(full, m, off));
+      const float tmax = __fadd_rn(u, m);                         // :194
+      const bool better = tmax > u;                               // strict '>' against the bare node
+      // ---- which groups / boundary entries can hold a first-key tie (-inf never does once tmax > u)
+      unsigned bb = 0, qbits = 0;
+      if (__fadd_rn(u, a.x) == tmax) bb |= 1u;
+      if (__fadd_rn(u, a.y) == tmax) bb |= 2u;
+      if (__fadd_rn(u, a.z) == tmax) bb |= 4u;
+      if (__fadd_rn(u, a.w) == tmax) bb |= 8u;
+#pragma unroll
+      for (int j = 0; j < NQL; j++)
+        if (__fadd_rn(u, qv[j]) == tmax) qbits |= 1u << j;
+      if (!better) { bb = 0; qbits = 0; }
+      const int mine = __popc(bb) + __popc(qbits);
+      int tot = mine;
+#pragma unroll
+      for (int off = LANES / 2; off > 0; off >>= 1) tot += __shfl_xor_sync(full, tot, off);
+      // ---- exactly one candidate: its lane finishes the node, or finds several ties inside an interior group
+      float bl = 0.f;
+      int be = -1;
+      const bool owner = tot == 1 && mine == 1;                   // implies better
+      bool solved = false;
+      if (owner) {
+        int e1 = eb + __ffs(bb) - 1;                              // the tied boundary entry
+        solved = bb != 0;
+        if (!solved) {                                            // an interior group: open it
+          const int q = qlo + 1 + s + (__ffs(qbits) - 1) * LANES;
           const float4 v = reinterpret_cast<const float4*>(uncn)[q];
-          const float4 t4 = reinterpret_cast<const float4*>(thn)[q];
-          const float4 l4 = reinterpret_cast<const float4*>(lasn)[q];
-          const int e = q << 2;
-          float dth, tl;
-          if (e >= lo && e <= hi && __fadd_rn(u, v.x) == tmax) {
-            dth = __fsub_rn(t4.x, tn); tl = __fadd_rn(__fmul_rn(dth, dth), l4.x);          // :197-198
-            if (tl < bb.l || (tl == bb.l && e < bb.e)) { bb.l = tl; bb.e = e; }
-          }
-          if (e + 1 >= lo && e + 1 <= hi && __fadd_rn(u, v.y) == tmax) {
-            dth = __fsub_rn(t4.y, tn); tl = __fadd_rn(__fmul_rn(dth, dth), l4.y);
-            if (tl < bb.l || (tl == bb.l && e + 1 < bb.e)) { bb.l = tl; bb.e = e + 1; }
-          }
-          if (e + 2 >= lo && e + 2 <= hi && __fadd_rn(u, v.z) == tmax) {
-            dth = __fsub_rn(t4.z, tn); tl = __fadd_rn(__fmul_rn(dth, dth), l4.z);
-            if (tl < bb.l || (tl == bb.l && e + 2 < bb.e)) { bb.l = tl; bb.e = e + 2; }
-          }
-          if (e + 3 >= lo && e + 3 <= hi && __fadd_rn(u, v.w) == tmax) {
-            dth = __fsub_rn(t4.w, tn); tl = __fadd_rn(__fmul_rn(dth, dth), l4.w);
-            if (tl < bb.l || (tl == bb.l && e + 3 < bb.e)) { bb.l = tl; bb.e = e + 3; }
-          }
-        };
-        if (s == 0 && __fadd_rn(u, mb) == tmax) open_group(qlo);
-        if (s == LANES - 1 && qhi != qlo && __fadd_rn(u, mb2) == tmax) open_group(qhi);
-        for (int q = qlo + 1 + s; q < qhi; q += LANES)
-          if (__fadd_rn(u, qmn[q]) == tmax) open_group(q);
-#pragma unroll
-        for (int off = LANES / 2; off > 0; off >>= 1) {
-          const float ol = __shfl_xor_sync(gmask, bb.l, off);
-          const int oe = __shfl_xor_sync(gmask, bb.e, off);
-          if (ol < bb.l || (ol == bb.l && oe < bb.e)) { bb.l = ol; bb.e = oe; }
+          unsigned eq = 0;
+          if (__fadd_rn(u, v.x) == tmax) eq |= 1u;
+          if (__fadd_rn(u, v.y) == tmax) eq |= 2u;
+          if (__fadd_rn(u, v.z) == tmax) eq |= 4u;
+          if (__fadd_rn(u, v.w) == tmax) eq |= 8u;
+          e1 = (q << 2) + __ffs(eq) - 1;
+          solved = __popc(eq) == 1;
         }
-        bu = tmax; bl = bb.l; be = bb.e;                        // :210-217
+        if (solved) {
+          const float dth = __fsub_rn(thn[e1], tn);               // :197-198
+          bl = __fadd_rn(__fmul_rn(dth, dth), lasn[e1]);
+          be = e1;
+        }
       }
-    }
-    // group-of-four maxima of the new unc[] (nodes 4j..4j+3 are 4*LANES adjacent lanes)
-    float gq = active ? bu : -INFINITY;
-    gq = fmaxf(gq, __shfl_xor_sync(full, gq, LANES));
-    gq = fmaxf(gq, __shfl_xor_sync(full, gq, 2 * LANES));
-    if (s == 0 && k < RP) {
+      // ---- queue what is left for phase B (one pushing lane per node)
+      const bool push = active && ((owner && !solved) || (s == 0 && tot >= 2));
+      const unsigned pb = __ballot_sync(full, push);
+      if (pb) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&s_ties[par], __popc(pb));
+        base = __shfl_sync(full, base, 0);
+        if (push) {
+          TieRec r;
+          r.k = k; r.lo = lo; r.hi = hi; r.u = u;
+          r.tn = tn; r.tmax = tmax; r.pad0 = 0.f; r.pad1 = 0.f;
+          rec[base + __popc(pb & ((1u << lane) - 1u))] = r;
+        }
+      }
+      // ---- results of this phase; group-of-four maxima of the new unc[] (4*LANES adjacent lanes)
+      const float bu = better ? tmax : u;                         // :210-217
+      float gq = active ? bu : -INFINITY;
+      gq = fmaxf(gq, __shfl_xor_sync(full, gq, LANES));
+      gq = fmaxf(gq, __shfl_xor_sync(full, gq, 2 * LANES));
       if (active) {
-        unc[buf * RP + k] = bu;
-        las[buf * RP + k] = bl;
-        th[buf * RP + k] = tn;
-        sub[(size_t)i * R + k] = be < 0 ? 255 : (uint8_t)be;
+        if (s == 0) {
+          unco[k] = bu;
+          unco[2 * RP + k] = tn;
+          if ((k & 3) == 0) qm[par * NQ + (k >> 2)] = gq;
+        }
+        if ((s == 0 && !better) || solved) {                      // bare node (las 0, no successor) or finished
+          unco[RP + k] = bl;
+          subi[k] = be < 0 ? 255 : (uint8_t)be;
+        }
       }
-      if ((k & 3) == 0) qm[buf * NQ + (k >> 2)] = gq;
     }
     __syncthreads();
-    buf ^= 1;
+    // ================= phase B: queued nodes, one warp each =================
+    const int nt = s_ties[par];
+    if (nt > 0) {                                                 // same for the whole CTA
+      for (int j = warp; j < nt; j += nwarps) {
+        const float4 r0 = reinterpret_cast<const float4*>(rec + j)[0], r1 = reinterpret_cast<const float4*>(rec + j)[1];
+        const int rk = __float_as_int(r0.x), rlo = __float_as_int(r0.y), rhi = __float_as_int(r0.z);
+        const float ru = r0.w, rtn = r1.x, rtmax = r1.y;
+        float tl_best = INFINITY;
+        int e_best = 0x7fffffff;
+#pragma unroll
+        for (int c = 0; c < NCH; c++) {                           // chunks of 128 entries, four per lane
+          const int e = c * 128 + lane * 4;
+          const float4 v = reinterpret_cast<const float4*>(uncn)[c * 32 + lane];
+          const float4 t4 = reinterpret_cast<const float4*>(thn)[c * 32 + lane];
+          const float4 l4 = reinterpret_cast<const float4*>(lasn)[c * 32 + lane];
+          const float vv[4] = {v.x, v.y, v.z, v.w}, tt[4] = {t4.x, t4.y, t4.z, t4.w}, ll[4] = {l4.x, l4.y, l4.z, l4.w};
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            const float dth = __fsub_rn(tt[q], rtn);              // :197-198
+            const float tl = __fadd_rn(__fmul_rn(dth, dth), ll[q]);
+            const bool tie = e + q >= rlo && e + q <= rhi && __fadd_rn(ru, vv[q]) == rtmax;
+            if (tie && tl < tl_best) { tl_best = tl; e_best = e + q; }    // increasing e: first minimum stays
+          }
+        }
+        const unsigned tmin = __reduce_min_sync(full, __float_as_uint(tl_best));   // las >= +0: bit order = value order
+        const int be = __reduce_min_sync(full, __float_as_uint(tl_best) == tmin ? e_best : 0x7fffffff);
+        if (lane == 0) {
+          unco[RP + rk] = __uint_as_float(tmin);
+          subi[rk] = (uint8_t)be;
+        }
+      }
+      __syncthreads();
+    }
   }
-  // ray 0 results are in buffer buf^1.  Best start against a default (0,0,null) trajectory (:99-104)
+  // ray 0 results are in state[0].  Best start against a default (0,0,null) trajectory (:99-104)
   if (threadIdx.x == 0) {
-    const float* u0 = unc + (buf ^ 1) * RP;
-    const float* l0 = las + (buf ^ 1) * RP;
+    const float* u0 = state;
+    const float* l0 = state + RP;
     float bu = 0.f, bl = 0.f;
     int bk = -1;
     for (int kk = 0; kk < R; kk++) {
@@ -208,11 +276,10 @@ planner_solve_kernel(const float* __restrict__ umaps, int W, int R, int RP, cons
     if (xz) {
       float x = 0.f, z = 0.f;
       if (kk >= 0) {
-        x = node_xz[((size_t)i * R + kk) * 2];
-        z = node_xz[((size_t)i * R + kk) * 2 + 1];
+        const float2 p = *reinterpret_cast<const float2*>(node_xz + ((size_t)i * R + kk) * 2);
+        x = p.x; z = p.y;
       }
-      xz[((size_t)blockIdx.x * W + i) * 2] = x;
-      xz[((size_t)blockIdx.x * W + i) * 2 + 1] = z;
+      *reinterpret_cast<float2*>(xz + ((size_t)blockIdx.x * W + i) * 2) = make_float2(x, z);
     }
   }
 }
@@ -221,32 +288,45 @@ planner_solve_kernel(const float* __restrict__ umaps, int W, int R, int RP, cons
 
 using namespace dpv;
 
+namespace {
+
+template <int LANES, int NQL>
+int launch_solve(const LcPlanner* p, const float* umaps, int n, int warps, int32_t* ks, float* xz, int32_t* counts,
+                 cudaStream_t st) {
+  static_assert(LANES >= 2, "the two boundary groups of a window are held by different lanes");
+  const int W = p->W, R = p->R;
+  constexpr int RP = 4 * LANES * NQL;
+  DPV_REQUIRE(R <= RP, "lc_planner_solve: R=%d does not fit the %d-entry kernel", R, RP);
+  const size_t smem = (size_t)6 * RP * 4 + (size_t)2 * (RP / 4) * 4 + (size_t)R * sizeof(TieRec) +
+                      (size_t)((W + 7) & ~7) * 2 + (size_t)W * R;
+  DPV_REQUIRE(smem <= 227 * 1024, "lc_planner_solve: W*R = %d*%d back-pointers exceed shared memory", W, R);
+  auto kern = planner_solve_kernel<LANES, NQL>;
+  DPV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int threads = 32 * warps;
+  const int need = ((R * LANES + 31) / 32) * 32;                  // phase A: LANES threads per node
+  if (threads < need) threads = need;
+  DPV_REQUIRE(threads <= 1024, "lc_planner_solve: R=%d needs %d threads", R, threads);
+  kern<<<n, threads, smem, st>>>(umaps, W, R, p->d_theta, p->d_xz, p->d_win, ks, xz, counts);
+  return DPV_OK;
+}
+
+}  // namespace
+
 extern "C" int lc_planner_solve(LcPlanner* p, const float* umaps, int n, int32_t* ks, float* xz, int32_t* counts,
                                 void* stream) {
   DPV_REQUIRE(p && umaps, "lc_planner_solve: null pointer");
   DPV_REQUIRE(n > 0, "lc_planner_solve: n=%d", n);
-  const int W = p->W, R = p->R;
-  const int RP = ((R + 3) / 4) * 4;
-  int lanes = 4;
-  if (const char* e = getenv("DPV_PLANNER_LANES")) lanes = atoi(e);                // tuning aid (1,2,4,8)
-  if (lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8) lanes = 4;
-  while (lanes > 1 && RP * lanes > 1024) lanes >>= 1;
-  const int threads = ((RP * lanes + 31) / 32) * 32;
-  const int NQ = RP / 4;
-  size_t smem = (size_t)6 * RP * 4 + (size_t)(2 * NQ + (NQ & 1) * 2) * 4 + (size_t)((W + 1) & ~1) * 2 + (size_t)W * R;
-  DPV_REQUIRE(smem <= 227 * 1024, "lc_planner_solve: W*R = %d*%d back-pointers exceed shared memory", W, R);
+  int lanes = 4, warps = 16;
+  if (const char* e = getenv("DPV_PLANNER_LANES")) lanes = atoi(e);                // tuning aids
+  if (const char* e = getenv("DPV_PLANNER_WARPS")) warps = atoi(e);
+  if (warps < 1) warps = 1;
+  if (warps > 32) warps = 32;
   cudaStream_t st = (cudaStream_t)stream;
-#define LAUNCH(L)                                                                                               \
-  do {                                                                                                          \
-    DPV_CUDA(cudaFuncSetAttribute(planner_solve_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize,         \
-                                  (int)smem));                                                                  \
-    planner_solve_kernel<L><<<n, threads, smem, st>>>(umaps, W, R, RP, p->d_theta, p->d_xz, p->d_win, ks, xz,   \
-                                                      counts);                                                  \
-  } while (0)
-  if (lanes == 8) LAUNCH(8);
-  else if (lanes == 4) LAUNCH(4);
-  else if (lanes == 2) LAUNCH(2);
-  else LAUNCH(1);
-#undef LAUNCH
+  int rc;
+  if (p->R > 128) rc = launch_solve<4, 16>(p, umaps, n, warps, ks, xz, counts, st);     // up to 256 entries
+  else if (lanes == 8) rc = launch_solve<8, 4>(p, umaps, n, warps, ks, xz, counts, st);
+  else if (lanes == 2) rc = launch_solve<2, 16>(p, umaps, n, warps, ks, xz, counts, st);
+  else rc = launch_solve<4, 8>(p, umaps, n, warps, ks, xz, counts, st);
+  if (rc != DPV_OK) return rc;
   return check_launch("lc_planner_solve");
 }
