@@ -64,8 +64,9 @@ class LCDevice:
 
     def __del__(self):
         h = getattr(self, "_h", None)
-        if h and _lib._lib is not None:
-            _lib._lib.lc_device_destroy(h)
+        loaded = getattr(_lib, "_lib", None)          # module globals are already gone at interpreter exit
+        if h and loaded is not None:
+            loaded.lc_device_destroy(h)
             self._h = None
 
     def valid_angles(self):
@@ -164,8 +165,9 @@ class PlannerRT:
 
     def __del__(self):
         h = getattr(self, "_h", None)
-        if h and _lib._lib is not None:
-            _lib._lib.lc_planner_destroy(h)
+        loaded = getattr(_lib, "_lib", None)
+        if h and loaded is not None:
+            loaded.lc_planner_destroy(h)
             self._h = None
 
     def edge_count(self):

@@ -22,8 +22,8 @@ def main():
     B, D, H, W, R, nc = st.shape
     um = st.umaps.view(B * nc, R, W)
     ref = None
-    for cl in (2, 4, 8):
-        for warps in (8, 16, 32):
+    for cl in (2, 4):
+        for warps in (4, 8, 16):
             os.environ["DPV_PLANNER_LANES"] = str(cl)
             os.environ["DPV_PLANNER_WARPS"] = str(warps)
             ks = torch.empty_like(st.ks)
