@@ -57,6 +57,14 @@ SIGNATURES = {
     "lc_sense_likelihood": (c_int, [c_vp, c_fp, c_fp, c_fp, c_int, c_int, c_fp, c_int, c_fp, c_vp]),
     "lc_sense_fuse": (c_int, [c_vp, c_fp, c_fp, c_fp, c_fp, c_int, c_int, c_fp, c_int, c_int, c_int, c_int, c_fp, c_fp,
                               c_vp]),
+    "dpv_truth_dpv": (c_int, [c_fp, c_fp, c_int, c_int, c_int, c_fp, c_int, c_f, c_fp, c_vp]),
+    "lc_likelihood_true": (c_int, [c_fp, c_fp, c_fp, c_fp, c_f, c_f, c_ll, c_fp, c_int, c_fp, c_fp, c_vp]),
+    "dpv_inverse_warp": (c_int, [c_fp, c_fp, c_fp, c_fp, c_int, c_int, c_int, c_int, c_int, c_int, c_fp, c_vp, c_vp]),
+    "dpv_correlation_shape": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_int, ctypes.POINTER(c_int),
+                                      ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
+    "dpv_correlation": (c_int, [c_fp, c_fp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_fp, c_vp]),
+    "dpv_depth_errors": (c_int, [c_fp, c_fp, c_int, c_int, c_int, c_fp, c_vp]),
+    "dpv_unc_rmse": (c_int, [c_fp, c_fp, c_int, c_int, c_fp, c_fp, c_vp]),
 }
 
 _lib = None

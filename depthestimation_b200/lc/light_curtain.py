@@ -174,3 +174,14 @@ class LightCurtain:
 
     def sense_low(self, depth_rgb, design_pts_lc, visualizer=None, noise=None):
         return self._sense(depth_rgb, design_pts_lc, "low", noise)
+
+    def gen_lc_dpv_true(self, sensed_arr, std_div, peak_img=None):
+        """light_curtain.py:1106-1125 — likelihood of a real sensor return under the intensity model
+        (img_utils.lc_intensities_to_dist).  sensed_arr [3,H,W] = (depth, intensity 0..255, thickness) -> DPV [D,H,W]."""
+        s = ops.f32(sensed_arr, self.device)
+        depth = s[0]
+        mask = (depth > 0).float()
+        unc = (s[2] * mask) / std_div                                  # :1122, "** 1"
+        inten = (s[1] * mask) / 255.
+        peak = 0.2 if peak_img is None else ops.f32(peak_img, self.device)
+        return ops.likelihood_true(depth, inten, unc, self.d_candi, 0.1, peak)

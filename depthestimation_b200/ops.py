@@ -165,3 +165,96 @@ def plan_prepare(uf, flow, steps, R, umaps=None, argmax=None, field_pre=None):
     check(lib().lc_plan_prepare(ptr(uf), B, D, W, int(R), ptr(flow), ctypes.cast(st, ctypes.c_void_p), n,
                                 ptr(umaps), ptr(argmax), ptr(field_pre), stream_ptr(dev)))
     return umaps, argmax, field_pre
+
+
+# --------------------------------------------------------------------------------------------------
+# callers either side of the fused path
+# --------------------------------------------------------------------------------------------------
+def truth_dpv(dmaps, masks, d_candi, var=0.3):
+    """dmaps [B,H,W], masks [B,1,H,W] or [B,H,W] -> [B,D,H,W] (gen_dpv_withmask)."""
+    dm = f32(dmaps)
+    mk = f32(masks, dm.device).reshape(dm.shape)
+    B, H, W = dm.shape
+    dc = d_candi_tensor(d_candi, dm.device)
+    out = torch.empty(B, dc.numel(), H, W, device=dm.device)
+    with torch.cuda.device(_dev(dm)):
+        check(lib().dpv_truth_dpv(ptr(dm), ptr(mk), B, H, W, ptr(dc), dc.numel(), float(var), ptr(out),
+                                  stream_ptr(dm.device)))
+    return out
+
+
+def likelihood_true(placement, intensity, inten_sigma, d_candi, noise_sigma=0.1, peak=0.2, want_mean=False):
+    """Per-pixel inputs of any (equal) shape S -> lik [D,*S] (and mean intensities [D,*S])."""
+    z = f32(placement)
+    x = f32(intensity, z.device).reshape(z.shape)
+    sg = f32(inten_sigma, z.device).reshape(z.shape)
+    pk_t, pk_c = (None, float(peak)) if isinstance(peak, (int, float)) else (f32(peak, z.device).reshape(z.shape), 0.0)
+    dc = d_candi_tensor(d_candi, z.device)
+    D = dc.numel()
+    lik = torch.empty((D,) + tuple(z.shape), device=z.device)
+    mean = torch.empty_like(lik) if want_mean else None
+    with torch.cuda.device(_dev(z)):
+        check(lib().lc_likelihood_true(ptr(z), ptr(x), ptr(sg), ptr(pk_t), pk_c, float(noise_sigma), z.numel(), ptr(dc),
+                                       D, ptr(mean), ptr(lik), stream_ptr(z.device)))
+    return (mean, lik) if want_mean else lik
+
+
+_WARP_MODES = {"bilinear": 0, "nearest": 1}
+_WARP_PADDING = {"zeros": 0, "border": 1, "reflection": 2}
+
+
+def inverse_warp(img, depth, Kinv, P, mode="bilinear", padding_mode="zeros"):
+    """img [B,C,H,W], depth [B,H,W], Kinv [B,3,3], P [B,3,4] -> (warped [B,C,H,W], valid [B,H,W] bool)."""
+    im = f32(img)
+    dp = f32(depth, im.device)
+    ki = f32(Kinv, im.device)
+    pm = f32(P, im.device)
+    B, C, H, W = im.shape
+    if mode not in _WARP_MODES or padding_mode not in _WARP_PADDING:
+        raise ValueError("inverse_warp: mode %r / padding_mode %r" % (mode, padding_mode))
+    out = torch.empty_like(im)
+    valid = torch.empty(B, H, W, dtype=torch.uint8, device=im.device)
+    with torch.cuda.device(_dev(im)):
+        check(lib().dpv_inverse_warp(ptr(im), ptr(dp), ptr(ki), ptr(pm), B, C, H, W, _WARP_MODES[mode],
+                                     _WARP_PADDING[padding_mode], ptr(out), valid.data_ptr(), stream_ptr(im.device)))
+    return out, valid.bool()
+
+
+def correlation(x1, x2, pad_size, kernel_size, max_displacement, stride1, stride2):
+    """x1, x2 [B,C,H,W] -> [B,(2*(max_displacement//stride2)+1)^2,outH,outW]."""
+    a = f32(x1)
+    b = f32(x2, a.device)
+    if a.shape != b.shape:
+        raise ValueError("correlation: inputs differ in shape")
+    B, C, H, W = a.shape
+    oc, oh, ow = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    check(lib().dpv_correlation_shape(H, W, pad_size, kernel_size, max_displacement, stride1, stride2,
+                                      ctypes.byref(oc), ctypes.byref(oh), ctypes.byref(ow)))
+    out = torch.empty(B, oc.value, oh.value, ow.value, device=a.device)
+    with torch.cuda.device(_dev(a)):
+        check(lib().dpv_correlation(ptr(a), ptr(b), B, C, H, W, pad_size, kernel_size, max_displacement, stride1,
+                                    stride2, ptr(out), stream_ptr(a.device)))
+    return out
+
+
+def depth_errors(pred, gt):
+    """pred, gt [n,H,W] (gt < 0 invalid) -> [n,10] (9 KITTI metrics + valid-pixel count)."""
+    p = f32(pred)
+    g = f32(gt, p.device)
+    n, H, W = p.shape
+    out = torch.empty(n, 10, device=p.device)
+    with torch.cuda.device(_dev(p)):
+        check(lib().dpv_depth_errors(ptr(p), ptr(g), n, H, W, ptr(out), stream_ptr(p.device)))
+    return out
+
+
+def unc_rmse(field_truth, field_pred, d_candi):
+    """fields [D,W] probabilities -> 0-dim tensor."""
+    t = f32(field_truth)
+    p = f32(field_pred, t.device)
+    D, W = t.shape
+    dc = d_candi_tensor(d_candi, t.device)
+    out = torch.empty(1, device=t.device)
+    with torch.cuda.device(_dev(t)):
+        check(lib().dpv_unc_rmse(ptr(t), ptr(p), D, W, ptr(dc), ptr(out), stream_ptr(t.device)))
+    return out[0]

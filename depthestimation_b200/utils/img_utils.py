@@ -61,3 +61,64 @@ def gen_ufield(dpv_predicted, d_candi, intr_up, visualizer=None, img=None, BV_lo
         hi, _ = uf.max(1)
         uf = (uf - lo) / (hi - lo)
     return uf, dz
+
+
+def gen_dpv_withmask(dmaps, masks, d_candi, var=0.3):                # img_utils.py:567-582
+    return ops.truth_dpv(dmaps, masks, d_candi, var)
+
+
+def lc_intensities_to_dist(d_candi, placement, intensity, inten_sigma, noise_sigma, mean_scaling):
+    """img_utils.py:144-157.  placement/intensity/inten_sigma [...,1] -> (mean_intensities, norm_lhoods) [...,D]."""
+    shp = placement.shape[:-1]
+    peak = mean_scaling if isinstance(mean_scaling, (int, float)) else mean_scaling.reshape(shp)
+    mean, lik = ops.likelihood_true(placement.reshape(shp), intensity.reshape(shp), inten_sigma.reshape(shp), d_candi,
+                                    noise_sigma, peak, want_mean=True)
+    nd = len(shp)
+    back = list(range(1, nd + 1)) + [0]                               # depth-major [D,...] -> [...,D]
+    return mean.permute(*back), lik.permute(*back)
+
+
+def compute_unc_field(dpv_refined_predicted, dpv_refined_truth, d_candi, intr_refined, mask_refined, cfg):
+    """img_utils.py:366-369."""
+    unc_field_truth, _ = gen_ufield(dpv_refined_truth, d_candi, intr_refined.squeeze(0), BV_log=False,
+                                    mask=mask_refined, cfg=cfg)
+    unc_field_predicted, debugmap = gen_ufield(dpv_refined_predicted, d_candi, intr_refined.squeeze(0), BV_log=True,
+                                               cfg=cfg)
+    return unc_field_truth, unc_field_predicted, debugmap
+
+
+def compute_unc_rmse(unc_field_truth, unc_field_predicted, d_candi, plot=False):   # img_utils.py:371-390
+    return ops.unc_rmse(unc_field_truth[0], unc_field_predicted[0], d_candi)
+
+
+ERROR_NAMES = ("mae", "rmse", "inverse mae", "inverse rmse", "log mae", "log rmse", "scale invariant log",
+               "abs relative", "squared relative")                    # evaluate_depth.h:122-130
+
+
+def depth_error(predicted, truth):
+    """img_utils.py:162-167 + depthError (evaluate_depth.h:20-118): 9 errors of one image pair.
+    Accepts CUDA tensors [H,W] (or [n,H,W] -> [n,9]); zeros are invalid, as in the reference."""
+    p = torch.as_tensor(predicted)
+    t = torch.as_tensor(truth)
+    single = p.dim() == 2
+    if single:
+        p, t = p.unsqueeze(0), t.unsqueeze(0)
+    p = torch.where(p == 0, torch.full_like(p, -1.0), p) + epsilon
+    t = torch.where(t == 0, torch.full_like(t, -1.0), t) + epsilon
+    out = ops.depth_errors(p, t)
+    if bool((out[:, 9] == 0).any()):
+        raise RuntimeError("depth_error: ground truth has no valid pixel")   # evaluate_depth.h:94-97 throws
+    return out[0, :9] if single else out[:, :9]
+
+
+def eval_errors(errors):
+    """evaluateErrors (evaluate_depth.h:120-142, utils.h:23-48): name -> [mean, min (capped at 1), max (floored at 0)]."""
+    e = torch.stack([torch.as_tensor(x).float().reshape(9) for x in errors]).cpu()
+    res = {}
+    for i, name in enumerate(ERROR_NAMES):
+        col = e[:, i]
+        mean = torch.tensor(0.0)
+        for v in col:                                                 # sequential float sum like statMean
+            mean = mean + v
+        res[name] = [float(mean / len(col)), float(min(1.0, col.min())), float(max(0.0, col.max()))]
+    return res

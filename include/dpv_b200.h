@@ -161,6 +161,40 @@ int lc_sense_fuse(const LcDevice* dev, const float* logp_in, const float* depth,
                   const float* noise, int B, int nc, const float* d_candi, int D, int spread_iter,
                   int spread_n, int flags, float* logp_out, float* mean_out, void* stream);
 
+/* ---- callers either side of the fused path ----------------------------- */
+
+/* img_utils.gen_dpv_withmask (utils/img_utils.py:567-582): soft label of variance `var` around dmaps where
+ * masks = 1, uniform 1/D where masks = 0, clamped to [eps, 1].  dmaps, masks [B,H,W] -> out [B,D,H,W]. */
+int dpv_truth_dpv(const float* dmaps, const float* masks, int B, int H, int W, const float* d_candi, int D,
+                  float var, float* out, void* stream);
+/* img_utils.lc_intensities_to_dist (utils/img_utils.py:144-157), the likelihood of LightCurtain.gen_lc_dpv_true
+ * (lc/light_curtain.py:1106-1125): mean_i[d] = exp(-(|d - placement| / inten_sigma)^2) * peak,
+ * lik = softmax_d log N(intensity; mean_i[d], noise_sigma).  Per-pixel inputs [npix]; peak may be NULL
+ * (peak_const is used).  Outputs are depth-major [D,npix]; mean_out may be NULL. */
+int lc_likelihood_true(const float* placement, const float* intensity, const float* inten_sigma, const float* peak,
+                       float peak_const, float noise_sigma, long long npix, const float* d_candi, int D,
+                       float* mean_out, float* lik_out, void* stream);
+/* utils/inverse_warp.py:174-210 (pixel2cam :26-40, cam2pixel :43-69, F.grid_sample align_corners=False).
+ * img [B,C,H,W], depth [B,H,W], Kinv [B,3,3] = intrinsics^-1, P [B,3,4] = intrinsics @ pose
+ *   -> out [B,C,H,W], valid (nullable) [B,H,W] bytes.  mode 0 bilinear / 1 nearest; padding 0 zeros / 1 border /
+ * 2 reflection. */
+int dpv_inverse_warp(const float* img, const float* depth, const float* Kinv, const float* P, int B, int C, int H,
+                     int W, int mode, int padding, float* out, uint8_t* valid, void* stream);
+/* models/correlation_package (correlation_cuda.cc:21-38 shapes, correlation_cuda_kernel.cu:44-112 forward):
+ * out[b, (tj,ti), y, x] = mean over the kernel window and channels of pad(in1)[.., y1+j, x1+i] * pad(in2)[.., y2+j, x2+i],
+ * x1 = x*stride1 + max_displacement, x2 = x1 + ti*stride2.  in1, in2 [B,C,H,W] -> out [B,outC,outH,outW]. */
+int dpv_correlation_shape(int H, int W, int pad_size, int kernel_size, int max_displacement, int stride1,
+                          int stride2, int* outC, int* outH, int* outW);
+int dpv_correlation(const float* in1, const float* in2, int B, int C, int H, int W, int pad_size, int kernel_size,
+                    int max_displacement, int stride1, int stride2, float* out, void* stream);
+/* depthError (external/deval_lib/src/evaluate_depth.h:20-118): pred, gt [n,H,W] (gt < 0 = invalid)
+ *   -> out [n,10]: mae, rmse, inverse mae, inverse rmse, log mae, log rmse, scale invariant log, abs relative,
+ *      squared relative, number of valid pixels. */
+int dpv_depth_errors(const float* pred, const float* gt, int n_images, int H, int W, float* out, void* stream);
+/* img_utils.compute_unc_rmse (utils/img_utils.py:371-382): fields [D,W] (probabilities) -> out[1]. */
+int dpv_unc_rmse(const float* field_truth, const float* field_pred, int D, int W, const float* d_candi, float* out,
+                 void* stream);
+
 #ifdef __cplusplus
 }
 #endif

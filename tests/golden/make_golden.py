@@ -190,6 +190,63 @@ def case_light_curtain():
          angles=np.array(lc.fw_large.angles_output, np.float32))
 
 
+def case_aux():
+    """Rows a17 (gen_lc_dpv_true), a18 (inverse_warp), a19 (correlation_native twin) and compute_unc_rmse,
+    run on the unmodified reference -> aux.npz."""
+    import importlib.util
+    _install_lcsim_stubs()
+    import lc.light_curtain as LC
+    iw = ref_shim.load_inverse_warp()
+    g = torch.Generator().manual_seed(7)
+    # ---- inverse_warp: euler 6-vector, quaternion 6-vector and a 4x4 pose
+    B, C, H, W = 2, 3, 20, 28
+    img = torch.randn(B, C, H, W, generator=g)
+    depth = 4.0 + 6.0 * torch.rand(B, H, W, generator=g)
+    K, _ = intrinsics(W, H, hfov=60.0, vfov=45.0)
+    Kb = torch.tensor(K).unsqueeze(0).repeat(B, 1, 1)
+    pose6 = torch.tensor([[0.30, -0.10, 0.20, 0.02, -0.03, 0.01], [-0.40, 0.05, -0.30, -0.01, 0.04, 0.03]])
+    iw.pixel_coords = None
+    w_eb, v_eb = iw.inverse_warp(img, depth, pose6, Kb)
+    w_en, v_en = iw.inverse_warp(img, depth, pose6, Kb, mode="nearest", padding_mode="border")
+    w_qb, v_qb = iw.inverse_warp(img, depth, pose6, Kb, rotation_mode="quat", padding_mode="border")
+    pose44 = iw.pose_vec2mat_full(pose6)
+    w_m, v_m = iw.inverse_warp(img, depth, pose44, Kb)
+    # ---- correlation_native (kernel 1, strides 1, pad = max displacement)
+    spec = importlib.util.spec_from_file_location("ref_corr_native", "/root/reference/models/correlation_native.py")
+    cn = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(cn)
+    x1 = torch.randn(2, 5, 9, 11, generator=g)
+    x2 = torch.randn(2, 5, 9, 11, generator=g)
+    corr3 = cn.Correlation(max_displacement=3)(x1, x2)
+    # ---- compute_unc_rmse on two uncertainty fields (one with a NaN column)
+    D = 8
+    d = IU.powerf(5., 40., D, 1.0)
+    ft = torch.softmax(torch.randn(1, D, 24, generator=g), 1)
+    fp = torch.softmax(torch.randn(1, D, 24, generator=g), 1)
+    ft[0, :, 5] = float("nan")
+    rm = IU.compute_unc_rmse(ft.clone(), fp.clone(), d)
+    # ---- gen_lc_dpv_true (real-sensor likelihood)
+    class _Self:
+        pass
+    me = _Self()
+    me.d_candi = IU.powerf(5., 40., 16, 1.0)
+    me.device = torch.device("cpu")
+    sensed = np.zeros((3, 6, 10), np.float32)
+    sensed[0] = 5.0 + 30.0 * torch.rand(6, 10, generator=g).numpy()
+    sensed[0, 1, 2:5] = 0.0                                    # no return
+    sensed[1] = 255.0 * torch.rand(6, 10, generator=g).numpy()
+    sensed[2] = 0.5 + 2.0 * torch.rand(6, 10, generator=g).numpy()
+    peak = 0.1 + 0.3 * torch.rand(6, 10, generator=g).numpy()
+    true_const = LC.LightCurtain.gen_lc_dpv_true(me, torch.tensor(sensed), 2.0)       # the method takes a tensor
+    true_peak = LC.LightCurtain.gen_lc_dpv_true(me, torch.tensor(sensed), 3.0, peak_img=peak.copy())
+    save("aux", iw_img=img, iw_depth=depth, iw_K=Kb, iw_pose6=pose6, iw_pose44=pose44,
+         iw_euler_bilinear=w_eb, iw_euler_bilinear_valid=v_eb, iw_euler_nearest_border=w_en,
+         iw_quat_border=w_qb, iw_mat=w_m, iw_mat_valid=v_m,
+         corr_x1=x1, corr_x2=x2, corr_native_d3=corr3,
+         rmse_truth=ft, rmse_pred=fp, rmse_d=d, rmse=rm,
+         true_d=me.d_candi, true_sensed=sensed, true_peak_img=peak, true_dpv_const=true_const, true_dpv_peak=true_peak)
+
+
 def case_lcsim_fixture():
     """The one known-answer vector the reference ships for lcsim: example/dpv.npy['angles']."""
     d = np.load("/root/reference/external/lcsim/python/example/dpv.npy", allow_pickle=True, encoding="bytes")[()]
@@ -206,3 +263,4 @@ if __name__ == "__main__":
     case_likelihood()
     case_light_curtain()
     case_lcsim_fixture()
+    case_aux()

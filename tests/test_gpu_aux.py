@@ -1,0 +1,160 @@
+"""GPU parity for the callers either side of the fused path, through the C ABI,
+against the golden vectors of the unmodified reference (tests/golden/aux.npz, likelihood.npz) and the CPU oracle.
+
+Tolerances: 1e-4 relative fp32 (north_star).  The warped images are compared with an absolute term of
+1e-4 * max|img|: a bilinear tap weight moves by ~1e-5 when the sampling coordinate (up to ~10^3 px, fp32)
+is rounded differently by the two matrix products.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import aux_oracle as A
+from oracle import dpv_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+RTOL = 1e-4
+
+
+def load(name):
+    return {k: v for k, v in np.load(os.path.join(G, name + ".npz")).items()}
+
+
+def cu(a):
+    return torch.as_tensor(np.asarray(a)).cuda()
+
+
+def close(a, b, rtol=RTOL, atol=1e-6, what=""):
+    a = a.detach().cpu().numpy() if torch.is_tensor(a) else np.asarray(a)
+    b = b.detach().cpu().numpy() if torch.is_tensor(b) else np.asarray(b)
+    np.testing.assert_allclose(a, b, rtol=rtol, atol=atol, equal_nan=True, err_msg=what)
+
+
+def test_gen_dpv_withmask_and_intensity_model_golden():
+    from depthestimation_b200.utils import img_utils
+    g = load("likelihood")
+    d = g["d_candi"]
+    close(img_utils.gen_dpv_withmask(cu(g["dmaps"]), cu(g["masks"]), d, 0.3), g["truth_dpv"], what="gen_dpv_withmask")
+    z, x = cu(g["z"]).unsqueeze(-1), cu(g["x"]).unsqueeze(-1)
+    sg = (torch.sqrt(cu(g["var"])) + 0.1).unsqueeze(-1)
+    m, l = img_utils.lc_intensities_to_dist(d, z, x, sg, 0.1, torch.ones_like(z) * 0.2)
+    assert m.shape == g["true_mean"].shape
+    close(m, g["true_mean"], what="mean intensities")
+    close(l, g["true_lik"], what="normalised likelihood")
+    m2, l2 = img_utils.lc_intensities_to_dist(d, z, x, sg, 0.1, 0.2)           # scalar peak
+    close(l2, g["true_lik"])
+
+
+def test_gen_lc_dpv_true_golden():
+    from depthestimation_b200.lc.light_curtain import LightCurtain
+    g = load("aux")
+    lc = LightCurtain.__new__(LightCurtain)
+    lc.d_candi = g["true_d"]
+    lc.device = torch.device("cuda", 0)
+    close(lc.gen_lc_dpv_true(g["true_sensed"], 2.0), g["true_dpv_const"], what="const peak")
+    close(lc.gen_lc_dpv_true(g["true_sensed"], 3.0, peak_img=g["true_peak_img"]), g["true_dpv_peak"], what="peak img")
+    # a pixel with no return (depth 0 -> sigma 0): uniform, or NaN only if a bin sits exactly on 0
+    out = lc.gen_lc_dpv_true(g["true_sensed"], 2.0)
+    np.testing.assert_allclose(out[:, 1, 3].cpu().numpy(), 1.0 / len(g["true_d"]), rtol=1e-5)
+
+
+def test_inverse_warp_golden():
+    from depthestimation_b200.utils import inverse_warp as IW
+    g = load("aux")
+    img, depth, K, p6, p44 = (cu(g[k]) for k in ("iw_img", "iw_depth", "iw_K", "iw_pose6", "iw_pose44"))
+    atol = 1e-4 * float(np.abs(g["iw_img"]).max())
+    out, valid = IW.inverse_warp(img, depth, p6, K)
+    close(out, g["iw_euler_bilinear"], atol=atol, what="euler bilinear zeros")
+    assert valid.dtype == torch.bool
+    assert (valid.cpu().numpy() != g["iw_euler_bilinear_valid"]).mean() < 0.005      # |g| == 1 exactly is knife-edge
+    close(IW.inverse_warp(img, depth, p6, K, rotation_mode="quat", padding_mode="border")[0], g["iw_quat_border"],
+          atol=atol, what="quat border")
+    out, valid = IW.inverse_warp(img, depth, p44, K)
+    close(out, g["iw_mat"], atol=atol, what="4x4 pose")
+    # nearest: a sampling coordinate within 1e-4 px of .5 may round to the other texel; everything else is exact
+    near = IW.inverse_warp(img, depth, p6, K, mode="nearest", padding_mode="border")[0].cpu().numpy()
+    assert (np.abs(near - g["iw_euler_nearest_border"]) > 1e-6).mean() < 0.005
+    close(IW.pose_vec2mat_full(p6), g["iw_pose44"], what="pose_vec2mat_full")
+    with pytest.raises(AssertionError):
+        IW.inverse_warp(img, depth.unsqueeze(1), p6, K)
+
+
+def test_inverse_warp_full_size_against_oracle_and_identity():
+    from depthestimation_b200.utils import inverse_warp as IW
+    gen = torch.Generator().manual_seed(3)
+    B, C, H, W = 2, 3, 256, 768
+    img = torch.randn(B, C, H, W, generator=gen)
+    depth = 5.0 + 30.0 * torch.rand(B, H, W, generator=gen)
+    K = torch.tensor([[[455.0, 0, 384.0], [0, 533.0, 128.0], [0, 0, 1]]]).repeat(B, 1, 1)
+    pose = torch.tensor([[0.2, -0.05, 0.3, 0.01, -0.02, 0.005], [0.0, 0.0, 0.0, 0.0, 0.0, 0.0]])
+    ref, rvalid = A.inverse_warp(img, depth, A.pose_matrix(pose), K)
+    out, valid = IW.inverse_warp(img.cuda(), depth.cuda(), pose.cuda(), K.cuda())
+    d = (out.cpu() - ref).abs()
+    assert float(d.max()) < 2e-2 and float((d > 1e-3).float().mean()) < 1e-3, (float(d.max()), float(d.mean()))
+    assert float((valid.cpu() != rvalid).float().mean()) < 1e-3
+    # identity pose with align_corners=False sampling of a (w-1)-normalised grid: interior equals a fixed
+    # resampling of the image itself, so warping twice the same way is deterministic and finite
+    assert torch.isfinite(out).all()
+
+
+def test_correlation_golden_and_general():
+    from depthestimation_b200.models.correlation import Correlation, CorrelationNative
+    g = load("aux")
+    x1, x2 = cu(g["corr_x1"]), cu(g["corr_x2"])
+    close(CorrelationNative(max_displacement=3)(x1, x2), g["corr_native_d3"], what="native twin")
+    close(Correlation(pad_size=3, kernel_size=1, max_displacement=3, stride1=1, stride2=1)(x1, x2),
+          g["corr_native_d3"], what="package layer at the twin's setting")
+    gen = torch.Generator().manual_seed(5)
+    a = torch.randn(2, 16, 24, 40, generator=gen)
+    b = torch.randn(2, 16, 24, 40, generator=gen)
+    for pad, k, md, s1, s2 in [(4, 1, 4, 1, 1), (20, 1, 20, 1, 2), (4, 3, 4, 2, 2), (6, 3, 4, 1, 1)]:
+        out = Correlation(pad, k, md, s1, s2)(a.cuda(), b.cuda())
+        ref = A.correlation(a.numpy(), b.numpy(), pad, k, md, s1, s2)
+        assert tuple(out.shape) == ref.shape
+        close(out, ref, atol=2e-6, what="correlation pad=%d k=%d md=%d s=%d/%d" % (pad, k, md, s1, s2))
+    with pytest.raises(Exception):
+        Correlation(0, 1, 20, 1, 1)(a.cuda(), b.cuda())             # displacement larger than the frame: empty output
+    with pytest.raises(NotImplementedError):
+        Correlation(4, 1, 4, 1, 1)(a.cuda().requires_grad_(), b.cuda())
+
+
+def test_depth_error_and_eval_errors():
+    from depthestimation_b200.utils import img_utils
+    gen = torch.Generator().manual_seed(9)
+    H, W = 256, 768
+    gt = 5.0 + 30.0 * torch.rand(3, H, W, generator=gen)
+    gt[torch.rand(3, H, W, generator=gen) < 0.3] = 0.0              # KITTI-style sparse ground truth
+    pred = (gt + torch.randn(3, H, W, generator=gen)).clamp(min=0.5)
+    pred[gt == 0] = 7.0
+    got = img_utils.depth_error(pred.cuda(), gt.cuda())
+    assert got.shape == (3, 9)
+    for i in range(3):
+        ref = A.depth_errors(pred[i].numpy(), gt[i].numpy())
+        # the reference accumulates 4e5 terms sequentially in fp32 (relative error ~1e-5); the kernel sums in fp64
+        np.testing.assert_allclose(got[i].cpu().numpy(), ref, rtol=1e-4)
+    one = img_utils.depth_error(pred[0].cuda(), gt[0].cuda())
+    assert one.shape == (9,) and torch.equal(one, got[0])
+    res = img_utils.eval_errors([got[i] for i in range(3)])
+    assert list(res) == list(img_utils.ERROR_NAMES)
+    np.testing.assert_allclose(res["mae"][0], float(got[:, 0].mean()), rtol=1e-6)
+    assert res["mae"][1] == min(1.0, float(got[:, 0].min())) and res["mae"][2] == float(got[:, 0].max())
+    with pytest.raises(RuntimeError):
+        img_utils.depth_error(pred[0].cuda(), torch.zeros(H, W).cuda())
+
+
+def test_compute_unc_rmse_and_field():
+    from depthestimation_b200.utils import img_utils
+    g = load("aux")
+    got = img_utils.compute_unc_rmse(cu(g["rmse_truth"]), cu(g["rmse_pred"]), g["rmse_d"])
+    close(got, g["rmse"], what="compute_unc_rmse")
+    # compute_unc_field = two gen_ufield calls (truth: probabilities + mask, prediction: log-probabilities)
+    u = load("dpv_utils")
+    logp, K, d = cu(u["logp"]), cu(u["K"]), u["d_candi"]
+    cfg = "kitti"
+    ft, fp, _ = img_utils.compute_unc_field(logp, torch.exp(logp), d, K.unsqueeze(0), cu(u["mask"]), cfg)
+    close(ft, u["uf_masked"], atol=1e-5, what="truth field")
+    close(fp, u["uf_kitti"], atol=1e-5, what="predicted field")

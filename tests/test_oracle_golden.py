@@ -108,3 +108,53 @@ def test_light_curtain_python_half():
         close(lik, g["lik%d" % i])
     fused = LO.lc_loop(T(g["logp"]), depth, lc, g["Kup"], O.uf_params("kitti"), 3, [0.5], 2, 5)
     close(fused, g["fused"], rtol=1e-6, atol=1e-6)
+
+
+def real_sensor_likelihood(d_candi, sensed, std_div, peak=None):
+    """gen_lc_dpv_true (lc/light_curtain.py:1106-1125) on top of the oracle's intensity model."""
+    s = T(sensed)
+    mask = (s[0] > 0).float()
+    pk = torch.ones(s[0].shape).unsqueeze(-1) * 0.2 if peak is None else T(peak).float().unsqueeze(-1)
+    _, lik = O.intensity_model_likelihood(T(d_candi).float(), s[0].unsqueeze(-1), (s[1] * mask / 255.).unsqueeze(-1),
+                                          (s[2] * mask / std_div).unsqueeze(-1), 0.1, pk)
+    return lik.permute(2, 0, 1)
+
+
+def test_aux_rows_against_reference():
+    from oracle import aux_oracle as A
+    g = load("aux")
+    img, depth, K = T(g["iw_img"]), T(g["iw_depth"]), T(g["iw_K"])
+    pm = A.pose_matrix(T(g["iw_pose6"]), "euler")
+    close(pm, g["iw_pose44"][:, :3, :])
+    out, valid = A.inverse_warp(img, depth, pm, K)
+    close(out, g["iw_euler_bilinear"])
+    assert np.array_equal(valid.numpy(), g["iw_euler_bilinear_valid"])
+    close(A.inverse_warp(img, depth, pm, K, "nearest", "border")[0], g["iw_euler_nearest_border"])
+    close(A.inverse_warp(img, depth, A.pose_matrix(T(g["iw_pose6"]), "quat"), K, "bilinear", "border")[0],
+          g["iw_quat_border"])
+    out, valid = A.inverse_warp(img, depth, T(g["iw_pose44"])[:, :3, :], K)
+    close(out, g["iw_mat"])
+    assert np.array_equal(valid.numpy(), g["iw_mat_valid"])
+    # correlation: the general restatement at (pad 3, kernel 1, displacement 3, strides 1) is the native twin
+    close(A.correlation(g["corr_x1"], g["corr_x2"], 3, 1, 3, 1, 1), g["corr_native_d3"], rtol=1e-5, atol=1e-6)
+    close(A.unc_rmse(T(g["rmse_truth"]), T(g["rmse_pred"]), g["rmse_d"]), g["rmse"])
+    close(real_sensor_likelihood(g["true_d"], g["true_sensed"], 2.0), g["true_dpv_const"], rtol=1e-5)
+    close(real_sensor_likelihood(g["true_d"], g["true_sensed"], 3.0, g["true_peak_img"]), g["true_dpv_peak"], rtol=1e-5)
+
+
+def test_depth_errors_restatement_properties():
+    """depthError has no golden vector in the reference (parity unpinned, see oracle/aux_oracle.py): check the
+    restatement on hand-computable cases."""
+    from oracle import aux_oracle as A
+    gt = np.array([[2.0, 4.0, 0.0], [8.0, 0.0, 1.0]], np.float32)
+    e = A.depth_errors(gt, gt)
+    assert np.all(e == 0)
+    pred = gt * 2
+    e = A.depth_errors(pred, gt)
+    valid = gt[gt > 0]
+    np.testing.assert_allclose(e[0], np.mean(valid), rtol=1e-6)                      # mae = mean(gt)
+    np.testing.assert_allclose(e[1], np.sqrt(np.mean(valid ** 2)), rtol=1e-6)        # rmse
+    np.testing.assert_allclose(e[4], np.log(2.0), rtol=1e-6)                         # log mae
+    np.testing.assert_allclose(e[6], 0.0, atol=1e-3)                                 # scale invariant
+    np.testing.assert_allclose(e[7], 1.0, rtol=1e-6)                                 # abs relative
+    np.testing.assert_allclose(e[8], 1.0, rtol=1e-6)                                 # squared relative: e^2 / gt^2
