@@ -196,9 +196,10 @@ extern "C" int lc_plan_prepare(const float* uf, int B, int D, int W, int R, cons
   size_t sm1 = (size_t)(D + 2 * R) * kPrepCols * sizeof(float);
   size_t sm2 = (size_t)R * kPrepCols * sizeof(float);
   DPV_REQUIRE(sm1 <= 200 * 1024, "lc_plan_prepare: D + 2R too large for shared memory");
-  if (sm1 > 48 * 1024)
+  // static shared memory of the kernels counts against the 48 KB default too: opt in with some margin
+  if (sm1 > 40 * 1024)
     DPV_CUDA(cudaFuncSetAttribute(plan_prep_columns_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
-  if (sm2 > 48 * 1024)
+  if (sm2 > 40 * 1024)
     DPV_CUDA(cudaFuncSetAttribute(plan_prep_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
   plan_prep_columns_kernel<<<grid, kPrepCols * kPrepWarps, sm1, st>>>(uf, D, W, R, field_pre);
   int rc = check_launch("lc_plan_prepare/columns");

@@ -35,6 +35,9 @@ WORKLOADS = {
                               spread_n=5, d_min=5., d_max=40., dataset="kitti", R=128, stereo=True),
     "tiny": dict(B=2, T=2, H=32, W=64, D=16, C=16, iterations=2, step=[0.5], spread_iter=2, spread_n=5,
                  d_min=5., d_max=40., dataset="kitti", R=32, hfov=16.0, vfov=10.0),
+    # C4's depth / range resolution (D = C = R = 128: four lanes per pixel, 48 KB of staging in plan_prepare) at test size
+    "tiny_d128": dict(B=1, T=2, H=32, W=64, D=128, C=128, iterations=2, step=[0.5], spread_iter=2, spread_n=5,
+                      d_min=5., d_max=40., dataset="kitti", R=128, hfov=16.0, vfov=10.0, stereo=True),
 }
 
 

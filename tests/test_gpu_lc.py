@@ -182,11 +182,12 @@ def test_lc_process_golden_and_oracle_trace():
     assert torch.equal(both[0], one[0]) and torch.equal(both[1], one[0])
 
 
-def test_pipeline_tiny_matches_oracle_step():
+@pytest.mark.parametrize("workload", ["tiny", "tiny_d128"])
+def test_pipeline_tiny_matches_oracle_step(workload):
     """The whole hot path (DpvLcPipeline.step, what bench.py times) against the CPU oracle's step."""
     import bench
     from depthestimation_b200.pipeline import DpvLcPipeline, synthetic_batch
-    host, meta = synthetic_batch("tiny", seed=3)
+    host, meta = synthetic_batch(workload, seed=3)
     pipe = DpvLcPipeline(meta, torch.device("cuda", 0))
     out = pipe.step({k: v.cuda() for k, v in host.items()})
     exp = bench.oracle_step(host, meta)
