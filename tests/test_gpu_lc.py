@@ -95,6 +95,31 @@ def test_planner_bit_exact_on_reference_fixture():
             pl.get_design_points(np.zeros((5, 5), np.float32))
 
 
+@pytest.mark.parametrize("R", [37, 100, 160, 250])
+def test_planner_bit_exact_other_range_counts(R):
+    """Range counts that are not a multiple of 4 / exceed one 128-entry chunk (second kernel instance), with
+    heavily tied maps: DP indices identical to the oracle planner."""
+    from depthestimation_b200 import lcsim
+    g = load("lcsim_dpv_fixture")
+    W, H = 96, 64
+    K = g["intrinsics"].copy()
+    K[0, 2], K[1, 2] = W / 2, H / 2
+    dev, odev = _devices(K, W, H, 1.0e-4)
+    r_candi = np.linspace(5.0, 40.0, R).astype(np.float32)
+    pl, opl = lcsim.PlannerRT(dev, r_candi, W), olcsim.PlannerRT(odev, r_candi, W)
+    assert pl.edge_count() == opl.edge_count()
+    gen = np.random.default_rng(R)
+    fields = [gen.random((R, W), dtype=np.float32), np.round(gen.random((R, W)) * 2).astype(np.float32) / 2,
+              (gen.random((R, W)) > 0.9).astype(np.float32)]
+    ks, xz, counts = pl.solve(cu(np.stack(fields)))
+    for i, f in enumerate(fields):
+        exz, eks = opl.get_design_points(f, return_indices=True)
+        n = int(counts[i])
+        assert n == len(eks)
+        np.testing.assert_array_equal(ks[i, :n].cpu().numpy(), eks)
+        np.testing.assert_array_equal(xz[i, :n].cpu().numpy(), exz)
+
+
 def test_curtain_image_bit_exact():
     """LCDevice.get_return: design points, plane coefficients, surface, thickness and the quantised
     intensity are bit-identical to the oracle simulator (noise off and with an explicit noise image)."""
