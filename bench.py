@@ -167,14 +167,15 @@ def run_b200(args):
         start.record(main)
         for st in streams:
             st.wait_event(start)
+        coll = sharding.FrameOutputCollector(n, world)
         for i in range(n):
             with torch.cuda.stream(streams[i % S]):
-                out = pipes[i % S].step(x)
-                sharding.gather_frame_outputs(out, world)
+                coll.add(pipes[i % S].step(x))
         for st in streams:
             done = torch.cuda.Event()
             done.record(st)
             main.wait_event(done)
+        coll.finish()                                   # the one exchange of the path: all ranks' depth maps (NCCL)
 
     # ---- value: inputs resident in HBM --------------------------------------------------------
     run_steps(max(args.warmup, S))
@@ -273,6 +274,7 @@ def run_e2e(args, pipes, streams, host, x, dev, world, B, keys, sync, sharding):
         start.record(main)
         for st in streams:
             st.wait_event(start)
+        coll = sharding.FrameOutputCollector(n, world)
         for i in range(n):
             sl = i % S
             with torch.cuda.stream(streams[sl]):
@@ -281,10 +283,15 @@ def run_e2e(args, pipes, streams, host, x, dev, world, B, keys, sync, sharding):
                 xin = dict(x)
                 xin.update(bufs[sl])
                 out = pipes[sl].step(xin)
-                sharding.gather_frame_outputs(out, world)
+                coll.add(out)
                 for k in res_host[sl]:
                     if k in out:
                         res_host[sl][k].copy_(out[k], non_blocking=True)
+        for st in streams:
+            done = torch.cuda.Event()
+            done.record(st)
+            main.wait_event(done)
+        coll.finish()
         torch.cuda.synchronize(dev)
 
     loop(max(args.warmup, S))

@@ -45,3 +45,37 @@ def gather_frame_outputs(out, world, keys=("depth", "depth_lc")):
             dist.all_gather_into_tensor(full, t)
             res[k] = full
     return res
+
+
+class FrameOutputCollector:
+    """Keeps the per-frame result maps of the steps a rank runs and exchanges them once at the end
+    (north_star: "a single NCCL gather at the end"), so no collective sits between the steps of the path."""
+
+    def __init__(self, n_steps, world, keys=("depth", "depth_lc")):
+        self.n_steps, self.world, self.keys = n_steps, world, keys
+        self.buf = {}
+        self.count = 0
+
+    def add(self, out):
+        """Copies this step's maps into the rank-local buffer (on the current stream)."""
+        i = self.count % self.n_steps
+        for k in self.keys:
+            t = out.get(k)
+            if t is None:
+                continue
+            if k not in self.buf:
+                self.buf[k] = torch.empty((self.n_steps,) + tuple(t.shape), device=t.device, dtype=t.dtype)
+            self.buf[k][i].copy_(t, non_blocking=True)
+        self.count += 1
+
+    def finish(self):
+        """-> {key: [world, n_steps, B, H, W]} on every rank (all_gather over NVLink); rank-local view if world = 1."""
+        res = {}
+        for k, t in self.buf.items():
+            if self.world <= 1:
+                res[k] = t.unsqueeze(0)
+                continue
+            full = torch.empty((self.world * t.shape[0],) + tuple(t.shape[1:]), device=t.device, dtype=t.dtype)
+            dist.all_gather_into_tensor(full, t)                       # concatenated along dim 0 (gloo needs this form)
+            res[k] = full.view((self.world,) + tuple(t.shape))
+        return res
