@@ -39,8 +39,9 @@ SIGNATURES = {
     "dpv_resample_depth": (c_int, [c_fp, c_int, c_int, c_int, c_int, c_int, c_int, c_fp, c_vp]),
     "dpv_bayes_fuse": (c_int, [c_fp, c_fp, c_int, c_int, c_int, c_int, c_int, c_fp, c_int, c_int, c_fp, c_fp,
                                c_vp]),
+    "dpv_ufield_scratch_bytes": (ctypes.c_size_t, [c_int, c_int, c_int]),
     "dpv_ufield": (c_int, [c_fp, c_fp, c_fp, c_int, c_int, c_int, c_int, c_fp, c_fp,
-                           ctypes.POINTER(DpvUfieldParams), c_fp, c_fp, c_vp]),
+                           ctypes.POINTER(DpvUfieldParams), c_fp, c_fp, c_vp, ctypes.c_size_t, c_vp]),
     "lc_plan_prepare": (c_int, [c_fp, c_int, c_int, c_int, c_int, c_fp, c_fp, c_int, c_fp, c_ip, c_fp, c_vp]),
     "lc_device_create": (c_int, [c_int, c_int, c_fp, c_fp, c_f, c_f, c_f, c_f, c_f, c_int, c_f,
                                  ctypes.POINTER(c_vp)]),

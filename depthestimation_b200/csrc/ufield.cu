@@ -3,8 +3,14 @@
 // The reference makes ~6 full passes over the 50 MB volume (2 nearest grid_samples, 2 expectations,
 // exp * mask, sum).  Here the row-shifted grid_samples collapse into integer index functions
 // (mask_back(y,x) is a pure function of mean[y',x'] at one source pixel), the
-// expectation comes from the kernel that last wrote the DPV, and only the rows of a column that are
-// inside the road band are read from the volume: one block = 32 columns x all D planes.
+// expectation comes from the kernel that last wrote the DPV, and only the pixels inside the road band are
+// read from the volume.  Three small grids instead of one long-running block per 32 columns (which was bound
+// by serial DRAM latency: 113 us for 19 MB of traffic):
+//   colmin (quash modes only)  per-column minimum of the masked depth
+//   mask                       forward count per column, inverse-shifted band mask as one 32-bit word per
+//                              (row, 32-column group), depth_zero
+//   sum                        one warp per (depth plane, 32 columns): walks the non-empty rows in ascending
+//                              order, eight loads in flight, and divides by the column count.
 #include "common.cuh"
 
 namespace dpv {
@@ -72,85 +78,84 @@ __device__ __forceinline__ void atomic_min_pos(float* addr, float v) {
 
 constexpr int kUfCols = 32;
 constexpr int kUfWarps = 8;
+constexpr int kUfRows = 64;          // rows per block in the per-pixel kernels
 
-__global__ void __launch_bounds__(kUfCols* kUfWarps)
-ufield_kernel(UfArgs a) {
-  extern __shared__ unsigned char smem_raw[];
-  const int H = a.H, W = a.W, D = a.D;
-  unsigned char* mb = smem_raw;                                   // [H][32] mask_back
-  int* rows = reinterpret_cast<int*>(smem_raw + (size_t)H * kUfCols);   // active row list [H]
-  __shared__ int count[kUfCols];
-  __shared__ float cmin_x[kUfCols], cmin_c[kUfCols];
-  __shared__ int nrows;
-  __shared__ float fill_s;
-
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int b = blockIdx.y;
-  const int x = blockIdx.x * kUfCols + lane;
-  const bool xin = x < W;
-  if (threadIdx.x == 0) {
-    nrows = 0;
-    float s = 0.f;
-    if (a.prm.bv_log)
-      for (int d = 0; d < D; d++) s += a.d_candi[d];              // zero-filled log-DPV => p = 1 in every bin
-    fill_s = s;
-  }
-  if (threadIdx.x < kUfCols) {
-    count[threadIdx.x] = 0;
-    cmin_x[threadIdx.x] = 3.0e38f;
-    cmin_c[threadIdx.x] = 3.0e38f;
-  }
-  __syncthreads();
-
+__device__ __forceinline__ UfCtx make_ctx(const UfArgs& a, int b, float fill) {
   UfCtx c;
-  c.mean = a.mean + (size_t)b * H * W;
-  c.mask = a.mask ? a.mask + (size_t)b * H * W : nullptr;
-  c.H = H; c.W = W; c.pshift = a.prm.pshift;
+  c.mean = a.mean + (size_t)b * a.H * a.W;
+  c.mask = a.mask ? a.mask + (size_t)b * a.H * a.W : nullptr;
+  c.H = a.H; c.W = a.W; c.pshift = a.prm.pshift;
   const float* K = a.K_up + b * 9;
   c.fy = K[4]; c.cy = K[5];
   c.ystart = a.prm.ystart; c.yend = a.prm.yend;
   c.maxd1 = a.prm.maxd - 1.f; c.mind = a.prm.mind;
-  c.fill = fill_s;
+  c.fill = fill;
+  return c;
+}
 
+// expectation of a zero-filled log-DPV (p = 1 in every bin): what an out-of-bounds shifted pixel sees
+__device__ __forceinline__ float zero_fill_depth(const UfArgs& a) {
+  float s = 0.f;
+  if (a.prm.bv_log)
+    for (int d = 0; d < a.D; d++) s += a.d_candi[d];
+  return s;
+}
+
+// masked depth with empty pixels pushed to 1000 (img_utils.py:533-535)
+__device__ __forceinline__ float quash_key(float z, float m) {
+  const float cl = z * m;
+  return cl == 0.f ? 1000.f : cl;
+}
+
+// grid (column groups, row blocks, B): cmin[b,x] = min_y quash_key   (img_utils.py:532-536)
+__global__ void __launch_bounds__(kUfCols* kUfWarps)
+ufield_colmin_kernel(UfArgs a, float* __restrict__ cmin) {
+  __shared__ float s_min[kUfCols];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, b = blockIdx.z;
+  const int x = blockIdx.x * kUfCols + lane;
+  if (threadIdx.x < kUfCols) s_min[threadIdx.x] = 3.0e38f;
+  __syncthreads();
+  const UfCtx c = make_ctx(a, b, zero_fill_depth(a));
+  if (x < a.W) {
+    float mx = 3.0e38f;
+    for (int y = blockIdx.y * kUfRows + warp; y < min(a.H, (int)(blockIdx.y + 1) * kUfRows); y += kUfWarps) {
+      float z;
+      const float m = band_mask(c, y, x, &z);
+      mx = fminf(mx, quash_key(z, m));
+    }
+    atomic_min_pos(&s_min[lane], mx);
+  }
+  __syncthreads();
+  if (threadIdx.x < kUfCols && x < a.W) atomic_min_pos(&cmin[(size_t)b * a.W + x], s_min[lane]);
+}
+
+// grid (column groups, row blocks, B): forward count, mask_back words, depth_zero
+__global__ void __launch_bounds__(kUfCols* kUfWarps)
+ufield_mask_kernel(UfArgs a, const float* __restrict__ cmin, unsigned* __restrict__ words, int* __restrict__ count) {
+  __shared__ int s_cnt[kUfCols];
+  const int H = a.H, W = a.W;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, b = blockIdx.z;
+  const int x = blockIdx.x * kUfCols + lane;
+  const bool xin = x < W;
+  if (threadIdx.x < kUfCols) s_cnt[threadIdx.x] = 0;
+  __syncthreads();
+  const UfCtx c = make_ctx(a, b, zero_fill_depth(a));
   // column that mask_back(.,x) looks at (inverse shift samples the forward mask at (ri[y], cs[x]))
   const int xc = !xin ? -1 : (c.pshift != 0 ? nearest_src(x, W, 0.f) : x);
-
-  if (a.prm.quash) {                                              // img_utils.py:532-539
-    float mx = 3.0e38f, mc = 3.0e38f;
-    for (int r = warp; r < H; r += kUfWarps) {
-      if (xin) {
-        float z;
-        float m = band_mask(c, r, x, &z);
-        float cl = z * m;
-        if (cl == 0.f) cl = 1000.f;
-        mx = fminf(mx, cl);
-      }
-      if (xc >= 0 && xc != x) {
-        float z;
-        float m = band_mask(c, r, xc, &z);
-        float cl = z * m;
-        if (cl == 0.f) cl = 1000.f;
-        mc = fminf(mc, cl);
-      }
-    }
-    if (xin) atomic_min_pos(&cmin_x[lane], mx);
-    if (xc >= 0 && xc != x) atomic_min_pos(&cmin_c[lane], mc);
-    __syncthreads();
-    if (xc == x) cmin_c[lane] = cmin_x[lane];
-    __syncthreads();
+  float qx = 0.f, qc = 0.f;
+  if (a.prm.quash) {
+    if (xin) qx = cmin[(size_t)b * W + x];
+    if (xc >= 0) qc = cmin[(size_t)b * W + xc];
   }
-
-  // phase 1: forward count of column x, mask_back of column x, list of rows with any band pixel
   int cnt = 0;
-  for (int y = warp; y < H; y += kUfWarps) {
+  for (int y = blockIdx.y * kUfRows + warp; y < min(H, (int)(blockIdx.y + 1) * kUfRows); y += kUfWarps) {
     float mback = 0.f;
     if (xin) {
       float z;
       float m = band_mask(c, y, x, &z);
-      if (a.prm.quash) {
-        float cl = z * m;
-        if (cl == 0.f) cl = 1000.f;
-        m = m * ((cl > cmin_x[lane] - 1.0f && cl < cmin_x[lane] + 1.0f) ? 1.f : 0.f);
+      if (a.prm.quash) {                                          // img_utils.py:537-539
+        const float cl = quash_key(z, m);
+        m = m * ((cl > qx - 1.0f && cl < qx + 1.0f) ? 1.f : 0.f);
       }
       cnt += (m != 0.f);
       // img_utils.py:541-545: mask_back = grid_sample(mask, inverse shift, nearest)
@@ -160,84 +165,94 @@ ufield_kernel(UfArgs a) {
         float zz;
         float m2 = band_mask(c, ry, xc, &zz);
         if (a.prm.quash) {
-          float cl = zz * m2;
-          if (cl == 0.f) cl = 1000.f;
-          m2 = m2 * ((cl > cmin_c[lane] - 1.0f && cl < cmin_c[lane] + 1.0f) ? 1.f : 0.f);
+          const float cl = quash_key(zz, m2);
+          m2 = m2 * ((cl > qc - 1.0f && cl < qc + 1.0f) ? 1.f : 0.f);
         }
         mback = m2;
       }
       if (a.depth_zero) a.depth_zero[((size_t)b * H + y) * W + x] = c.mean[(size_t)y * W + x] * mback;
     }
-    // mask values are 0/1 unless a fractional user mask is given; keep the float for that case
-    mb[y * kUfCols + lane] = (mback != 0.f) ? 1 : 0;
-    unsigned any = __ballot_sync(0xffffffffu, mback != 0.f);
-    if (lane == 0 && any) rows[atomicAdd(&nrows, 1)] = y;
+    // mask values are 0/1 (a fractional user mask only switches pixels on or off, as before)
+    const unsigned any = __ballot_sync(0xffffffffu, mback != 0.f);
+    if (lane == 0) words[((size_t)b * gridDim.x + blockIdx.x) * H + y] = any;
   }
-  if (cnt) atomicAdd(&count[lane], cnt);
+  if (cnt) atomicAdd(&s_cnt[lane], cnt);
   __syncthreads();
-  // deterministic row order: sort the (short) active list ascending — simple odd-even by one warp
-  const int n = nrows;
-  if (warp == 0) {
-    for (int pass = 0; pass < n; pass++) {
-      for (int i = 2 * lane + (pass & 1); i + 1 < n; i += 64) {
-        int r0 = rows[i], r1 = rows[i + 1];
-        if (r0 > r1) { rows[i] = r1; rows[i + 1] = r0; }
-      }
-      __syncwarp();
-    }
-  }
-  __syncthreads();
+  if (threadIdx.x < kUfCols && xin && s_cnt[lane]) atomicAdd(&count[(size_t)b * W + x], s_cnt[lane]);
+}
 
-  // phase 2: UF[d,x] = sum_y p[d,y,x] * mask_back[y,x] / count[x]   (img_utils.py:551-557)
-  const float denom = (float)count[lane];
-  const size_t HW = (size_t)H * W;
-  for (int d = warp; d < D; d += kUfWarps) {
-    const float* plane = a.dpv + ((size_t)b * D + d) * HW + x;
-    float acc = 0.f;
-    int i = 0;
-    for (; i + 4 <= n; i += 4) {
-      int y0 = rows[i], y1 = rows[i + 1], y2 = rows[i + 2], y3 = rows[i + 3];
-      bool m0 = xin && mb[y0 * kUfCols + lane], m1 = xin && mb[y1 * kUfCols + lane];
-      bool m2 = xin && mb[y2 * kUfCols + lane], m3 = xin && mb[y3 * kUfCols + lane];
-      float v0 = m0 ? __ldg(plane + (size_t)y0 * W) : 0.f;
-      float v1 = m1 ? __ldg(plane + (size_t)y1 * W) : 0.f;
-      float v2 = m2 ? __ldg(plane + (size_t)y2 * W) : 0.f;
-      float v3 = m3 ? __ldg(plane + (size_t)y3 * W) : 0.f;
-      if (a.prm.bv_log) { v0 = expf(v0); v1 = expf(v1); v2 = expf(v2); v3 = expf(v3); }
-      if (m0) acc += v0;
-      if (m1) acc += v1;
-      if (m2) acc += v2;
-      if (m3) acc += v3;
-    }
-    for (; i < n; i++) {
-      int y0 = rows[i];
-      if (xin && mb[y0 * kUfCols + lane]) {
-        float v0 = __ldg(plane + (size_t)y0 * W);
-        acc += a.prm.bv_log ? expf(v0) : v0;
+// grid (column groups, ceil(D / warps), B): UF[d,x] = sum_y p[d,y,x] * mask_back[y,x] / count[x]  (:551-557)
+__global__ void __launch_bounds__(kUfCols* kUfWarps)
+ufield_sum_kernel(UfArgs a, const unsigned* __restrict__ words, const int* __restrict__ count) {
+  const int H = a.H, W = a.W, D = a.D;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, b = blockIdx.z;
+  const int d = blockIdx.y * kUfWarps + warp;
+  const int x = blockIdx.x * kUfCols + lane;
+  if (d >= D) return;
+  const unsigned* wrow = words + ((size_t)b * gridDim.x + blockIdx.x) * H;
+  const float* plane = a.dpv + ((size_t)b * D + d) * (size_t)H * W + x;
+  const unsigned full = 0xffffffffu;
+  float acc = 0.f;
+  for (int y0 = 0; y0 < H; y0 += 32) {
+    const unsigned myw = (y0 + lane < H) ? wrow[y0 + lane] : 0u;
+    unsigned act = __ballot_sync(full, myw != 0u);
+    while (act) {                                                // rows with a band pixel, ascending, 8 at a time
+      float v[8];
+      bool on[8];
+#pragma unroll
+      for (int k = 0; k < 8; k++) {
+        const int r = act ? (__ffs(act) - 1) : 0;
+        const unsigned w = __shfl_sync(full, myw, r);
+        on[k] = act != 0u && ((w >> lane) & 1u);
+        act &= act - 1u;                                          // 0 stays 0
+        v[k] = on[k] ? __ldg(plane + (size_t)(y0 + r) * W) : 0.f;
       }
+#pragma unroll
+      for (int k = 0; k < 8; k++)
+        if (on[k]) acc += a.prm.bv_log ? expf(v[k]) : v[k];
     }
-    if (xin) a.uf[((size_t)b * D + d) * W + x] = acc / denom;
   }
+  if (x < W) a.uf[((size_t)b * D + d) * W + x] = acc / (float)count[(size_t)b * W + x];
 }
 
 }  // namespace dpv
 
 using namespace dpv;
 
+extern "C" size_t dpv_ufield_scratch_bytes(int B, int H, int W) {
+  const size_t G = (size_t)(W + kUfCols - 1) / kUfCols;
+  return (size_t)B * G * H * sizeof(unsigned) + 2 * (size_t)B * W * sizeof(float);
+}
+
 extern "C" int dpv_ufield(const float* dpv_, const float* mean, const float* mask, int B, int D, int H, int W,
                           const float* d_candi, const float* K_up, const DpvUfieldParams* prm, float* uf,
-                          float* depth_zero, void* stream) {
-  DPV_REQUIRE(dpv_ && mean && d_candi && K_up && prm && uf, "dpv_ufield: null pointer");
+                          float* depth_zero, void* scratch, size_t scratch_bytes, void* stream) {
+  DPV_REQUIRE(dpv_ && mean && d_candi && K_up && prm && uf && scratch, "dpv_ufield: null pointer");
   DPV_REQUIRE(B > 0 && D > 0 && H > 1 && W > 1, "dpv_ufield: bad shape");
-  DPV_REQUIRE(B <= 65535, "dpv_ufield: B too large");
+  DPV_REQUIRE(B <= 65535 && (D + kUfWarps - 1) / kUfWarps <= 65535, "dpv_ufield: B or D too large");
+  DPV_REQUIRE(scratch_bytes >= dpv_ufield_scratch_bytes(B, H, W), "dpv_ufield: scratch too small (%zu < %zu bytes)",
+              scratch_bytes, dpv_ufield_scratch_bytes(B, H, W));
+  DPV_REQUIRE(((uintptr_t)scratch & 3) == 0, "dpv_ufield: scratch must be 4-byte aligned");
   UfArgs a;
   a.dpv = dpv_; a.mean = mean; a.mask = mask; a.d_candi = d_candi; a.K_up = K_up; a.uf = uf;
   a.depth_zero = depth_zero; a.D = D; a.H = H; a.W = W; a.prm = *prm;
-  size_t smem = (size_t)H * kUfCols + (size_t)H * sizeof(int);
-  DPV_REQUIRE(smem <= 200 * 1024, "dpv_ufield: H=%d too large", H);
-  if (smem > 48 * 1024)
-    DPV_CUDA(cudaFuncSetAttribute(ufield_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dim3 grid((W + kUfCols - 1) / kUfCols, B);
-  ufield_kernel<<<grid, kUfCols * kUfWarps, smem, (cudaStream_t)stream>>>(a);
-  return check_launch("dpv_ufield");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int G = (W + kUfCols - 1) / kUfCols;
+  unsigned* words = reinterpret_cast<unsigned*>(scratch);
+  int* count = reinterpret_cast<int*>(words + (size_t)B * G * H);
+  float* cmin = reinterpret_cast<float*>(count + (size_t)B * W);
+  DPV_CUDA(cudaMemsetAsync(count, 0, (size_t)B * W * sizeof(int), st));
+  const dim3 gpix(G, (H + kUfRows - 1) / kUfRows, B);
+  int launches = 0;
+  if (a.prm.quash) {
+    DPV_CUDA(cudaMemsetAsync(cmin, 0x7f, (size_t)B * W * sizeof(float), st));     // 0x7f7f7f7f = 3.39e38
+    ufield_colmin_kernel<<<gpix, kUfCols * kUfWarps, 0, st>>>(a, cmin);
+    launches++;
+  }
+  ufield_mask_kernel<<<gpix, kUfCols * kUfWarps, 0, st>>>(a, cmin, words, count);
+  ufield_sum_kernel<<<dim3(G, (D + kUfWarps - 1) / kUfWarps, B), kUfCols * kUfWarps, 0, st>>>(a, words, count);
+  launches++;
+  const int rc = check_launch("dpv_ufield");
+  if (rc == DPV_OK) count_launch(launches);
+  return rc;
 }

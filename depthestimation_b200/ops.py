@@ -144,8 +144,10 @@ def ufield(dpv, mean, K_up, d_candi, params, bv_log=True, mask=None, want_depth=
                                int(bool(bv_log)))
     uf = out if out is not None else torch.empty(B, D, W, device=dev, dtype=torch.float32)
     dz = torch.empty(B, H, W, device=dev, dtype=torch.float32) if want_depth else None
+    nbytes = int(lib().dpv_ufield_scratch_bytes(B, H, W))
+    scratch = torch.empty(nbytes, device=dev, dtype=torch.uint8)      # caching allocator: no cudaMalloc per call
     check(lib().dpv_ufield(ptr(dpv), ptr(mean), ptr(mask), B, D, H, W, ptr(dc), ptr(K_up), ctypes.byref(prm),
-                           ptr(uf), ptr(dz), stream_ptr(dev)))
+                           ptr(uf), ptr(dz), scratch.data_ptr(), nbytes, stream_ptr(dev)))
     return uf, dz
 
 

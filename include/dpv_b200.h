@@ -14,6 +14,7 @@
 #ifndef DPV_B200_H_
 #define DPV_B200_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -93,9 +94,12 @@ typedef struct DpvUfieldParams {
   int quash;           /* img_utils.py:532-539 */
   int bv_log;
 } DpvUfieldParams;
+/* scratch: device memory of at least dpv_ufield_scratch_bytes(B,H,W) bytes, 4-byte aligned, owned by the caller
+ * (band-mask words, per-column counts and minima; contents are not needed after the call). */
+size_t dpv_ufield_scratch_bytes(int B, int H, int W);
 int dpv_ufield(const float* dpv, const float* mean, const float* mask, int B, int D, int H, int W,
                const float* d_candi, const float* K_up, const DpvUfieldParams* prm /*host*/, float* uf,
-               float* depth_zero, void* stream);
+               float* depth_zero, void* scratch, size_t scratch_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * (d2) Planner input.  lc/light_curtain.py:646-708 plan_default up to the planner calls
