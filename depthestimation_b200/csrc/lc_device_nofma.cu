@@ -260,8 +260,8 @@ int lc_device_hit_lut(const LcDevice* d, float* out) {
 // ---------------------------------------------------------------------------------------------
 namespace dpv {
 
-constexpr int kPlaneThreads = 256;
-constexpr int kPlaneCols = 128;     // columns per CTA (grid.y splits the image width)
+constexpr int kPlaneThreads = 512;
+constexpr int kPlaneCols = 64;      // columns per CTA (grid.y splits the image width): 4 per warp
 
 __device__ __forceinline__ float point_angle(float x, float z) {
   // -((atan2f(z, x) * 180 / M_PI) - 90) + 0 + 0   (dprocessor.cpp:528-531, 762)

@@ -10,6 +10,7 @@ namespace dpv {
 
 constexpr int kPrepCols = 32;
 constexpr int kPrepWarps = 4;
+constexpr int kWarpWarps = 32;      // plan_prep_warp_kernel: one row per warp and pass (short dependent chains)
 
 // ---------------------------------------------------------------------------------------------
 // P1 (column-local): side fix -> NaN columns -> bilinear row upsample D->R -> 5-tap depth mean ->
@@ -109,19 +110,21 @@ __device__ __forceinline__ float pow_like_torch(float x, float e) {
   return powf(x, e);
 }
 
-__global__ void __launch_bounds__(kPrepCols* kPrepWarps)
+__global__ void __launch_bounds__(kPrepCols* kWarpWarps)
 plan_prep_warp_kernel(const float* __restrict__ field_pre, const float* __restrict__ flow, int W, int R,
                       InvertSteps steps, float* __restrict__ umaps, int32_t* __restrict__ argmax_out) {
   extern __shared__ float sm[];
   float* fr = sm;                      // [R][32] warped field
   __shared__ int amax[kPrepCols];
+  __shared__ float pbest[kWarpWarps][kPrepCols];
+  __shared__ int pidx[kWarpWarps][kPrepCols];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int b = blockIdx.y;
   const int x = blockIdx.x * kPrepCols + lane;
   const bool xin = x < W;
   const float* f = field_pre + (size_t)b * R * W;
   const float ystep = (float)(2.0 / (double)(R - 1)), xstep = (float)(2.0 / (double)(W - 1));
-  for (int r = warp; r < R; r += kPrepWarps) {
+  for (int r = warp; r < R; r += kWarpWarps) {
     float val = 0.f;
     if (xin) {
       const float fx = flow[((size_t)r * W + x) * 2 + 0], fy = flow[((size_t)r * W + x) * 2 + 1];
@@ -144,12 +147,32 @@ plan_prep_warp_kernel(const float* __restrict__ field_pre, const float* __restri
     fr[r * kPrepCols + lane] = val;
   }
   __syncthreads();
-  if (warp == 0) {                     // torch.max(dim=0): first index of the maximum
-    float best = fr[lane];
-    int bi = 0;
-    for (int r = 1; r < R; r++) {
-      float v = fr[r * kPrepCols + lane];
-      if (v > best || (v != v && best == best)) { best = v; bi = r; }
+  // torch.max(dim=0): first index of the maximum (a NaN wins, the first NaN if several).  Every warp reduces its
+  // rows (ascending), warp 0 merges the partial results with the index as tie-break.
+  {
+    float best = -INFINITY;
+    int bi = 0x7fffffff;
+    bool have = false;
+    for (int r = warp; r < R; r += kWarpWarps) {
+      const float v = fr[r * kPrepCols + lane];
+      if (!have || v > best || (v != v && best == best)) { best = v; bi = r; have = true; }
+    }
+    pbest[warp][lane] = best;
+    pidx[warp][lane] = have ? bi : 0x7fffffff;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    float best = pbest[0][lane];
+    int bi = pidx[0][lane];
+    for (int k = 1; k < kWarpWarps; k++) {
+      const float v = pbest[k][lane];
+      const int vi = pidx[k][lane];
+      if (vi == 0x7fffffff) continue;
+      const bool vnan = v != v, bnan = best != best;
+      bool take;
+      if (vnan || bnan) take = vnan && (!bnan || vi < bi);        // NaN beats numbers; earliest NaN
+      else take = v > best || (v == best && vi < bi);
+      if (take) { best = v; bi = vi; }
     }
     amax[lane] = bi;
     if (xin && argmax_out) argmax_out[(size_t)b * W + x] = bi;
@@ -159,7 +182,7 @@ plan_prep_warp_kernel(const float* __restrict__ field_pre, const float* __restri
   const int pk = amax[lane];
   const int nmaps = 1 + 2 * steps.n;
   float* out = umaps + (size_t)b * nmaps * R * W;
-  for (int r = warp; r < R; r += kPrepWarps) {
+  for (int r = warp; r < R; r += kWarpWarps) {
     const float v = fr[r * kPrepCols + lane];
     out[(size_t)r * W + x] = v;
     const float left = (r < pk) ? 1.f : v;        // left_field[rows < idx] = 1
@@ -204,6 +227,6 @@ extern "C" int lc_plan_prepare(const float* uf, int B, int D, int W, int R, cons
   plan_prep_columns_kernel<<<grid, kPrepCols * kPrepWarps, sm1, st>>>(uf, D, W, R, field_pre);
   int rc = check_launch("lc_plan_prepare/columns");
   if (rc) return rc;
-  plan_prep_warp_kernel<<<grid, kPrepCols * kPrepWarps, sm2, st>>>(field_pre, flow, W, R, is, umaps, argmax);
+  plan_prep_warp_kernel<<<grid, kPrepCols * kWarpWarps, sm2, st>>>(field_pre, flow, W, R, is, umaps, argmax);
   return check_launch("lc_plan_prepare/warp");
 }
