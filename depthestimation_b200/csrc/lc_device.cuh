@@ -48,4 +48,8 @@ struct LcPlanner {
   float* d_theta = nullptr;     // [W,R]
   float* d_xz = nullptr;        // [W,R,2]
   uint8_t* d_win = nullptr;     // [W,R,2] lo,hi (lo > hi = no edge); last ray has none
+  // lc_planner_solve's producer -> consumer log (grown on demand; one solve at a time per handle)
+  unsigned char* d_log = nullptr;
+  size_t log_bytes = 0;
+  int epoch = 0;
 };

@@ -103,6 +103,7 @@ void lc_planner_destroy(LcPlanner* p) {
   cudaFree(p->d_theta);
   cudaFree(p->d_xz);
   cudaFree(p->d_win);
+  cudaFree(p->d_log);
   delete p;
 }
 
