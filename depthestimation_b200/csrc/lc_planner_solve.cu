@@ -17,8 +17,8 @@
 //      can hold a first-key tie (fl(u + .) == fl(u + m)) are counted.  If exactly one group qualifies, its lane
 //      opens it; if exactly one of its entries ties, the successor is known.  A needs only unc/qm of the
 //      previous ray, never the second key, so it runs ahead at its own pace and appends, per ray, unc[] and a
-//      code per node (successor | bare | tie) to the log, then publishes the ray with a release store.
-//   B. (second CTA) follows the log a few rays behind (acquire loads, prefetched two rays ahead): fills in the
+//      code per node (successor | bare | tie) to the log as self-describing 8-byte entries (no fence, no flag).
+//   B. (second CTA) follows the log (entries prefetched two rays ahead, re-read until tagged): fills in the
 //      second key las of the nodes A finished, and resolves the tie nodes, one WARP per node: the previous ray
 //      sits in the warp's registers, four entries per lane; tie flags, the second key for the tied entries,
 //      and two REDUX.min give the exact (las, e) minimum with no divergence, however many entries tie.  B owns
@@ -39,28 +39,18 @@ constexpr unsigned kNoWindow = 1u;   // lo = 1 > hi = 0
 constexpr int kCodeBare = -1;        // node keeps its own value: las 0, no successor
 constexpr int kCodeTie = -2;         // several edges tie on the first key: B decides
 
-struct PlannerLog {                  // per umap, in global memory (LcPlanner::d_log)
-  float* unc;                        // [W][RP]
-  int16_t* code;                     // [W][RP]
-  int* flag;                         // [W]  == epoch once the ray is published
-};
-
-__device__ __forceinline__ PlannerLog log_of(unsigned char* base, size_t per_map, int map, int W, int RP) {
-  PlannerLog l;
-  unsigned char* p = base + (size_t)map * per_map;
-  l.unc = reinterpret_cast<float*>(p);
-  l.code = reinterpret_cast<int16_t*>(p + (size_t)W * RP * 4);
-  l.flag = reinterpret_cast<int*>(p + (size_t)W * RP * 6);
-  return l;
+// The log A writes and B follows (global memory, LcPlanner::d_log): one 8-byte entry per (ray, node),
+//   bits 0-31 unc, 32-47 code (successor | bare | tie), 48-63 tag of the solve that wrote it.
+// An aligned 8-byte store is single-copy atomic and the entry is self-describing, so no flag, fence or ordering
+// between entries is needed: B re-reads an entry until its tag is the current one.
+__device__ __forceinline__ unsigned long long log_entry(float unc, int code, unsigned tag) {
+  return (unsigned long long)__float_as_uint(unc) | ((unsigned long long)(unsigned)(code & 0xffff) << 32) |
+         ((unsigned long long)tag << 48);
 }
-
-__device__ __forceinline__ int ld_acquire(const int* p) {
-  int v;
-  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+__device__ __forceinline__ unsigned long long ld_relaxed(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
   return v;
-}
-__device__ __forceinline__ void st_release(int* p, int v) {
-  asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -68,7 +58,7 @@ __device__ __forceinline__ void st_release(int* p, int v) {
 // ------------------------------------------------------------------------------------------------
 template <int LANES, int NQL>
 __device__ __forceinline__ void planner_part_a(unsigned char* smraw, const float* __restrict__ umap, int W, int R,
-                                               const uint8_t* __restrict__ win, PlannerLog lg, int epoch) {
+                                               const uint8_t* __restrict__ win, unsigned long long* __restrict__ lg, unsigned tag) {
   constexpr int NQ = LANES * NQL;                                 // groups of four per ray
   constexpr int RP = 4 * NQ;                                      // padded ray length
   constexpr int SLOT = RP + 2 * NQ;                               // unc (pad -inf) + qm (padded: no index clamp)
@@ -178,18 +168,16 @@ __device__ __forceinline__ void planner_part_a(unsigned char* smraw, const float
     if (active) {
       if (s == 0) {
         unco[k] = bu;
-        lg.unc[(size_t)i * RP + k] = bu;
         if ((k & 3) == 0) unco[RP + (k >> 2)] = gq;
       }
-      // one lane per node writes the code: the owner when a single candidate exists, lane 0 otherwise
+      // one lane per node appends the log entry: the owner when a single candidate exists, lane 0 otherwise
       if (!better) {
-        if (s == 0) lg.code[(size_t)i * RP + k] = (int16_t)kCodeBare;
+        if (s == 0) lg[(size_t)i * RP + k] = log_entry(bu, kCodeBare, tag);
       } else if (owner || (s == 0 && tot >= 2)) {
-        lg.code[(size_t)i * RP + k] = (int16_t)code;
+        lg[(size_t)i * RP + k] = log_entry(bu, code, tag);
       }
     }
-    __syncthreads();                                              // ray i complete in shared memory ...
-    if (threadIdx.x == 0) st_release(lg.flag + i, epoch);         // ... and (cumulatively) in the log
+    __syncthreads();                                              // ray i complete in shared memory
   }
 }
 
@@ -197,15 +185,15 @@ __device__ __forceinline__ void planner_part_a(unsigned char* smraw, const float
 // part B: second keys (las), tie nodes, back-pointers, path
 // ------------------------------------------------------------------------------------------------
 struct LogRay {          // what a node's thread needs of one ray
-  float unc, u, th;
-  int code;
+  unsigned long long entry;
+  float u, th;
   unsigned w;
 };
 
 template <int NCH>
 __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float* __restrict__ umap, int W, int R,
                                                const float* __restrict__ theta, const float* __restrict__ node_xz,
-                                               const uint8_t* __restrict__ win, PlannerLog lg, int epoch, int map,
+                                               const uint8_t* __restrict__ win, const unsigned long long* lg, unsigned tag, int map,
                                                int32_t* __restrict__ ks, float* __restrict__ xz,
                                                int32_t* __restrict__ counts) {
   constexpr int RP = 128 * NCH;
@@ -219,33 +207,24 @@ __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int k = threadIdx.x;                                      // node whose log entries this thread follows
   const bool node = k < R;
-  const bool poller = warp == nwarps - 1;                         // this warp only watches A's progress
-  const int tie_warps = nwarps - 1;
   const unsigned full = 0xffffffffu;
 
   for (int i = threadIdx.x; i < 6 * RP; i += blockDim.x) state[i] = ((i % (3 * RP)) < RP) ? -INFINITY : 0.f;
   if (threadIdx.x < 2) s_nt[threadIdx.x] = 0;
 
-  auto wait_ray = [&](int i) {                                    // one thread spins; A never waits for B
-    if (i >= 0)
-      while (ld_acquire(lg.flag + i) != epoch) __nanosleep(64);
-  };
-  auto load_ray = [&](int i) {
+  auto load_ray = [&](int i) {                                    // may come back with an old tag: checked at use
     LogRay r;
-    r.unc = -INFINITY; r.u = 0.f; r.th = 0.f; r.code = kCodeBare; r.w = kNoWindow;
+    r.entry = 0ull; r.u = 0.f; r.th = 0.f; r.w = kNoWindow;
     if (node && i >= 0) {
-      r.unc = __ldcg(lg.unc + (size_t)i * RP + k);
-      r.code = (int)__ldcg(lg.code + (size_t)i * RP + k);
+      r.entry = ld_relaxed(lg + (size_t)i * RP + k);
       r.u = __ldg(umap + (size_t)k * W + i);
       r.th = __ldg(theta + (size_t)i * R + k);
       if (i < W - 1) r.w = __ldg(reinterpret_cast<const uint16_t*>(win) + (size_t)i * R + k);
     }
     return r;
   };
-  // rays W-1, W-2 are loaded before the loop; inside, ray i-2 is requested during ray i, and its publication was
-  // confirmed one iteration earlier (the poller waits for ray i-3 during ray i)
-  if (poller && lane == 0) { wait_ray(W - 1); wait_ray(W - 2); wait_ray(W - 3); }
   __syncthreads();
+  // rays W-1, W-2 are requested before the loop; inside, ray i-2 is requested during ray i
   LogRay cur = load_ray(W - 1), nxt = load_ray(W - 2);
 
   int pc = 0;                                                     // buffer of the previous ray (i+1); 1-pc: ray i
@@ -256,20 +235,27 @@ __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float
     const int par = i & 1;
     // ---- every node: stage the ray, finish what A decided, queue the ties
     {
-      const LogRay r = cur;
+      LogRay r = cur;
       cur = nxt;
       nxt = load_ray(i - 2);
+      if (node)                                                   // A has not got here yet: wait for this node's entry
+        while ((unsigned)(r.entry >> 48) != tag) {
+          __nanosleep(32);
+          r.entry = ld_relaxed(lg + (size_t)i * RP + k);
+        }
+      const float r_unc = __uint_as_float((unsigned)r.entry);
+      const int r_code = (int)(short)(unsigned short)(r.entry >> 32);
       const int lo = (int)(r.w & 0xffu), hi = (int)(r.w >> 8);
       bool tie = false;
       if (node) {
-        sc[k] = r.unc;
+        sc[k] = r_unc;
         sc[2 * RP + k] = r.th;
         nin[k] = make_float4(r.u, r.th, __int_as_float(lo), __int_as_float(hi));
-        if (r.code >= 0) {                                        // successor known: planning.cpp:197-198
-          const float dth = __fsub_rn(sp[2 * RP + r.code], r.th);
-          sc[RP + k] = __fadd_rn(__fmul_rn(dth, dth), sp[RP + r.code]);
-          subi[k] = (uint8_t)r.code;
-        } else if (r.code == kCodeBare) {
+        if (r_code >= 0) {                                        // successor known: planning.cpp:197-198
+          const float dth = __fsub_rn(sp[2 * RP + r_code], r.th);
+          sc[RP + k] = __fadd_rn(__fmul_rn(dth, dth), sp[RP + r_code]);
+          subi[k] = (uint8_t)r_code;
+        } else if (r_code == kCodeBare) {
           sc[RP + k] = 0.f;
           subi[k] = 255;
         } else {
@@ -288,12 +274,10 @@ __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float
       if (threadIdx.x == 0) s_nt[par ^ 1] = 0;                    // read during the previous ray, pushed on the next
     }
     __syncthreads();
-    // ---- tie nodes, one warp each; the last warp confirms that ray i-3 is published meanwhile
-    if (poller) {
-      if (lane == 0) wait_ray(i - 3);
-    } else {
+    // ---- tie nodes, one warp each
+    {
       const int nt = s_nt[par];
-      for (int j = warp; j < nt; j += tie_warps) {
+      for (int j = warp; j < nt; j += nwarps) {
         const int rk = list[j];
         const float4 in = nin[rk];
         const float ru = in.x, rtn = in.y, rtmax = sc[rk];
@@ -371,17 +355,17 @@ __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float
 template <int LANES, int NQL>
 __global__ void __launch_bounds__(1024)
 planner_solve_kernel(const float* __restrict__ umaps, int W, int R, const float* __restrict__ theta,
-                     const float* __restrict__ node_xz, const uint8_t* __restrict__ win, unsigned char* log_base,
-                     size_t log_per_map, int epoch, int32_t* __restrict__ ks, float* __restrict__ xz,
+                     const float* __restrict__ node_xz, const uint8_t* __restrict__ win, unsigned long long* log_base,
+                     size_t log_per_map, unsigned tag, int32_t* __restrict__ ks, float* __restrict__ xz,
                      int32_t* __restrict__ counts) {
   constexpr int RP = 4 * LANES * NQL;
   static_assert(RP % 128 == 0, "ray length must fill whole warps in part B");
   extern __shared__ __align__(16) unsigned char smraw[];
   const int map = blockIdx.x >> 1;
   const float* umap = umaps + (size_t)map * R * W;
-  const PlannerLog lg = log_of(log_base, log_per_map, map, W, RP);
-  if ((blockIdx.x & 1) == 0) planner_part_a<LANES, NQL>(smraw, umap, W, R, win, lg, epoch);
-  else planner_part_b<RP / 128>(smraw, umap, W, R, theta, node_xz, win, lg, epoch, map, ks, xz, counts);
+  unsigned long long* lg = log_base + (size_t)map * log_per_map;
+  if ((blockIdx.x & 1) == 0) planner_part_a<LANES, NQL>(smraw, umap, W, R, win, lg, tag);
+  else planner_part_b<RP / 128>(smraw, umap, W, R, theta, node_xz, win, lg, tag, map, ks, xz, counts);
 }
 
 }  // namespace dpv
@@ -398,17 +382,19 @@ int launch_solve(LcPlanner* p, const float* umaps, int n, int warps, int32_t* ks
   constexpr int RP = 4 * LANES * NQL;
   DPV_REQUIRE(R <= RP, "lc_planner_solve: R=%d does not fit the %d-entry kernel", R, RP);
   // the log A writes and B follows: grown on demand, kept in the handle
-  const size_t per_map = (((size_t)W * RP * 6 + (size_t)W * 4) + 255) & ~(size_t)255;
-  if (p->log_bytes < per_map * n) {
+  const size_t per_map = (size_t)W * RP;                          // entries per umap
+  if (p->log_bytes < per_map * n * 8) {
     if (p->d_log) DPV_CUDA(cudaFree(p->d_log));
     p->d_log = nullptr;
     p->log_bytes = 0;
-    DPV_CUDA(cudaMalloc(&p->d_log, per_map * n));
-    DPV_CUDA(cudaMemsetAsync(p->d_log, 0, per_map * n, st));      // flags 0: no ray published under any epoch >= 1
-    p->log_bytes = per_map * n;
+    DPV_CUDA(cudaMalloc(&p->d_log, per_map * n * 8));
+    p->log_bytes = per_map * n * 8;
     p->epoch = 0;
   }
   p->epoch += 1;
+  if (p->epoch > 0xffff) p->epoch = 1;
+  if (p->epoch == 1)                                              // tag 0 = "written by no solve"; also on tag wrap-around
+    DPV_CUDA(cudaMemsetAsync(p->d_log, 0, p->log_bytes, st));
   const size_t smem_b = (size_t)6 * RP * 4 + (size_t)RP * 16 + (size_t)RP * 4 + (size_t)((W + 7) & ~7) * 2 + (size_t)W * R;
   const size_t smem_a = (size_t)2 * (RP + 2 * (RP / 4)) * 4;
   const size_t smem = smem_a > smem_b ? smem_a : smem_b;
@@ -416,9 +402,9 @@ int launch_solve(LcPlanner* p, const float* umaps, int n, int warps, int32_t* ks
   auto kern = planner_solve_kernel<LANES, NQL>;
   DPV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int threads = ((R * LANES + 31) / 32) * 32;                     // part A: LANES threads per node
-  if (warps < 2) warps = 2;                                       // part B: tie warps + the polling warp
+  if (warps < 1) warps = 1;                                       // part B: one warp per tie node
   if (threads < 32 * warps) threads = 32 * warps;
-  if (threads < ((R + 31) / 32) * 32 + 32) threads = ((R + 31) / 32) * 32 + 32;   // B follows one node per thread
+  if (threads < ((R + 31) / 32) * 32) threads = ((R + 31) / 32) * 32;            // B follows one node per thread
   DPV_REQUIRE(threads <= 1024, "lc_planner_solve: R=%d needs %d threads", R, threads);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)(2 * n));
@@ -433,7 +419,8 @@ int launch_solve(LcPlanner* p, const float* umaps, int n, int warps, int32_t* ks
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   DPV_CUDA(cudaLaunchKernelEx(&cfg, kern, umaps, W, R, (const float*)p->d_theta, (const float*)p->d_xz,
-                              (const uint8_t*)p->d_win, p->d_log, per_map, p->epoch, ks, xz, counts));
+                              (const uint8_t*)p->d_win, (unsigned long long*)p->d_log, per_map, (unsigned)p->epoch, ks, xz,
+                              counts));
   return DPV_OK;
 }
 
@@ -443,7 +430,7 @@ extern "C" int lc_planner_solve(LcPlanner* p, const float* umaps, int n, int32_t
                                 void* stream) {
   DPV_REQUIRE(p && umaps, "lc_planner_solve: null pointer");
   DPV_REQUIRE(n > 0, "lc_planner_solve: n=%d", n);
-  int lanes = 4, warps = 16;                                      // warps = part-B warps (incl. the polling warp)
+  int lanes = 2, warps = 16;                                      // warps = part-B warps
   if (const char* e = getenv("DPV_PLANNER_LANES")) lanes = atoi(e);                // tuning aids
   if (const char* e = getenv("DPV_PLANNER_WARPS")) warps = atoi(e);
   cudaStream_t st = (cudaStream_t)stream;
