@@ -18,8 +18,9 @@
 //      opens it; if exactly one of its entries ties, the successor is known.  A needs only unc/qm of the
 //      previous ray, never the second key, so it runs ahead at its own pace and appends, per ray, unc[] and a
 //      code per node (successor | bare | tie) to the log as self-describing 8-byte entries (no fence, no flag).
-//   B. (second CTA) follows the log (entries prefetched two rays ahead, re-read until tagged): fills in the
-//      second key las of the nodes A finished, and resolves the tie nodes, one WARP per node: the previous ray
+//   B. (second CTA) follows the log (entries prefetched, re-read until tagged).  One step and one barrier per
+//      ray: it fills in the second key las of the nodes A finished, stages the next ray (independent work), and
+//      resolves the tie nodes, one WARP per node: the previous ray
 //      sits in the warp's registers, four entries per lane; tie flags, the second key for the tied entries,
 //      and two REDUX.min give the exact (las, e) minimum with no divergence, however many entries tie.  B owns
 //      the back-pointers (W*R bytes of shared memory) and unrolls the path at the end.
@@ -193,24 +194,27 @@ struct LogRay {          // what a node's thread needs of one ray
 template <int NCH>
 __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float* __restrict__ umap, int W, int R,
                                                const float* __restrict__ theta, const float* __restrict__ node_xz,
-                                               const uint8_t* __restrict__ win, const unsigned long long* lg, unsigned tag, int map,
-                                               int32_t* __restrict__ ks, float* __restrict__ xz,
-                                               int32_t* __restrict__ counts) {
+                                               const uint8_t* __restrict__ win, const unsigned long long* lg,
+                                               unsigned tag, int map, int32_t* __restrict__ ks,
+                                               float* __restrict__ xz, int32_t* __restrict__ counts) {
   constexpr int RP = 128 * NCH;
-  float* state = reinterpret_cast<float*>(smraw);                 // [2][3][RP]: unc (pad -inf), las, th
-  float4* nin = reinterpret_cast<float4*>(state + 6 * RP);        // [RP]: u, theta, lo, hi of the current ray's nodes
-  int* list = reinterpret_cast<int*>(nin + RP);                   // [RP] tie nodes of the current ray
-  int16_t* path = reinterpret_cast<int16_t*>(list + RP);          // [W rounded to 8]
+  constexpr int SLOT = 3 * RP;                                    // unc (pad -inf), las, th of one ray
+  float* state = reinterpret_cast<float*>(smraw);                 // [3][SLOT] ring over rays
+  float4* nin = reinterpret_cast<float4*>(state + 3 * SLOT);      // [2][RP]: u, theta, lo, hi of a ray's nodes
+  int* list = reinterpret_cast<int*>(nin + 2 * RP);               // [2][RP] tie nodes of a ray
+  int16_t* path = reinterpret_cast<int16_t*>(list + 2 * RP);      // [W rounded to 8]
   uint8_t* sub = reinterpret_cast<uint8_t*>(path + ((W + 7) & ~7));   // [W][R]
-  __shared__ int s_nt[2];
+  __shared__ int s_nt[3];                                         // tie counts, ring like state
   __shared__ int s_cnt;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int k = threadIdx.x;                                      // node whose log entries this thread follows
   const bool node = k < R;
+  const bool node_warp = warp * 32 < R;
   const unsigned full = 0xffffffffu;
 
-  for (int i = threadIdx.x; i < 6 * RP; i += blockDim.x) state[i] = ((i % (3 * RP)) < RP) ? -INFINITY : 0.f;
-  if (threadIdx.x < 2) s_nt[threadIdx.x] = 0;
+  for (int i = threadIdx.x; i < 3 * SLOT; i += blockDim.x) state[i] = ((i % SLOT) < RP) ? -INFINITY : 0.f;
+  if (threadIdx.x < 3) s_nt[threadIdx.x] = 0;
+  __syncthreads();
 
   auto load_ray = [&](int i) {                                    // may come back with an old tag: checked at use
     LogRay r;
@@ -223,93 +227,102 @@ __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float
     }
     return r;
   };
-  __syncthreads();
-  // rays W-1, W-2 are requested before the loop; inside, ray i-2 is requested during ray i
-  LogRay cur = load_ray(W - 1), nxt = load_ray(W - 2);
+  // Stage ray i for the step that will finish it: unc and theta into its ring slot, the node inputs, the list of
+  // tie nodes.  Returns the node's code (successor | bare | tie) and theta for the thread to keep.
+  auto stage_ray = [&](int i, LogRay r, int slot, int& code_out, float& th_out) {
+    if (node)                                                     // A has not got here yet: wait for this node's entry
+      while ((unsigned)(r.entry >> 48) != tag) {
+        __nanosleep(32);
+        r.entry = ld_relaxed(lg + (size_t)i * RP + k);
+      }
+    const int code = (int)(short)(unsigned short)(r.entry >> 32);
+    const int lo = (int)(r.w & 0xffu), hi = (int)(r.w >> 8);
+    if (node) {
+      float* s = state + slot * SLOT;
+      s[k] = __uint_as_float((unsigned)r.entry);
+      s[2 * RP + k] = r.th;
+      nin[(i & 1) * RP + k] = make_float4(r.u, r.th, __int_as_float(lo), __int_as_float(hi));
+    }
+    const bool tie = node && code == kCodeTie;
+    const unsigned pb = __ballot_sync(full, tie);
+    if (pb) {
+      int base = 0;
+      if (lane == 0) base = atomicAdd(&s_nt[slot], __popc(pb));
+      base = __shfl_sync(full, base, 0);
+      if (tie) list[(i & 1) * RP + base + __popc(pb & ((1u << lane) - 1u))] = k;
+    }
+    code_out = code;
+    th_out = r.th;
+  };
 
-  int pc = 0;                                                     // buffer of the previous ray (i+1); 1-pc: ray i
+  // ring slots: sa = ray i+1 (complete), sb = ray i (staged, finished in this step), sc_ = ray i-1 (staged in this step)
+  int sa = W % 3, sb = (W - 1) % 3, sc_ = (W + 1) % 3;
+  LogRay nxt = load_ray(W - 2), nx2 = load_ray(W - 3);            // entries are requested two rays before their staging
+  int code = kCodeBare;
+  float tn = 0.f;
+  if (node_warp) stage_ray(W - 1, load_ray(W - 1), sb, code, tn);
+  __syncthreads();
+
   for (int i = W - 1; i >= 0; i--) {
-    const float* sp = state + pc * 3 * RP;                        // ray i+1: unc, las, th
-    float* sc = state + (1 - pc) * 3 * RP;                        // ray i
+    const float* sp = state + sa * SLOT;                          // ray i+1: unc, las, th
+    float* sc = state + sb * SLOT;                                // ray i
     uint8_t* subi = sub + (size_t)i * R;
-    const int par = i & 1;
-    // ---- every node: stage the ray, finish what A decided, queue the ties
-    {
-      LogRay r = cur;
-      cur = nxt;
-      nxt = load_ray(i - 2);
-      if (node)                                                   // A has not got here yet: wait for this node's entry
-        while ((unsigned)(r.entry >> 48) != tag) {
-          __nanosleep(32);
-          r.entry = ld_relaxed(lg + (size_t)i * RP + k);
-        }
-      const float r_unc = __uint_as_float((unsigned)r.entry);
-      const int r_code = (int)(short)(unsigned short)(r.entry >> 32);
-      const int lo = (int)(r.w & 0xffu), hi = (int)(r.w >> 8);
-      bool tie = false;
+    if (threadIdx.x == 0) s_nt[sa] = 0;                           // its ties were read a step ago; pushed again next step
+    if (node_warp) {
+      // ---- nodes A finished: second key from the successor (planning.cpp:197-198); bare nodes: las 0
       if (node) {
-        sc[k] = r_unc;
-        sc[2 * RP + k] = r.th;
-        nin[k] = make_float4(r.u, r.th, __int_as_float(lo), __int_as_float(hi));
-        if (r_code >= 0) {                                        // successor known: planning.cpp:197-198
-          const float dth = __fsub_rn(sp[2 * RP + r_code], r.th);
-          sc[RP + k] = __fadd_rn(__fmul_rn(dth, dth), sp[RP + r_code]);
-          subi[k] = (uint8_t)r_code;
-        } else if (r_code == kCodeBare) {
+        if (code >= 0) {
+          const float dth = __fsub_rn(sp[2 * RP + code], tn);
+          sc[RP + k] = __fadd_rn(__fmul_rn(dth, dth), sp[RP + code]);
+          subi[k] = (uint8_t)code;
+        } else if (code == kCodeBare) {
           sc[RP + k] = 0.f;
           subi[k] = 255;
-        } else {
-          tie = true;
         }
       }
-      if (warp * 32 < R) {                                        // warps that hold nodes
-        const unsigned pb = __ballot_sync(full, tie);
-        if (pb) {
-          int base = 0;
-          if (lane == 0) base = atomicAdd(&s_nt[par], __popc(pb));
-          base = __shfl_sync(full, base, 0);
-          if (tie) list[base + __popc(pb & ((1u << lane) - 1u))] = k;
-        }
-      }
-      if (threadIdx.x == 0) s_nt[par ^ 1] = 0;                    // read during the previous ray, pushed on the next
+      // ---- stage ray i-1 for the next step (independent of everything this step computes)
+      const LogRay r = nxt;
+      nxt = nx2;
+      nx2 = load_ray(i - 3);
+      if (i > 0) stage_ray(i - 1, r, sc_, code, tn);
     }
-    __syncthreads();
-    // ---- tie nodes, one warp each
-    {
-      const int nt = s_nt[par];
-      for (int j = warp; j < nt; j += nwarps) {
-        const int rk = list[j];
-        const float4 in = nin[rk];
-        const float ru = in.x, rtn = in.y, rtmax = sc[rk];
-        const int rlo = __float_as_int(in.z), rhi = __float_as_int(in.w);
-        float tl_best = INFINITY;
-        int e_best = 0x7fffffff;
+    // ---- tie nodes of ray i, one warp each, handed out from the last warp down (the first warps hold the nodes)
+    const int nt = s_nt[sb];
+    const float4* ninb = nin + (i & 1) * RP;
+    const int* listb = list + (i & 1) * RP;
+    for (int j = nwarps - 1 - warp; j < nt; j += nwarps) {
+      const int rk = listb[j];
+      const float4 in = ninb[rk];
+      const float ru = in.x, rtn = in.y, rtmax = sc[rk];
+      const int rlo = __float_as_int(in.z), rhi = __float_as_int(in.w);
+      float tl_best = INFINITY;
+      int e_best = 0x7fffffff;
 #pragma unroll
-        for (int c = 0; c < NCH; c++) {                           // chunks of 128 entries, four per lane
-          const int e = c * 128 + lane * 4;
-          const float4 v = reinterpret_cast<const float4*>(sp)[c * 32 + lane];
-          const float4 l4 = reinterpret_cast<const float4*>(sp + RP)[c * 32 + lane];
-          const float4 t4 = reinterpret_cast<const float4*>(sp + 2 * RP)[c * 32 + lane];
-          const float vv[4] = {v.x, v.y, v.z, v.w}, tt[4] = {t4.x, t4.y, t4.z, t4.w}, ll[4] = {l4.x, l4.y, l4.z, l4.w};
+      for (int c = 0; c < NCH; c++) {                             // chunks of 128 entries, four per lane
+        const int e = c * 128 + lane * 4;
+        const float4 v = reinterpret_cast<const float4*>(sp)[c * 32 + lane];
+        const float4 l4 = reinterpret_cast<const float4*>(sp + RP)[c * 32 + lane];
+        const float4 t4 = reinterpret_cast<const float4*>(sp + 2 * RP)[c * 32 + lane];
+        const float vv[4] = {v.x, v.y, v.z, v.w}, tt[4] = {t4.x, t4.y, t4.z, t4.w}, ll[4] = {l4.x, l4.y, l4.z, l4.w};
 #pragma unroll
-          for (int q = 0; q < 4; q++) {
-            const float dth = __fsub_rn(tt[q], rtn);              // :197-198
-            const float tl = __fadd_rn(__fmul_rn(dth, dth), ll[q]);
-            const bool tie = e + q >= rlo && e + q <= rhi && __fadd_rn(ru, vv[q]) == rtmax;
-            if (tie && tl < tl_best) { tl_best = tl; e_best = e + q; }    // increasing e: first minimum stays
-          }
+        for (int q = 0; q < 4; q++) {
+          const float dth = __fsub_rn(tt[q], rtn);                // :197-198
+          const float tl = __fadd_rn(__fmul_rn(dth, dth), ll[q]);
+          const bool tie = e + q >= rlo && e + q <= rhi && __fadd_rn(ru, vv[q]) == rtmax;
+          if (tie && tl < tl_best) { tl_best = tl; e_best = e + q; }      // increasing e: first minimum stays
         }
-        const unsigned tmin = __reduce_min_sync(full, __float_as_uint(tl_best));   // las >= +0: bit order = value order
-        const int be = __reduce_min_sync(full, __float_as_uint(tl_best) == tmin ? e_best : 0x7fffffff);
-        if (lane == 0) {
-          sc[RP + rk] = __uint_as_float(tmin);
-          subi[rk] = (uint8_t)be;
-        }
+      }
+      const unsigned tmin = __reduce_min_sync(full, __float_as_uint(tl_best));   // las >= +0: bit order = value order
+      const int be = __reduce_min_sync(full, __float_as_uint(tl_best) == tmin ? e_best : 0x7fffffff);
+      if (lane == 0) {
+        sc[RP + rk] = __uint_as_float(tmin);
+        subi[rk] = (uint8_t)be;
       }
     }
     __syncthreads();
-    pc = 1 - pc;
+    const int t = sa; sa = sb; sb = sc_; sc_ = t;                 // ray i+1's slot is free for ray i-2
   }
+  const int pc = sa;                                              // ray 0 after the last rotation
   // ray 0 is in buffer pc.  Best start against a default (0,0,null) trajectory (planning.cpp:99-104)
   if (threadIdx.x == 0) {
     const float* u0 = state + pc * 3 * RP;
@@ -395,7 +408,8 @@ int launch_solve(LcPlanner* p, const float* umaps, int n, int warps, int32_t* ks
   if (p->epoch > 0xffff) p->epoch = 1;
   if (p->epoch == 1)                                              // tag 0 = "written by no solve"; also on tag wrap-around
     DPV_CUDA(cudaMemsetAsync(p->d_log, 0, p->log_bytes, st));
-  const size_t smem_b = (size_t)6 * RP * 4 + (size_t)RP * 16 + (size_t)RP * 4 + (size_t)((W + 7) & ~7) * 2 + (size_t)W * R;
+  const size_t smem_b = (size_t)9 * RP * 4 + (size_t)2 * RP * 16 + (size_t)2 * RP * 4 + (size_t)((W + 7) & ~7) * 2 +
+                        (size_t)W * R;
   const size_t smem_a = (size_t)2 * (RP + 2 * (RP / 4)) * 4;
   const size_t smem = smem_a > smem_b ? smem_a : smem_b;
   DPV_REQUIRE(smem <= 227 * 1024, "lc_planner_solve: W*R = %d*%d back-pointers exceed shared memory", W, R);

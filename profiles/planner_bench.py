@@ -23,7 +23,7 @@ def main():
     um = st.umaps.view(B * nc, R, W)
     ref = None
     for cl in (2, 4):
-        for warps in (8, 16, 24):
+        for warps in (16, 24, 32):
             os.environ["DPV_PLANNER_LANES"] = str(cl)
             os.environ["DPV_PLANNER_WARPS"] = str(warps)
             ks = torch.empty_like(st.ks)
