@@ -45,6 +45,7 @@ def build(force=False, verbose=False):
         o = os.path.join(objdir, os.path.basename(s)[:-3] + ".o")
         objs.append(o)
         extra = ["-fmad=false"] if s.endswith("_nofma.cu") else []      # lcsim geometry: round as written
+        extra += os.environ.get("DPV_NVCC_EXTRA", "").split()              # development: e.g. -DDPV_FUSE_BLOCKS16=8
         cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
         procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     failed = False

@@ -5,6 +5,7 @@
 // is one fully-used 128 B line).
 #include <atomic>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "dpv_pixel.cuh"
@@ -39,23 +40,24 @@ __device__ __forceinline__ float lane_group_sum(float v) {
 }
 
 template <int DPT, int T>
-__global__ void __launch_bounds__(kThreads, 4)
-lsm_stats_kernel(const float* __restrict__ x, const float* __restrict__ add, int D, int H, int W, long long npix,
+__global__ void __launch_bounds__(kThreads, DPT <= 16 ? 8 : 4)
+lsm_stats_kernel(const float* __restrict__ x, const float* __restrict__ add, int D, int H, int W,
                  const float* __restrict__ d_candi, float* __restrict__ logp, float* __restrict__ mean_o,
                  float* __restrict__ var_o, float* __restrict__ ent_o, float* __restrict__ carry) {
   __shared__ float dc[DPT * T];
   for (int i = threadIdx.x; i < DPT * T; i += blockDim.x) dc[i] = i < D ? d_candi[i] : 0.f;
   __syncthreads();
-  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  // every lane of a warp stays alive for the shuffles: out-of-range pixels are clamped and not stored
-  const bool live = gid / T < npix;
-  const long long pix = live ? gid / T : npix - 1;
+  // grid.y = sample, grid.x covers one image: the per-pixel index arithmetic stays in 32 bits.
+  // Every lane of a warp stays alive for the shuffles: out-of-range pixels are clamped and not stored.
+  const unsigned HW = (unsigned)H * (unsigned)W;
+  const unsigned hw_raw = (blockIdx.x * blockDim.x + threadIdx.x) / T;
+  const bool live = hw_raw < HW;
+  const unsigned hw = live ? hw_raw : HW - 1;
   const int tl = threadIdx.x & (T - 1);
   const int d0 = tl * DPT;
   const float* dcl = dc + d0;
-  const size_t HW = (size_t)H * W;
-  const int b = (int)(pix / (long long)HW);
-  const size_t hw = (size_t)(pix - (long long)b * HW);
+  const int b = blockIdx.y;
+  const size_t pix = (size_t)b * HW + hw;
   const size_t base = ((size_t)b * D + d0) * HW + hw;
 
   float t[DPT];
@@ -78,13 +80,13 @@ lsm_stats_kernel(const float* __restrict__ x, const float* __restrict__ add, int
   for (int d = 0; d < DPT; d += 2) {
     t[d] -= m;
     t[d + 1] -= m;
-    e[d] = expf(t[d]);                 // exp(-inf) = 0 for the padding bins
-    e[d + 1] = expf(t[d + 1]);
+    e[d] = exp2f_approx(t[d] * 1.4426950408889634f);       // exp(-inf) = 0 for the padding bins
+    e[d + 1] = exp2f_approx(t[d + 1] * 1.4426950408889634f);
     s0 += e[d];
     s1 += e[d + 1];
   }
   const float ssum = lane_group_sum<T>(s0 + s1);
-  const float lse = logf(ssum);
+  const float lse = log2f_approx(ssum) * 0.6931471805599453f;   // ssum in [1, D]
   const float inv = 1.f / ssum;
   float mean0 = 0.f, mean1 = 0.f, ent0 = 0.f, ent1 = 0.f;
 #pragma unroll
@@ -123,7 +125,7 @@ lsm_stats_kernel(const float* __restrict__ x, const float* __restrict__ add, int
   }
   if (carry && live) {
     // F.interpolate(scale_factor=0.25, 'nearest'): dst (j,i) <- src (4j, 4i)
-    const int y = (int)(hw / W), xx = (int)(hw % W);
+    const int y = (int)(hw / (unsigned)W), xx = (int)(hw - (unsigned)y * (unsigned)W);
     const int h4 = H / 4, w4 = W / 4;
     if ((y & 3) == 0 && (xx & 3) == 0 && (y >> 2) < h4 && (xx >> 2) < w4) {
       float* c = carry + ((size_t)b * D + d0) * h4 * w4 + (size_t)(y >> 2) * w4 + (xx >> 2);
@@ -323,15 +325,19 @@ int dpv_logsoftmax_stats(const float* x, const float* add, int B, int D, int H, 
   DPV_REQUIRE(x && logp && d_candi, "dpv_logsoftmax_stats: null pointer");
   DPV_REQUIRE(B > 0 && D > 0 && H > 0 && W > 0, "dpv_logsoftmax_stats: bad shape B=%d D=%d H=%d W=%d", B, D, H, W);
   cudaStream_t st = (cudaStream_t)stream;
-  const long long npix = (long long)B * H * W;
+  const long long npix = (long long)B * H * W, hw_img = (long long)H * W;
+  DPV_REQUIRE(B <= 65535 && hw_img * 32 < (1ll << 31), "dpv_logsoftmax_stats: B=%d or image too large", B);
   const unsigned g = blocks_for(npix, kThreads);
 #define LAUNCH(DPT, T)                                                                                       \
-  lsm_stats_kernel<DPT, T><<<blocks_for(npix * T, kThreads), kThreads, 0, st>>>(x, add, D, H, W, npix, d_candi, \
-                                                                                logp, mean, var, entropy, carry)
+  lsm_stats_kernel<DPT, T><<<dim3(blocks_for(hw_img * T, kThreads), (unsigned)B), kThreads, 0, st>>>( \
+      x, add, D, H, W, d_candi, logp, mean, var, entropy, carry)
   if (D <= 16) LAUNCH(16, 1);
   else if (D <= 32) LAUNCH(32, 1);
-  else if (D <= 64) LAUNCH(32, 2);
-  else if (D <= 128) LAUNCH(32, 4);
+  else if (D <= 64) {
+    static const int lanes = getenv("DPV_LSM_LANES") ? atoi(getenv("DPV_LSM_LANES")) : 4;
+    if (lanes == 2) LAUNCH(32, 2);                             // 4 lanes: 64 registers, twice the resident warps
+    else LAUNCH(16, 4);
+  } else if (D <= 128) LAUNCH(32, 4);
   else
     lsm_stats_generic_kernel<<<g, kThreads, 0, st>>>(x, add, D, H, W, npix, d_candi, logp, mean, var, entropy, carry);
 #undef LAUNCH

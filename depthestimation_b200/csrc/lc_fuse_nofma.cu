@@ -11,12 +11,18 @@
 // (identical up to fp32 rounding; an extra rescale is inserted only if the running sum leaves fp32 range).
 // The volume may be kept as log-probability (the reference's format) or as clamped probability between
 // the iterations of one lc_process call (flags), which removes exp/log from the inner iterations.
+#include <cstdlib>
+
 #include "lc_sense.cuh"
 
 namespace dpv {
 
 constexpr int kFuseThreads = 128;
 constexpr int kMaxCurtains = 8;
+#ifndef DPV_FUSE_BLOCKS16
+#define DPV_FUSE_BLOCKS16 8
+#endif
+constexpr int kFuseBlocks16 = DPV_FUSE_BLOCKS16;   // resident CTAs per SM asked for when a lane holds 16 bins
 
 __device__ __forceinline__ float2 splat2(float a) { return make_float2(a, a); }
 
@@ -84,9 +90,9 @@ __device__ __forceinline__ void spread_pass(Col<DPT / 2>& p, int d0, int D, int 
 }
 
 template <int DPT, int T, int HALF, bool FULL>
-__global__ void __launch_bounds__(kFuseThreads, 4)
+__global__ void __launch_bounds__(kFuseThreads, DPT <= 16 ? kFuseBlocks16 : 4)
 sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float* __restrict__ depth,
-                  const float* __restrict__ planes, const float* __restrict__ noise, int nc, long long npix,
+                  const float* __restrict__ planes, const float* __restrict__ noise, int nc,
                   const float* __restrict__ d_candi, int D, int spread_iter, int flags,
                   float* __restrict__ vol_out, float* __restrict__ mean_out) {
   constexpr int NP = DPT / 2;
@@ -97,19 +103,19 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
     dc[i] = (j < DPT && d < D) ? d_candi[d] : 0.f;
   }
   __syncthreads();
-  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const long long pix = gid / T;
-  if (pix >= npix) return;                                   // whole lane groups leave together
+  // grid.y = sample, grid.x covers one image: all per-pixel index arithmetic stays in 32 bits
+  const unsigned HW = (unsigned)dv.H * (unsigned)dv.W;
+  const unsigned hw = (blockIdx.x * blockDim.x + threadIdx.x) / T;
+  if (hw >= HW) return;                                      // whole lane groups leave together
   const int lane = threadIdx.x & 31;
   const int t = lane & (T - 1);
   const int gbase = lane & ~(T - 1);
   const unsigned gmask = (T == 32 ? 0xffffffffu : ((1u << T) - 1u)) << gbase;
   const int d0 = t * DPT;
   const float4* dc4 = reinterpret_cast<const float4*>(dc + t * STR);
-  const size_t HW = (size_t)dv.H * dv.W;
-  const int b = (int)(pix / (long long)HW);
-  const size_t hw = (size_t)(pix - (long long)b * HW);
-  const int v = (int)(hw / dv.W), u = (int)(hw % dv.W);
+  const int b = blockIdx.y;
+  const size_t pix = (size_t)b * HW + hw;
+  const int v = (int)(hw / (unsigned)dv.W), u = (int)(hw - (unsigned)v * (unsigned)dv.W);
   const size_t base = ((size_t)b * D + d0) * HW + hw;
   auto valid = [&](int d) -> bool { return FULL || d0 + d < D; };
 
@@ -273,13 +279,14 @@ extern "C" int lc_sense_fuse(const LcDevice* dev, const float* logp_in, const fl
   DPV_REQUIRE(D <= 128, "lc_sense_fuse: D=%d > 128 unsupported", D);
   DPV_REQUIRE(((uintptr_t)planes & 15) == 0, "lc_sense_fuse: planes must be 16-byte aligned");
   DPV_REQUIRE((flags & ~3) == 0, "lc_sense_fuse: unknown flags %d", flags);
-  const long long npix = (long long)B * dev->H * dev->W;
+  const long long hw_img = (long long)dev->H * dev->W;
+  DPV_REQUIRE(B <= 65535 && hw_img * 32 < (1ll << 31), "lc_sense_fuse: B=%d or image too large", B);
   cudaStream_t st = (cudaStream_t)stream;
   const int half = spread_iter == 0 ? 0 : spread_n / 2;
 #define LAUNCH4(DPT, T, HALF, FULL)                                                                                \
   sense_fuse_kernel<DPT, T, HALF, FULL>                                                                            \
-      <<<(unsigned)((npix * T + kFuseThreads - 1) / kFuseThreads), kFuseThreads, 0, st>>>(                         \
-          dev->view, logp_in, depth, planes, noise, nc, npix, d_candi, D, spread_iter, flags, logp_out, mean_out)
+      <<<dim3((unsigned)((hw_img * T + kFuseThreads - 1) / kFuseThreads), (unsigned)B), kFuseThreads, 0, st>>>(    \
+          dev->view, logp_in, depth, planes, noise, nc, d_candi, D, spread_iter, flags, logp_out, mean_out)
 #define LAUNCH3(DPT, T, HALF)                        \
   do {                                               \
     if (D == DPT * T) LAUNCH4(DPT, T, HALF, true);   \
@@ -296,7 +303,11 @@ extern "C" int lc_sense_fuse(const LcDevice* dev, const float* logp_in, const fl
   // D == DPT*T (16, 32, 64, 128) compiles without any per-bin bound check
   if (D <= 16) LAUNCH(16, 1);
   else if (D <= 32) LAUNCH(32, 1);
-  else if (D <= 64) LAUNCH(32, 2);
+  else if (D <= 64) {
+    static const int lanes = getenv("DPV_FUSE_LANES") ? atoi(getenv("DPV_FUSE_LANES")) : 4;
+    if (lanes == 2) LAUNCH(32, 2);                             // 4 lanes: 64 registers, twice the resident warps
+    else LAUNCH(16, 4);
+  }
   else LAUNCH(32, 4);
 #undef LAUNCH
 #undef LAUNCH3
