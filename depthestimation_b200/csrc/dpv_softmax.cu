@@ -39,7 +39,7 @@ __device__ __forceinline__ float lane_group_sum(float v) {
   return v;
 }
 
-template <int DPT, int T>
+template <int DPT, int T, bool FULL>
 __global__ void __launch_bounds__(kThreads, DPT <= 16 ? 8 : 4)
 lsm_stats_kernel(const float* __restrict__ x, const float* __restrict__ add, int D, int H, int W,
                  const float* __restrict__ d_candi, float* __restrict__ logp, float* __restrict__ mean_o,
@@ -60,13 +60,19 @@ lsm_stats_kernel(const float* __restrict__ x, const float* __restrict__ add, int
   const size_t pix = (size_t)b * HW + hw;
   const size_t base = ((size_t)b * D + d0) * HW + hw;
 
+  // FULL (D == DPT*T): no per-bin bound checks.  Plane pointers are bumped by HW (one 64-bit add each).
+  auto valid = [&](int d) -> bool { return FULL || d0 + d < D; };
   float t[DPT];
+  {
+    const float* xp = x + base;
 #pragma unroll
-  for (int d = 0; d < DPT; d++) t[d] = (d0 + d < D) ? ld_stream(x + base + (size_t)d * HW) : -INFINITY;
+    for (int d = 0; d < DPT; d++, xp = bump(xp, HW)) t[d] = valid(d) ? ld_stream(xp) : -INFINITY;
+  }
   if (add != nullptr) {
+    const float* ap = add + base;
 #pragma unroll
-    for (int d = 0; d < DPT; d++)
-      if (d0 + d < D) t[d] += ld_stream(add + base + (size_t)d * HW);
+    for (int d = 0; d < DPT; d++, ap = bump(ap, HW))
+      if (valid(d)) t[d] += ld_stream(ap);
   }
   float m0 = t[0], m1 = t[1];
 #pragma unroll
@@ -89,18 +95,19 @@ lsm_stats_kernel(const float* __restrict__ x, const float* __restrict__ add, int
   const float lse = log2f_approx(ssum) * 0.6931471805599453f;   // ssum in [1, D]
   const float inv = 1.f / ssum;
   float mean0 = 0.f, mean1 = 0.f, ent0 = 0.f, ent1 = 0.f;
+  float* lpp = logp + base;
 #pragma unroll
-  for (int d = 0; d < DPT; d += 2) {
+  for (int d = 0; d < DPT; d += 2, lpp = bump(bump(lpp, HW), HW)) {
     const float lp0 = t[d] - lse, lp1 = t[d + 1] - lse;
     e[d] *= inv;
     e[d + 1] *= inv;
-    if (d0 + d < D) {
-      if (live) st_stream(logp + base + (size_t)d * HW, lp0);
+    if (valid(d)) {
+      if (live) st_stream(lpp, lp0);
       mean0 = fmaf(dcl[d], e[d], mean0);
       ent0 = fmaf(-e[d], lp0, ent0);
     }
-    if (d0 + d + 1 < D) {
-      if (live) st_stream(logp + base + (size_t)(d + 1) * HW, lp1);
+    if (valid(d + 1)) {
+      if (live) st_stream(lpp + HW, lp1);
       mean1 = fmaf(dcl[d + 1], e[d + 1], mean1);
       ent1 = fmaf(-e[d + 1], lp1, ent1);
     }
@@ -131,7 +138,7 @@ lsm_stats_kernel(const float* __restrict__ x, const float* __restrict__ add, int
       float* c = carry + ((size_t)b * D + d0) * h4 * w4 + (size_t)(y >> 2) * w4 + (xx >> 2);
 #pragma unroll
       for (int d = 0; d < DPT; d++)
-        if (d0 + d < D) c[(size_t)d * h4 * w4] = t[d];
+        if (valid(d)) c[(size_t)d * h4 * w4] = t[d];
     }
   }
 }
@@ -329,8 +336,14 @@ int dpv_logsoftmax_stats(const float* x, const float* add, int B, int D, int H, 
   DPV_REQUIRE(B <= 65535 && hw_img * 32 < (1ll << 31), "dpv_logsoftmax_stats: B=%d or image too large", B);
   const unsigned g = blocks_for(npix, kThreads);
 #define LAUNCH(DPT, T)                                                                                       \
-  lsm_stats_kernel<DPT, T><<<dim3(blocks_for(hw_img * T, kThreads), (unsigned)B), kThreads, 0, st>>>( \
-      x, add, D, H, W, d_candi, logp, mean, var, entropy, carry)
+  do {                                                                                                          \
+    if (D == DPT * T)                                                                                           \
+      lsm_stats_kernel<DPT, T, true><<<dim3(blocks_for(hw_img * T, kThreads), (unsigned)B), kThreads, 0, st>>>( \
+          x, add, D, H, W, d_candi, logp, mean, var, entropy, carry);                                           \
+    else                                                                                                        \
+      lsm_stats_kernel<DPT, T, false><<<dim3(blocks_for(hw_img * T, kThreads), (unsigned)B), kThreads, 0, st>>>( \
+          x, add, D, H, W, d_candi, logp, mean, var, entropy, carry);                                           \
+  } while (0)
   if (D <= 16) LAUNCH(16, 1);
   else if (D <= 32) LAUNCH(32, 1);
   else if (D <= 64) {

@@ -122,9 +122,9 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
   // ---- issue the volume loads first; the curtain geometry below overlaps their latency
   Col<NP> p;
   {
-    const float* src = vol_in + base;
+    const float* src = vol_in + base;                        // bumped by one plane per bin: one 64-bit add each
 #pragma unroll
-    for (int d = 0; d < DPT; d++) p.set(d, valid(d) ? ld_stream(src + (size_t)d * HW) : 0.f);
+    for (int d = 0; d < DPT; d++, src = bump(src, HW)) p.set(d, valid(d) ? ld_stream(src) : 0.f);
   }
   const float gt = depth[pix];
 
@@ -252,12 +252,12 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
     float* dst = vol_out + base;
     if (flags & 2) {
 #pragma unroll
-      for (int d = 0; d < DPT; d++)
-        if (valid(d)) st_stream(dst + (size_t)d * HW, p.get(d));
+      for (int d = 0; d < DPT; d++, dst = bump(dst, HW))
+        if (valid(d)) st_stream(dst, p.get(d));
     } else {
 #pragma unroll
-      for (int d = 0; d < DPT; d++)
-        if (valid(d)) st_stream(dst + (size_t)d * HW, log2f_approx(p.get(d)) * 0.6931471805599453f);
+      for (int d = 0; d < DPT; d++, dst = bump(dst, HW))
+        if (valid(d)) st_stream(dst, log2f_approx(p.get(d)) * 0.6931471805599453f);
     }
   }
   const float mean = group_sum<T>((m0.x + m0.y) + (m1.x + m1.y), gmask);
