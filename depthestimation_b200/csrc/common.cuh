@@ -56,6 +56,13 @@ __device__ __forceinline__ P* bump(P* p, unsigned n) {
   return p;
 }
 
+// 1/x on the MUFU pipe (rcp.approx.ftz: 1 ulp)
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // 2^x on the MUFU pipe (ex2.approx.ftz: 2 ulp; denormal results flush to 0)
 __device__ __forceinline__ float exp2f_approx(float x) {
   float y;

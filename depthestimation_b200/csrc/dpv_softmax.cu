@@ -45,12 +45,12 @@ lsm_stats_kernel(const float* __restrict__ x, const float* __restrict__ add, int
                  const float* __restrict__ d_candi, float* __restrict__ logp, float* __restrict__ mean_o,
                  float* __restrict__ var_o, float* __restrict__ ent_o, float* __restrict__ carry) {
   __shared__ float dc[DPT * T];
-  for (int i = threadIdx.x; i < DPT * T; i += blockDim.x) dc[i] = i < D ? d_candi[i] : 0.f;
+  for (int i = threadIdx.x; i < DPT * T; i += kThreads) dc[i] = i < D ? d_candi[i] : 0.f;
   __syncthreads();
   // grid.y = sample, grid.x covers one image: the per-pixel index arithmetic stays in 32 bits.
   // Every lane of a warp stays alive for the shuffles: out-of-range pixels are clamped and not stored.
   const unsigned HW = (unsigned)H * (unsigned)W;
-  const unsigned hw_raw = (blockIdx.x * blockDim.x + threadIdx.x) / T;
+  const unsigned hw_raw = (blockIdx.x * kThreads + threadIdx.x) / T;
   const bool live = hw_raw < HW;
   const unsigned hw = live ? hw_raw : HW - 1;
   const int tl = threadIdx.x & (T - 1);
@@ -197,7 +197,7 @@ __global__ void __launch_bounds__(kThreads)
 expectation_kernel(const float* __restrict__ dpv, int D, size_t HW, long long npix,
                    const float* __restrict__ d_candi, int bv_log, float* __restrict__ mean_o) {
   __shared__ float dc[DPT];
-  for (int i = threadIdx.x; i < DPT; i += blockDim.x) dc[i] = i < D ? d_candi[i] : 0.f;
+  for (int i = threadIdx.x; i < DPT; i += kThreads) dc[i] = i < D ? d_candi[i] : 0.f;
   __syncthreads();
   const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (pix >= npix) return;
@@ -285,7 +285,7 @@ bayes_fuse_kernel(const float* __restrict__ logp_in, const float* __restrict__ l
                   long long npix, const float* __restrict__ d_candi, int spread_iter, int spread_n,
                   float* __restrict__ logp_out, float* __restrict__ mean_out) {
   __shared__ float dc[DPT];
-  for (int i = threadIdx.x; i < DPT; i += blockDim.x) dc[i] = i < D ? d_candi[i] : 0.f;
+  for (int i = threadIdx.x; i < DPT; i += kThreads) dc[i] = i < D ? d_candi[i] : 0.f;
   __syncthreads();
   const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (pix >= npix) return;

@@ -98,19 +98,22 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
   constexpr int NP = DPT / 2;
   constexpr int STR = DPT + 4;      // lane slices of d_candi, padded: 16-byte aligned and 4 banks apart
   __shared__ __align__(16) float dc[STR * T];
-  for (int i = threadIdx.x; i < STR * T; i += blockDim.x) {
+  for (int i = threadIdx.x; i < STR * T; i += kFuseThreads) {
     const int tt = i / STR, j = i - tt * STR, d = tt * DPT + j;
     dc[i] = (j < DPT && d < D) ? d_candi[d] : 0.f;
   }
   __syncthreads();
   // grid.y = sample, grid.x covers one image: all per-pixel index arithmetic stays in 32 bits
   const unsigned HW = (unsigned)dv.H * (unsigned)dv.W;
-  const unsigned hw = (blockIdx.x * blockDim.x + threadIdx.x) / T;
-  if (hw >= HW) return;                                      // whole lane groups leave together
+  // every lane of a warp stays alive (full-mask shuffles, no divergence bookkeeping): pixels past the end of
+  // the image are clamped to the last one and not stored
+  const unsigned hw_raw = (blockIdx.x * kFuseThreads + threadIdx.x) / T;
+  const bool live = hw_raw < HW;
+  const unsigned hw = live ? hw_raw : HW - 1;
   const int lane = threadIdx.x & 31;
   const int t = lane & (T - 1);
   const int gbase = lane & ~(T - 1);
-  const unsigned gmask = (T == 32 ? 0xffffffffu : ((1u << T) - 1u)) << gbase;
+  constexpr unsigned gmask = 0xffffffffu;
   const int d0 = t * DPT;
   const float4* dc4 = reinterpret_cast<const float4*>(dc + t * STR);
   const int b = blockIdx.y;
@@ -155,20 +158,21 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
         for (int d = 0; d < DPT; d++) p.set(d, valid(d) ? fminf(fmaxf(exp2f_approx(p.get(d) * 1.4426950408889634f), eps_floor()), 1.f) : 0.f);
       }
     }
+    // g[d] = exp(-(dc-z)^2 / den) as ex2((dc-z)^2 * kk), kk = -log2(e)/den  (img_utils.py:183-186), divided once by
+    // the sensing lane; den = 0 -> kk = -inf: g = 0 (NaN at dc == z), as in the reference
+    const float mine_kk = -1.4426950408889634f / mine.den;
     const int jn = min(T, nc - c0);
 #pragma unroll 1
     for (int j = 0; j < jn; j++) {
-      Lik L = mine;
+      float Lz = mine.z, Lkk = mine_kk, LA = mine.A, LBu = mine.Bu;
       if (T > 1) {
-        L.z = __shfl_sync(gmask, mine.z, gbase + j);
-        L.den = __shfl_sync(gmask, mine.den, gbase + j);
-        L.A = __shfl_sync(gmask, mine.A, gbase + j);
-        L.Bu = __shfl_sync(gmask, mine.Bu, gbase + j);
+        Lz = __shfl_sync(gmask, mine.z, gbase + j);
+        Lkk = __shfl_sync(gmask, mine_kk, gbase + j);
+        LA = __shfl_sync(gmask, mine.A, gbase + j);
+        LBu = __shfl_sync(gmask, mine.Bu, gbase + j);
       }
-      // ---- likelihood of this curtain over the depth bins (mixed_model, light_curtain.py:247-252):
-      // g[d] = exp(-(dc-z)^2 / den) as ex2((dc-z)^2 * kk), kk = -log2(e)/den  (img_utils.py:183-186);
-      // den = 0 -> kk = -inf: g = 0 (NaN at dc == z), as in the reference
-      const float2 kk2 = splat2(-1.4426950408889634f / L.den), nz2 = splat2(-L.z);
+      // ---- likelihood of this curtain over the depth bins (mixed_model, light_curtain.py:247-252)
+      const float2 kk2 = splat2(Lkk), nz2 = splat2(-Lz);
       Col<NP> g;
       float2 a0 = splat2(0.f), a1 = splat2(0.f);
 #pragma unroll
@@ -183,23 +187,29 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
         a0 = __fadd2_rn(a0, g.v[k]);
         a1 = __fadd2_rn(a1, g.v[k + 1]);
       }
-      const float sg = group_sum<T>((a0.x + a0.y) + (a1.x + a1.y), gmask);
+      const float sgl = (a0.x + a0.y) + (a1.x + a1.y);       // this lane's share of sum(g)
+      const float sg = group_sum<T>(sgl, gmask);
       // sg == 0 or NaN: g/sg is NaN -> -1 in every bin -> constant mixture -> uniform likelihood -> no-op
       bool ok = sg > 0.f;
-      const float2 As2 = splat2(L.A / sg), Bu2 = splat2(L.Bu);
-      a0 = splat2(0.f); a1 = splat2(0.f);
+      // m = soft * A + uni * B before its clamp at 0 (kept signed: the floor eps*sm below is positive, so
+      // max(m, eps*sm) == max(max(m, 0), eps*sm)); sum(max(m, 0)) = (sum(m) + sum|m|) / 2 with sum(m) in closed form
+      const float As = LA * rcp_approx(sg);
+      const float2 As2 = splat2(As), Bu2 = splat2(LBu);
+      float b0 = 0.f, b1 = 0.f;
+      int nvalid = 0;
 #pragma unroll
-      for (int k = 0; k < NP; k += 2) {                      // clamp(soft * A + uni * B, 0, inf)
-        float2 m0 = __ffma2_rn(g.v[k], As2, Bu2), m1 = __ffma2_rn(g.v[k + 1], As2, Bu2);
-        m0 = make_float2(valid(2 * k) ? fmaxf(m0.x, 0.f) : 0.f, valid(2 * k + 1) ? fmaxf(m0.y, 0.f) : 0.f);
-        m1 = make_float2(valid(2 * k + 2) ? fmaxf(m1.x, 0.f) : 0.f, valid(2 * k + 3) ? fmaxf(m1.y, 0.f) : 0.f);
-        g.v[k] = m0;
-        g.v[k + 1] = m1;
-        a0 = __fadd2_rn(a0, m0);
-        a1 = __fadd2_rn(a1, m1);
+      for (int k = 0; k < NP; k++) {
+        float2 m = __ffma2_rn(g.v[k], As2, Bu2);
+        if (!valid(2 * k)) m.x = 0.f; else nvalid++;
+        if (!valid(2 * k + 1)) m.y = 0.f; else nvalid++;
+        g.v[k] = m;
+        b0 += fabsf(m.x);
+        b1 += fabsf(m.y);
       }
-      const float sm = group_sum<T>((a0.x + a0.y) + (a1.x + a1.y), gmask);
+      const float sml = 0.5f * (fmaf(As, sgl, (float)nvalid * LBu) + (b0 + b1));
+      const float sm = group_sum<T>(sml, gmask);
       ok = ok && (sm > 0.f);                                 // 0/0 in every bin -> NaN -> 0 -> eps: uniform again
+      float sl = 0.f;
       if (ok) {
         // models.py:1109-1112: p *= clamp(m / sm, eps, 1), renormalise.  Everything here is homogeneous in p,
         // so the common factor 1/sm is left to the final renormalisation: p *= max(m, eps * sm); m <= sm
@@ -213,12 +223,13 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
           a0 = __fadd2_rn(a0, p.v[k]);
           a1 = __fadd2_rn(a1, p.v[k + 1]);
         }
-        const float s = group_sum<T>((a0.x + a0.y) + (a1.x + a1.y), gmask);
-        if (s < 1e-12f || s > 1e12f) {                       // rescale only to stay inside fp32 range
-          const float2 inv2 = splat2(1.f / s);
+        sl = (a0.x + a0.y) + (a1.x + a1.y);
+      }
+      const float s = group_sum<T>(sl, gmask);               // outside the branch: the whole warp shuffles
+      if (ok && (s < 1e-12f || s > 1e12f)) {                 // rescale only to stay inside fp32 range
+        const float2 inv2 = splat2(1.f / s);
 #pragma unroll
-          for (int k = 0; k < NP; k++) p.v[k] = __fmul2_rn(p.v[k], inv2);
-        }
+        for (int k = 0; k < NP; k++) p.v[k] = __fmul2_rn(p.v[k], inv2);
       }
     }
     c0 += T;
@@ -253,15 +264,15 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
     if (flags & 2) {
 #pragma unroll
       for (int d = 0; d < DPT; d++, dst = bump(dst, HW))
-        if (valid(d)) st_stream(dst, p.get(d));
+        if (valid(d) && live) st_stream(dst, p.get(d));
     } else {
 #pragma unroll
       for (int d = 0; d < DPT; d++, dst = bump(dst, HW))
-        if (valid(d)) st_stream(dst, log2f_approx(p.get(d)) * 0.6931471805599453f);
+        if (valid(d) && live) st_stream(dst, log2f_approx(p.get(d)) * 0.6931471805599453f);
     }
   }
   const float mean = group_sum<T>((m0.x + m0.y) + (m1.x + m1.y), gmask);
-  if (mean_out && t == 0) mean_out[pix] = mean;
+  if (mean_out && t == 0 && live) mean_out[pix] = mean;
 }
 
 }  // namespace dpv
