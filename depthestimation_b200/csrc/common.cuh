@@ -56,6 +56,12 @@ __device__ __forceinline__ P* bump(P* p, unsigned n) {
   return p;
 }
 
+// x, with its value hidden from the optimiser (keeps an operand substitution ahead of a division in place)
+__device__ __forceinline__ float opaque(float x) {
+  asm("" : "+f"(x));
+  return x;
+}
+
 // 1/x on the MUFU pipe (rcp.approx.ftz: 1 ulp)
 __device__ __forceinline__ float rcp_approx(float x) {
   float y;

@@ -17,12 +17,15 @@
 
 namespace dpv {
 
-constexpr int kFuseThreads = 128;
+#ifndef DPV_FUSE_THREADS
+#define DPV_FUSE_THREADS 128
+#endif
+constexpr int kFuseThreads = DPV_FUSE_THREADS;
 constexpr int kMaxCurtains = 8;
 #ifndef DPV_FUSE_BLOCKS16
 #define DPV_FUSE_BLOCKS16 8
 #endif
-constexpr int kFuseBlocks16 = DPV_FUSE_BLOCKS16;   // resident CTAs per SM asked for when a lane holds 16 bins
+constexpr int kFuseBlocks16 = DPV_FUSE_BLOCKS16 * 128 / DPV_FUSE_THREADS;   // resident CTAs per SM asked for when a lane holds 16 bins
 
 __device__ __forceinline__ float2 splat2(float a) { return make_float2(a, a); }
 
@@ -90,7 +93,7 @@ __device__ __forceinline__ void spread_pass(Col<DPT / 2>& p, int d0, int D, int 
 }
 
 template <int DPT, int T, int HALF, bool FULL>
-__global__ void __launch_bounds__(kFuseThreads, DPT <= 16 ? kFuseBlocks16 : 4)
+__global__ void __launch_bounds__(kFuseThreads, DPT <= 16 ? kFuseBlocks16 : 4 * 128 / kFuseThreads)
 sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float* __restrict__ depth,
                   const float* __restrict__ planes, const float* __restrict__ noise, int nc,
                   const float* __restrict__ d_candi, int D, int spread_iter, int flags,
@@ -103,22 +106,23 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
     dc[i] = (j < DPT && d < D) ? d_candi[d] : 0.f;
   }
   __syncthreads();
-  // grid.y = sample, grid.x covers one image: all per-pixel index arithmetic stays in 32 bits
+  // grid = (column chunks, rows, samples): no per-thread integer division, all pixel indices in 32 bits.
+  // Every lane of a warp stays alive (full-mask shuffles, no divergence bookkeeping): columns past the end of
+  // the row are clamped to the last one and not stored
   const unsigned HW = (unsigned)dv.H * (unsigned)dv.W;
-  // every lane of a warp stays alive (full-mask shuffles, no divergence bookkeeping): pixels past the end of
-  // the image are clamped to the last one and not stored
-  const unsigned hw_raw = (blockIdx.x * kFuseThreads + threadIdx.x) / T;
-  const bool live = hw_raw < HW;
-  const unsigned hw = live ? hw_raw : HW - 1;
+  const int u_raw = (int)(blockIdx.x * (kFuseThreads / T) + threadIdx.x / T);
+  const bool live = u_raw < dv.W;
+  const int u = live ? u_raw : dv.W - 1;
+  const int v = (int)blockIdx.y;
+  const unsigned hw = (unsigned)v * (unsigned)dv.W + (unsigned)u;
   const int lane = threadIdx.x & 31;
   const int t = lane & (T - 1);
   const int gbase = lane & ~(T - 1);
   constexpr unsigned gmask = 0xffffffffu;
   const int d0 = t * DPT;
   const float4* dc4 = reinterpret_cast<const float4*>(dc + t * STR);
-  const int b = blockIdx.y;
+  const int b = blockIdx.z;
   const size_t pix = (size_t)b * HW + hw;
-  const int v = (int)(hw / (unsigned)dv.W), u = (int)(hw - (unsigned)v * (unsigned)dv.W);
   const size_t base = ((size_t)b * D + d0) * HW + hw;
   auto valid = [&](int d) -> bool { return FULL || d0 + d < D; };
 
@@ -132,11 +136,12 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
   const float gt = depth[pix];
 
   int c0 = 0;
+  int unchecked = (flags & 4) ? 0 : 1;                       // multiplications since the column's total was last seen
 #pragma unroll 1
   do {
     // ---- sensing: in rounds of T curtains, lane t of the group senses curtain c0 + t (all lanes busy, same code)
     Lik mine;
-    mine.z = 0.f; mine.den = 0.f; mine.A = 0.f; mine.Bu = 0.f;
+    mine.z = 0.f; mine.den = 1.f; mine.A = 0.f; mine.Bu = 0.f;      // idle lane: never broadcast
     if (c0 + t < nc) {
       const int cu = b * nc + c0 + t;
       const float4* P4 = reinterpret_cast<const float4*>(planes + ((size_t)cu * dv.W + u) * 12);
@@ -150,7 +155,9 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
       mine = lik_params(r, gt, D);
     }
     if (c0 == 0) {                                           // models.py:1097 (after the loads have landed)
-      if (flags & 1) {
+      if (flags & 4) {
+        // the caller's own output of the previous iteration: already inside [eps, 1]
+      } else if (flags & 1) {
 #pragma unroll
         for (int d = 0; d < DPT; d++) p.set(d, valid(d) ? fminf(fmaxf(p.get(d), eps_floor()), 1.f) : 0.f);
       } else {
@@ -160,7 +167,10 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
     }
     // g[d] = exp(-(dc-z)^2 / den) as ex2((dc-z)^2 * kk), kk = -log2(e)/den  (img_utils.py:183-186), divided once by
     // the sensing lane; den = 0 -> kk = -inf: g = 0 (NaN at dc == z), as in the reference
-    const float mine_kk = -1.4426950408889634f / mine.den;
+    // (an un-sensed pixel has den == 0: answered without the division's special-case path)
+    const bool den_pos = mine.den > 0.f;
+    const float kk_q = -1.4426950408889634f / opaque(den_pos ? mine.den : 1.f);
+    const float mine_kk = den_pos ? kk_q : (mine.den == 0.f ? -INFINITY : NAN);   // den = 2 sigma^2 is never -0
     const int jn = min(T, nc - c0);
 #pragma unroll 1
     for (int j = 0; j < jn; j++) {
@@ -209,27 +219,33 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
       const float sml = 0.5f * (fmaf(As, sgl, (float)nvalid * LBu) + (b0 + b1));
       const float sm = group_sum<T>(sml, gmask);
       ok = ok && (sm > 0.f);                                 // 0/0 in every bin -> NaN -> 0 -> eps: uniform again
-      float sl = 0.f;
       if (ok) {
         // models.py:1109-1112: p *= clamp(m / sm, eps, 1), renormalise.  Everything here is homogeneous in p,
         // so the common factor 1/sm is left to the final renormalisation: p *= max(m, eps * sm); m <= sm
         // already bounds the ratio by 1.
         const float esm = eps_floor() * sm;
+#pragma unroll
+        for (int k = 0; k < NP; k++)
+          p.v[k] = __fmul2_rn(p.v[k], make_float2(fmaxf(g.v[k].x, esm), fmaxf(g.v[k].y, esm)));
+      }
+      // One multiplication shrinks a column's total by at most eps (and grows it by at most sm <= 3), so a column
+      // that starts normalised (largest bin >= 1/D) stays inside fp32 range over two of them; its total is looked
+      // at, and rescaled if it left [1e-12, 1e12], after every second one (after the first one too when the input
+      // is not known to be normalised).
+      if (++unchecked >= 2) {
+        unchecked = 0;
         a0 = splat2(0.f); a1 = splat2(0.f);
 #pragma unroll
         for (int k = 0; k < NP; k += 2) {
-          p.v[k] = __fmul2_rn(p.v[k], make_float2(fmaxf(g.v[k].x, esm), fmaxf(g.v[k].y, esm)));
-          p.v[k + 1] = __fmul2_rn(p.v[k + 1], make_float2(fmaxf(g.v[k + 1].x, esm), fmaxf(g.v[k + 1].y, esm)));
           a0 = __fadd2_rn(a0, p.v[k]);
           a1 = __fadd2_rn(a1, p.v[k + 1]);
         }
-        sl = (a0.x + a0.y) + (a1.x + a1.y);
-      }
-      const float s = group_sum<T>(sl, gmask);               // outside the branch: the whole warp shuffles
-      if (ok && (s < 1e-12f || s > 1e12f)) {                 // rescale only to stay inside fp32 range
-        const float2 inv2 = splat2(1.f / s);
+        const float s = group_sum<T>((a0.x + a0.y) + (a1.x + a1.y), gmask);
+        if (s < 1e-12f || s > 1e12f) {
+          const float2 inv2 = splat2(1.f / s);
 #pragma unroll
-        for (int k = 0; k < NP; k++) p.v[k] = __fmul2_rn(p.v[k], inv2);
+          for (int k = 0; k < NP; k++) p.v[k] = __fmul2_rn(p.v[k], inv2);
+        }
       }
     }
     c0 += T;
@@ -252,8 +268,10 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
   for (int k = 0; k < NP; k += 2) {
     const float4 q = dc4[k >> 1];
     float2 c0v = __fmul2_rn(p.v[k], inv2), c1v = __fmul2_rn(p.v[k + 1], inv2);
-    c0v = make_float2(fminf(fmaxf(c0v.x, eps_floor()), 1.f), fminf(fmaxf(c0v.y, eps_floor()), 1.f));
-    c1v = make_float2(fminf(fmaxf(c1v.x, eps_floor()), 1.f), fminf(fmaxf(c1v.y, eps_floor()), 1.f));
+    // clamp(., eps, 1): the upper bound cannot bind -- a sum of positive floats is >= each term, and
+    // x * fl(1/x) <= 1 + 2^-24 rounds to 1 (ties to even)
+    c0v = make_float2(fmaxf(c0v.x, eps_floor()), fmaxf(c0v.y, eps_floor()));
+    c1v = make_float2(fmaxf(c1v.x, eps_floor()), fmaxf(c1v.y, eps_floor()));
     p.v[k] = c0v;
     p.v[k + 1] = c1v;
     m0 = __ffma2_rn(make_float2(q.x, q.y), c0v, m0);         // d_candi is 0 in the padding bins
@@ -289,14 +307,16 @@ extern "C" int lc_sense_fuse(const LcDevice* dev, const float* logp_in, const fl
               "lc_sense_fuse: spread_n=%d not in {1,3,5,7}", spread_n);
   DPV_REQUIRE(D <= 128, "lc_sense_fuse: D=%d > 128 unsupported", D);
   DPV_REQUIRE(((uintptr_t)planes & 15) == 0, "lc_sense_fuse: planes must be 16-byte aligned");
-  DPV_REQUIRE((flags & ~3) == 0, "lc_sense_fuse: unknown flags %d", flags);
+  DPV_REQUIRE((flags & ~7) == 0, "lc_sense_fuse: unknown flags %d", flags);
+  DPV_REQUIRE(!(flags & 4) || (flags & 1), "lc_sense_fuse: LC_FUSE_IN_CLAMPED needs LC_FUSE_IN_PROB");
   const long long hw_img = (long long)dev->H * dev->W;
-  DPV_REQUIRE(B <= 65535 && hw_img * 32 < (1ll << 31), "lc_sense_fuse: B=%d or image too large", B);
+  DPV_REQUIRE(B <= 65535 && dev->H <= 65535 && hw_img * 32 < (1ll << 31), "lc_sense_fuse: B=%d or image too large", B);
   cudaStream_t st = (cudaStream_t)stream;
   const int half = spread_iter == 0 ? 0 : spread_n / 2;
 #define LAUNCH4(DPT, T, HALF, FULL)                                                                                \
   sense_fuse_kernel<DPT, T, HALF, FULL>                                                                            \
-      <<<dim3((unsigned)((hw_img * T + kFuseThreads - 1) / kFuseThreads), (unsigned)B), kFuseThreads, 0, st>>>(    \
+      <<<dim3((unsigned)((dev->W * T + kFuseThreads - 1) / kFuseThreads), (unsigned)dev->H, (unsigned)B),         \
+         kFuseThreads, 0, st>>>(                                                                                   \
           dev->view, logp_in, depth, planes, noise, nc, d_candi, D, spread_iter, flags, logp_out, mean_out)
 #define LAUNCH3(DPT, T, HALF)                        \
   do {                                               \

@@ -26,6 +26,21 @@ __device__ __forceinline__ void intersect(const float* P, float rx, float ry, fl
 __device__ __forceinline__ Ret sense_pixel(const LcDeviceView& dv, const float* __restrict__ P, int u, int v,
                                            float zval, const float* noise) {
   Ret r;
+  // A column without a design point carries a NaN centre plane and all-zero thickness planes
+  // (curtain_planes_kernel): every quotient below is then NaN and the pixel has no return.  Same result without
+  // sending three divisions and a double-precision square root down their NaN slow paths.
+  {
+    const bool nan0 = (P[0] != P[0]) || (P[1] != P[1]) || (P[2] != P[2]) || (P[3] != P[3]);
+    bool zero12 = true;
+#pragma unroll
+    for (int k = 4; k < 12; k++) zero12 = zero12 && (P[k] == 0.f);
+    if (nan0 && zero12) {
+      r.x = r.y = r.z = NAN;
+      r.inten = 0.f;
+      r.thick = NAN;
+      return r;
+    }
+  }
   const float rx = dv.nn_x[u], ry = dv.nn_y[v];
   float c[3], bot[3], top[3];
   intersect(P, rx, ry, 1.0f, c);
@@ -70,6 +85,25 @@ struct Lik {
   float A, Bu;  // mixture weight, (1-A) * (1/D)
 };
 
+// a / b for a finite b > 0, rounded like the IEEE division, with a zero numerator answered directly (+-0 / b = +-0):
+// 0 / b goes through the division's special-case path (FCHK), and un-sensed pixels (most of the image) have exactly that
+__device__ __forceinline__ float div_zero_fast(float a, float b) {
+  const bool z = a == 0.f;
+  const float q = opaque(z ? b : a) / b;      // opaque: the compiler otherwise divides a itself and selects after
+  return z ? a : q;
+}
+
+// it / 255 for the integer intensities 0..255 the simulator emits (dprocessor.cpp:990): reciprocal, one Newton
+// step, one residual correction -- the division's own fast path, correctly rounded for all 256 values (checked
+// exhaustively on the host), without its special-case path for it == 0
+__device__ __forceinline__ float div255(float it) {
+  if (!(it >= 0.f && it <= 255.f)) return it / 255.0f;
+  const float rc0 = 1.0f / 255.0f;
+  const float rc = fmaf(fmaf(-255.f, rc0, 1.f), rc0, rc0);
+  const float q = it * rc;
+  return fmaf(fmaf(-255.f, q, it), rc, q);
+}
+
 __device__ __forceinline__ Lik lik_params(const Ret& r, float gt, int D) {
   float z = r.z, th = r.thick, it = r.inten;
   if (r.x != r.x) { z = 0.f; it = 0.f; }            // light_curtain.py:847 (whole pixel -> 0)
@@ -78,7 +112,7 @@ __device__ __forceinline__ Lik lik_params(const Ret& r, float gt, int D) {
   z = z * mask;
   th = th * mask;
   it = it * mask;
-  const float x = it / 255.0f;
+  const float x = div255(it);
   // mapping(), light_curtain.py:228-244 (m = 20, f = 0.5)
   float A;
   if (x > 0.5f) {
@@ -90,9 +124,9 @@ __device__ __forceinline__ Lik lik_params(const Ret& r, float gt, int D) {
   }
   Lik L;
   L.z = z;
-  const float t10 = th / 10.0f;
+  const float t10 = div_zero_fast(th, 10.0f);
   const float var = t10 * t10;
-  const float sg = sqrtf(var);
+  const float sg = var == 0.f ? var : sqrtf(opaque(var == 0.f ? 1.f : var));     // sqrt(+-0) = +-0, off the slow path
   L.den = 2.f * (sg * sg);
   L.A = A;
   L.Bu = (1.0f / (float)D) * (1.f - A);

@@ -82,7 +82,8 @@ def lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n,
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
     dev.sense_fuse(state.logp, depth, state.planes, nc, lc.d_candi, spread_iter, spread_n, noise=noise,
-                   out=state.logp, mean=state.mean, in_prob=in_prob, out_prob=out_prob)
+                   out=state.logp, mean=state.mean, in_prob=in_prob, out_prob=out_prob,
+                   in_clamped=in_prob)           # a probability volume here is the previous iteration's own output
     if events is not None:
         e1.record()
         events.append((e0, e1))

@@ -158,9 +158,12 @@ int lc_sense_likelihood(const LcDevice* dev, const float* planes, const float* d
  * volume is materialised.  logp_in [B,D,H,W], depth [B,H,W], planes [B,nc,W,12]
  *   -> logp_out [B,D,H,W] (may alias logp_in), mean_out (nullable) [B,H,W].
  * flags: 0 = log-probability in and out (the reference's format); LC_FUSE_IN_PROB / LC_FUSE_OUT_PROB keep the
- * volume as clamped probability between the iterations of one lc_process call (no exp/log per bin). */
+ * volume as clamped probability between the iterations of one lc_process call (no exp/log per bin);
+ * LC_FUSE_IN_CLAMPED (with LC_FUSE_IN_PROB) promises that the input is a previous call's LC_FUSE_OUT_PROB output,
+ * i.e. already inside [eps, 1], so the entry clamp of models.py:1097 is the identity and is not evaluated. */
 #define LC_FUSE_IN_PROB 1
 #define LC_FUSE_OUT_PROB 2
+#define LC_FUSE_IN_CLAMPED 4
 int lc_sense_fuse(const LcDevice* dev, const float* logp_in, const float* depth, const float* planes,
                   const float* noise, int B, int nc, const float* d_candi, int D, int spread_iter,
                   int spread_n, int flags, float* logp_out, float* mean_out, void* stream);

@@ -1,4 +1,4 @@
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -m gpu -q -x > gpurun_out/tests.log 2>&1; echo "tests rc=$?" >> gpurun_out/tests.log
-timeout 300 python profiles/kbench.py C2_mono_lc_b8 7 > gpurun_out/kbench.log 2>&1
-tail -2 gpurun_out/tests.log; cat gpurun_out/kbench.log
+tail -2 gpurun_out/tests.log
+TAG=noskip timeout 200 python profiles/fuse_bench.py 2>&1 | tail -1
