@@ -1,7 +1,6 @@
 """B200-native stand-in for the lcsim Python surface the DPV path uses:
 external/lcsim/python/sim.py:29-211 (LCDevice), planner.py:162-189 (PlannerRT) and the two
-pylc_lib functions bound at pylc_lib.cpp:114-251 (generateCameraAngles; transformPoints is only
-reached for rTc != I sensors and is a "next" row).  Same constructor dictionaries, same method
+pylc_lib functions bound at pylc_lib.cpp:114-251 (generateCameraAngles, transformPoints).  Same constructor dictionaries, same method
 names; arrays may be numpy (copied to the GPU) or CUDA tensors (used in place).
 """
 import ctypes
@@ -30,6 +29,52 @@ def generateCameraAngles(K, dist, w, h):
     out = np.zeros(int(w), np.float32)
     check(lib().lc_camera_angles(_hp(K), int(w), int(h), _hp(out)))
     return [float(v) for v in out]        # pybind11 hands std::vector<float> back as Python floats
+
+
+def transform_points(pts, thick, intr, M, width, height, filtering=0):
+    """Batched Depth::transformPoints (depth.cpp:143-222) on the GPU: pts [n,N,4], thick [n,N] (CUDA tensors or arrays),
+    intr [3,3], M [4,4] (host) -> maps [n,3,height,width] = (depth, intensity, thickness)."""
+    pts = f32(pts)
+    dev = pts.device
+    thick = f32(thick, dev).reshape(pts.shape[0], pts.shape[1])
+    n, N = int(pts.shape[0]), int(pts.shape[1])
+    K, T = _host_f32(intr).reshape(3, 3), _host_f32(M).reshape(4, 4)
+    maps = torch.empty(n, 3, int(height), int(width), device=dev, dtype=torch.float32)
+    nbytes = int(lib().lc_transform_points_scratch_bytes(n, int(width), int(height), int(filtering)))
+    scratch = torch.empty((nbytes + 7) // 8, device=dev, dtype=torch.int64)
+    with torch.cuda.device(dev):
+        check(lib().lc_transform_points(ptr(pts), ptr(thick), n, N, _hp(K), _hp(T), int(width), int(height),
+                                        int(filtering), ptr(maps), scratch.data_ptr(), nbytes, stream_ptr(dev)))
+    return maps
+
+
+def transformPoints(pts, thick, intr, M, width, height, params):
+    """pylc_lib.transformPoints (pylc_lib.cpp binding of depth.cpp:143-222): pts [N,4], thick [N] ->
+    (depth, intensity, thickness) maps [height,width]; numpy in -> numpy out, CUDA tensors in -> CUDA tensors out."""
+    as_numpy = not torch.is_tensor(pts)
+    p = f32(pts).reshape(1, -1, 4)
+    maps = transform_points(p, f32(thick, p.device).reshape(1, -1), intr, M, width, height,
+                            int(params.get("filtering", 0)))[0]
+    if as_numpy:
+        maps = maps.cpu().numpy()
+    return maps[0], maps[1], maps[2]
+
+
+def sweep_sample(sampling_depth, feat_z, feat_int, want_inds=False):
+    """models/models.py:924-927: sampling_depth [B,nc,H,W], feat_z / feat_int [B,K,H,W] -> intensities [B,nc,H,W]
+    of the sweep slice nearest in depth (and its index)."""
+    sd = f32(sampling_depth)
+    dev = sd.device
+    fz, fi = f32(feat_z, dev), f32(feat_int, dev)
+    B, nc, H, W = sd.shape
+    K = fz.shape[1]
+    if tuple(fz.shape) != (B, K, H, W) or tuple(fi.shape) != (B, K, H, W):
+        raise ValueError("sweep_sample: feat_z / feat_int must be [B,K,H,W] matching sampling_depth [B,nc,H,W]")
+    out = torch.empty_like(sd)
+    inds = torch.empty(B, nc, H, W, device=dev, dtype=torch.int32) if want_inds else None
+    with torch.cuda.device(dev):
+        check(lib().lc_sweep_sample(ptr(sd), ptr(fz), ptr(fi), B, nc, K, H, W, ptr(out), ptr(inds), stream_ptr(dev)))
+    return (out, inds) if want_inds else out
 
 
 class LCDevice:

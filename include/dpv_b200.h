@@ -168,6 +168,24 @@ int lc_sense_fuse(const LcDevice* dev, const float* logp_in, const float* depth,
                   const float* noise, int B, int nc, const float* d_candi, int D, int spread_iter,
                   int spread_n, int flags, float* logp_out, float* mean_out, void* stream);
 
+/* ---- real-sensor steps either side of the fusion -------------------------------------- */
+
+/* pylc.transformPoints = Depth::transformPoints (external/lcsim/lcsim/src/depth.cpp:143-222; bound at
+ * pylc_lib.cpp; called by lc/light_curtain.py:751,:831 and transform_measurement :1076-1089): n point sets
+ * pts [n,N,4] (x,y,z,intensity in the light-curtain camera), thick [n,N], intr host[3x3] (target camera), M host[4x4]
+ * (source -> target camera)  ->  maps [n,3,height,width] = (depth, intensity, thickness) of the nearest point per
+ * pixel (0 where none), pixels failing the `filtering`-neighbourhood outlier test zeroed (0 = no filter).
+ * scratch: device memory of lc_transform_points_scratch_bytes(...) bytes, 8-byte aligned, owned by the caller. */
+size_t lc_transform_points_scratch_bytes(int n, int width, int height, int filtering);
+int lc_transform_points(const float* pts, const float* thick, int n, int N, const float* intr, const float* M,
+                        int width, int height, int filtering, float* maps, void* scratch, size_t scratch_bytes,
+                        void* stream);
+/* BaseModel.lc_process_real's sampling of a recorded sweep (models/models.py:924-927):
+ * sampling_depth [B,nc,H,W], feat_z / feat_int [B,K,H,W] -> out [B,nc,H,W] = feat_int at the slice whose depth is
+ * nearest to sampling_depth (torch.argmin semantics: first minimum, NaN first), inds (nullable) [B,nc,H,W]. */
+int lc_sweep_sample(const float* sampling_depth, const float* feat_z, const float* feat_int, int B, int nc, int K,
+                    int H, int W, float* out, int32_t* inds, void* stream);
+
 /* ---- callers either side of the fused path ----------------------------- */
 
 /* img_utils.gen_dpv_withmask (utils/img_utils.py:567-582): soft label of variance `var` around dmaps where

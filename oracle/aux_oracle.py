@@ -159,3 +159,20 @@ def pose_matrix(vec, rotation_mode="euler"):
                            2 * w * z + 2 * x * y, w * w - x * x + y * y - z * z, 2 * y * z - 2 * w * x,
                            2 * x * z - 2 * w * y, 2 * w * x + 2 * y * z, w * w - x * x - y * y + z * z], 1).reshape(B, 3, 3)
     return torch.cat([rot, tr], 2)
+
+
+def sweep_sample(sampling_depth, feat_z, feat_int):
+    """models/models.py:924-926 (lc_process_real), per sample and curtain:
+    inds = argmin_k |sampling_depth - feat_z[k]| ; result = gather(feat_int, 0, inds).
+    sampling_depth [B,nc,H,W], feat_z / feat_int [B,K,H,W] -> (result [B,nc,H,W], inds [B,nc,H,W])."""
+    sd = torch.as_tensor(np.asarray(sampling_depth), dtype=torch.float32)
+    fz = torch.as_tensor(np.asarray(feat_z), dtype=torch.float32)
+    fi = torch.as_tensor(np.asarray(feat_int), dtype=torch.float32)
+    B, nc = sd.shape[:2]
+    res, ind = torch.empty_like(sd), torch.empty(sd.shape, dtype=torch.int64)
+    for b in range(B):
+        for c in range(nc):
+            inds = torch.argmin(torch.abs(sd[b, c].reshape(1, sd.shape[2], sd.shape[3]) - fz[b]), dim=0)
+            res[b, c] = torch.gather(fi[b], 0, inds.unsqueeze(0)).squeeze(0)
+            ind[b, c] = inds
+    return res, ind

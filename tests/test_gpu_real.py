@@ -1,0 +1,113 @@
+"""GPU parity for the real-sensor steps either side of the fusion, through the C ABI, against the CPU
+oracle: Depth::transformPoints (z-buffer re-projection, bit-exact: it is index / comparison work on values both sides
+compute with the same fp32 operations) and the sweep sampling of lc_process_real (bit-exact: argmin + gather)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import aux_oracle as A
+from oracle import lcsim as OL
+
+pytestmark = pytest.mark.gpu
+
+
+def _rig():
+    W, H = 160, 96
+    K = np.array([[140., 0., 79.5], [0., 140., 47.5], [0., 0., 1.]], np.float32)
+    a = np.radians(1.5)
+    M = np.eye(4, dtype=np.float32)
+    M[:3, :3] = np.array([[np.cos(a), 0., np.sin(a)], [0., 1., 0.], [-np.sin(a), 0., np.cos(a)]], np.float32)
+    M[:3, 3] = [0.05, -0.02, 0.03]
+    return W, H, K, M
+
+
+def _points(rng, n_sets, W, H, K):
+    """A curtain-like return per set: one point per pixel of an LC image (NaN / zero rows where nothing came back),
+    plus exact duplicates so that several points tie in depth on one pixel."""
+    us, vs = np.meshgrid(np.arange(W, dtype=np.float32), np.arange(H, dtype=np.float32))
+    sets, thick = [], []
+    for s in range(n_sets):
+        z = (6. + 3. * np.sin(us / 23. + s) + rng.uniform(0, 4., size=us.shape) * (rng.uniform(size=us.shape) < 0.2))
+        z = z.astype(np.float32)
+        x = (us - K[0, 2]) / K[0, 0] * z
+        y = (vs - K[1, 2]) / K[1, 1] * z
+        it = np.floor(rng.uniform(0, 256, size=us.shape)).astype(np.float32)
+        p = np.stack([x, y, z, it], -1).reshape(-1, 4).astype(np.float32)
+        th = rng.uniform(0.05, 2.0, size=p.shape[0]).astype(np.float32)
+        dead = rng.uniform(size=p.shape[0]) < 0.15
+        p[dead] = 0.                                        # output_lc[np.isnan(...)] = 0 (models.py:918-919)
+        p[rng.uniform(size=p.shape[0]) < 0.02, :3] = np.nan
+        p[rng.uniform(size=p.shape[0]) < 0.01, 2] = -3.     # behind the camera
+        dup = rng.integers(0, p.shape[0], size=p.shape[0] // 8)
+        p = np.concatenate([p, p[dup] * np.array([1, 1, 1, 0.5], np.float32)], 0)
+        th = np.concatenate([th, th[dup] + 1.], 0)
+        sets.append(p)
+        thick.append(th)
+    return np.stack(sets), np.stack(thick)
+
+
+@pytest.mark.parametrize("filtering", [0, 1, 2])
+def test_transform_points_bit_exact(filtering):
+    from depthestimation_b200 import lcsim
+    rng = np.random.default_rng(3 + filtering)
+    W, H, K, M = _rig()
+    pts, thick = _points(rng, 3, W, H, K)
+    maps = lcsim.transform_points(torch.as_tensor(pts).cuda(), torch.as_tensor(thick).cuda(), K, M, W, H, filtering)
+    maps = maps.cpu().numpy()
+    for s in range(pts.shape[0]):
+        d, i, t = OL.transformPoints(pts[s], thick[s], K, M, W, H, {"filtering": filtering})
+        assert (d != 0).mean() > 0.3                          # the case exercises the z-buffer
+        np.testing.assert_array_equal(maps[s, 0], d)
+        np.testing.assert_array_equal(maps[s, 1], i)
+        np.testing.assert_array_equal(maps[s, 2], t)
+
+
+def test_transform_points_pylc_surface_numpy_roundtrip():
+    from depthestimation_b200 import lcsim
+    rng = np.random.default_rng(11)
+    W, H, K, M = _rig()
+    pts, thick = _points(rng, 1, W, H, K)
+    d, i, t = lcsim.transformPoints(pts[0], thick[0], K, M, W, H, {"filtering": 0})
+    assert isinstance(d, np.ndarray) and d.shape == (H, W)
+    od, oi, ot = OL.transformPoints(pts[0], thick[0], K, M, W, H, {"filtering": 0})
+    np.testing.assert_array_equal(d, od)
+    np.testing.assert_array_equal(i, oi)
+    np.testing.assert_array_equal(t, ot)
+
+
+def test_transform_points_identity_is_the_image_itself():
+    """Property at full size: with M = I and the LC camera's own intrinsics every pixel centre re-projects onto
+    (int)(u + 1.0 - 0.5) = u, so the depth map comes back unchanged (no z-buffer collisions)."""
+    from depthestimation_b200 import lcsim
+    W, H = 768, 256
+    K = np.array([[454., 0., 384.], [0., 533., 128.], [0., 0., 1.]], np.float32)
+    us, vs = np.meshgrid(np.arange(W, dtype=np.float64), np.arange(H, dtype=np.float64))
+    z = 5. + 30. * ((us * 7 + vs * 13) % 97) / 97.
+    # projections at u + 1.0 so that the truncation in (int)(p - 0.5) is far from a boundary
+    p = np.stack([(us + 1.0 - K[0, 2]) / K[0, 0] * z, (vs + 1.0 - K[1, 2]) / K[1, 1] * z, z, us % 256], -1)
+    p = p.reshape(1, -1, 4).astype(np.float32)
+    th = np.full((1, p.shape[1]), 0.7, np.float32)
+    maps = lcsim.transform_points(torch.as_tensor(p).cuda(), torch.as_tensor(th).cuda(), K, np.eye(4), W, H, 0)
+    maps = maps.cpu().numpy()
+    np.testing.assert_array_equal(maps[0, 0], p[0, :, 2].reshape(H, W))
+    np.testing.assert_array_equal(maps[0, 1], p[0, :, 3].reshape(H, W))
+    assert (maps[0, 2] == np.float32(0.7)).all()
+
+
+@pytest.mark.parametrize("nc", [1, 3, 5])
+def test_sweep_sample_bit_exact(nc):
+    from depthestimation_b200 import lcsim
+    rng = np.random.default_rng(nc)
+    B, K, H, W = 2, 37, 24, 40
+    fz = np.sort(rng.uniform(3., 18., size=(B, K, H, W)).astype(np.float32), axis=1)
+    fz[:, 5] = fz[:, 4]                                      # exact ties between slices: the first one wins
+    fz[0, 9, 3, :] = 1000.                                   # models.py:897: NaN depths replaced by 1000
+    fi = rng.uniform(0, 255, size=(B, K, H, W)).astype(np.float32)
+    sd = rng.uniform(2., 19., size=(B, nc, H, W)).astype(np.float32)
+    sd[0, 0, 0, :5] = np.nan                                 # torch.argmin: a NaN difference wins (first index)
+    sd[1, nc - 1, 2, 2] = 0.
+    out, inds = lcsim.sweep_sample(torch.as_tensor(sd).cuda(), torch.as_tensor(fz).cuda(), torch.as_tensor(fi).cuda(),
+                                   want_inds=True)
+    ref, rinds = A.sweep_sample(sd, fz, fi)
+    np.testing.assert_array_equal(inds.cpu().numpy(), rinds.numpy().astype(np.int32))
+    np.testing.assert_array_equal(out.cpu().numpy(), ref.numpy())
