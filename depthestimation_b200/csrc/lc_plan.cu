@@ -17,12 +17,13 @@ constexpr int kWarpWarps = 32;      // plan_prep_warp_kernel: one row per warp a
 // per-column min-max normalise -> NaN->eps.   light_curtain.py:654-681, 79-85, 207-218
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kPrepCols* kPrepWarps)
-plan_prep_columns_kernel(const float* __restrict__ uf, int D, int W, int R, float* __restrict__ field_pre) {
+plan_prep_columns_kernel(const float* __restrict__ uf, int D, int W, int R, int flags, float* __restrict__ field_pre) {
   extern __shared__ float sm[];
   float* u = sm;                        // [D][32]
   float* f0 = sm + (size_t)D * kPrepCols;        // [R][32]
   float* f1 = f0 + (size_t)R * kPrepCols;        // [R][32]
   __shared__ int has_nan[kPrepCols];
+  __shared__ int has_bad[kPrepCols + 4];        // column (with a halo of 2) holds a NaN or an infinity after :658-662
   __shared__ float lo_s[kPrepWarps][kPrepCols], hi_s[kPrepWarps][kPrepCols];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int b = blockIdx.y;
@@ -34,16 +35,34 @@ plan_prep_columns_kernel(const float* __restrict__ uf, int D, int W, int R, floa
   if (x == W - 1) sx = W - 2;
   if (W == 2) sx = 1;
   if (threadIdx.x < kPrepCols) has_nan[threadIdx.x] = 0;
+  if (threadIdx.x < kPrepCols + 4) has_bad[threadIdx.x] = 0;
   __syncthreads();
-  bool nan_here = false;
+  bool nan_here = false, inf_here = false;
   for (int d = warp; d < D; d += kPrepWarps) {
     float v = xin ? uf[((size_t)b * D + d) * W + sx] : 0.f;
     u[d * kPrepCols + lane] = v;
     nan_here |= (v != v);
+    inf_here |= (fabsf(v) == INFINITY);
   }
   if (nan_here) has_nan[lane] = 1;
+  if (inf_here || (nan_here && !(flags & 1))) has_bad[lane + 2] = 1;
+  if (lane < 4) {                               // the two columns either side of this block's 32
+    const int hx = blockIdx.x * kPrepCols + (lane < 2 ? lane - 2 : kPrepCols + lane - 2);
+    if (hx >= 0 && hx < W) {
+      int hsx = hx;
+      if (hx == 0) hsx = 1;
+      if (hx == W - 1) hsx = W - 2;
+      if (W == 2) hsx = 1;
+      bool bad = false;
+      for (int d = warp; d < D; d += kPrepWarps) {
+        const float v = uf[((size_t)b * D + d) * W + hsx];
+        bad |= (fabsf(v) == INFINITY) || ((v != v) && !(flags & 1));
+      }
+      if (bad) has_bad[lane < 2 ? lane : kPrepCols + lane] = 1;
+    }
+  }
   __syncthreads();
-  if (has_nan[lane]) {                                          // :658-662
+  if ((flags & 1) && has_nan[lane]) {                           // :658-662 (plan_default), :517-521 (plan_m1)
     for (int d = warp; d < D; d += kPrepWarps) u[d * kPrepCols + lane] = (d == D - 1) ? 1.0f : eps_floor();
   }
   __syncthreads();
@@ -67,6 +86,9 @@ plan_prep_columns_kernel(const float* __restrict__ uf, int D, int W, int R, floa
       int rr = r + j;
       if (rr >= 0 && rr < R) s += 0.2f * f0[rr * kPrepCols + lane];
     }
+    // the reference's kernel is 5x5 with zeros outside its middle column, and 0 * (NaN or inf) = NaN: a column
+    // within two of a non-finite one turns NaN as a whole
+    if (has_bad[lane] | has_bad[lane + 1] | has_bad[lane + 3] | has_bad[lane + 4]) s = NAN;
     f1[r * kPrepCols + lane] = s;
     lo = fminf(lo, s);
     hi = fmaxf(hi, s);
@@ -86,8 +108,9 @@ plan_prep_columns_kernel(const float* __restrict__ uf, int D, int W, int R, floa
   }
   const float span = hi - lo;
   for (int r = warp; r < R; r += kPrepWarps) {
-    float v = (f1[r * kPrepCols + lane] - lo) / span;            // normalize :207-210
-    if (v != v) v = eps_floor();                                  // :681
+    float v = f1[r * kPrepCols + lane];
+    if (flags & 2) v = (v - lo) / span;                           // normalize :207-210
+    if ((flags & 4) && v != v) v = eps_floor();                   // :681
     if (xin) field_pre[((size_t)b * R + r) * W + x] = v;
   }
 }
@@ -224,9 +247,35 @@ extern "C" int lc_plan_prepare(const float* uf, int B, int D, int W, int R, cons
     DPV_CUDA(cudaFuncSetAttribute(plan_prep_columns_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
   if (sm2 > 40 * 1024)
     DPV_CUDA(cudaFuncSetAttribute(plan_prep_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
-  plan_prep_columns_kernel<<<grid, kPrepCols * kPrepWarps, sm1, st>>>(uf, D, W, R, field_pre);
+  plan_prep_columns_kernel<<<grid, kPrepCols * kPrepWarps, sm1, st>>>(uf, D, W, R, 1 | 2 | 4, field_pre);
   int rc = check_launch("lc_plan_prepare/columns");
   if (rc) return rc;
   plan_prep_warp_kernel<<<grid, kPrepCols * kWarpWarps, sm2, st>>>(field_pre, flow, W, R, is, umaps, argmax);
   return check_launch("lc_plan_prepare/warp");
+}
+
+// The planning field alone, for the planners that do not run the DP on the three default maps
+// (plan_sweep / plan_empty light_curtain.py:396-503, plan_m1 :505-552): side fix -> [NaN columns] -> row upsample ->
+// 5-tap mean -> [normalise] -> [NaN -> eps] -> polar warp.  flags = LC_FIELD_*.
+extern "C" int lc_plan_field(const float* uf, int B, int D, int W, int R, const float* flow, int flags,
+                             float* field_range, float* field_pre, void* stream) {
+  DPV_REQUIRE(uf && flow && field_range && field_pre, "lc_plan_field: null pointer (field_pre scratch is required)");
+  DPV_REQUIRE(B > 0 && D > 1 && W >= 4 && R > 1, "lc_plan_field: bad shape");
+  DPV_REQUIRE((flags & ~7) == 0 && B <= 65535, "lc_plan_field: unknown flags %d or B too large", flags);
+  cudaStream_t st = (cudaStream_t)stream;
+  InvertSteps is;
+  is.n = 0;
+  dim3 grid((W + kPrepCols - 1) / kPrepCols, B);
+  size_t sm1 = (size_t)(D + 2 * R) * kPrepCols * sizeof(float);
+  size_t sm2 = (size_t)R * kPrepCols * sizeof(float);
+  DPV_REQUIRE(sm1 <= 200 * 1024, "lc_plan_field: D + 2R too large for shared memory");
+  if (sm1 > 40 * 1024)
+    DPV_CUDA(cudaFuncSetAttribute(plan_prep_columns_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
+  if (sm2 > 40 * 1024)
+    DPV_CUDA(cudaFuncSetAttribute(plan_prep_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
+  plan_prep_columns_kernel<<<grid, kPrepCols * kPrepWarps, sm1, st>>>(uf, D, W, R, flags, field_pre);
+  int rc = check_launch("lc_plan_field/columns");
+  if (rc) return rc;
+  plan_prep_warp_kernel<<<grid, kPrepCols * kWarpWarps, sm2, st>>>(field_pre, flow, W, R, is, field_range, nullptr);
+  return check_launch("lc_plan_field/warp");
 }

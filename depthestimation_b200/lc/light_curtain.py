@@ -157,6 +157,70 @@ class LightCurtain:
     def plan_default_low(self, field, cfg):
         return self._plan_default(field, cfg, "low")
 
+    # ---- flat sweeps (light_curtain.py:262-266, 387-503) ------------------------------------------
+    def get_flat(self, z):
+        """2000 design points (x, z) at depth z, x from -10 m in 1 cm steps (:262-266)."""
+        x = np.arange(-10., 10., 0.01)
+        return np.stack([x, np.full_like(x, z)], 1).astype(np.float32)
+
+    def _field_visual(self, field, mode, flags):
+        """The polar planning field as the reference's [R,W,3] visual (:475-480): the warp runs on the GPU, the
+        side columns are copied from their neighbours afterwards."""
+        r = self.rig(mode)
+        fr, _ = ops.plan_field(field.unsqueeze(0), r.flow, len(self.r_candi_up), flags)
+        fr = fr[0]
+        fr[:, 0] = fr[:, 1]
+        fr[:, -1] = fr[:, -2]
+        return np.repeat(fr.cpu().numpy()[:, :, np.newaxis], 3, axis=2)
+
+    def _plan_sweep(self, field, cfg, mode):
+        vis = self._field_visual(field, mode, 2)                     # normalised, NaN columns kept (:465)
+        d_up = np.asarray(self.d_candi_up)
+        pts_all = []
+        for z in np.arange(cfg["start"], cfg["end"], cfg["step"]):   # :485-500
+            pts = self.get_flat(z)
+            pts_all.append(pts)
+            rows = np.digitize(pts[:, 1], d_up) - 1
+            cols = np.arange(pts.shape[0])
+            keep = (rows < 256) & (rows >= 0) & (cols < vis.shape[1])
+            vis[rows[keep], cols[keep], :] = [1, 0, 1]
+        self.field_visual = vis
+        return pts_all, vis
+
+    def plan_sweep_high(self, field, cfg):
+        """-> (list of flat curtains [2000,2] at cfg start/end/step depths, field_visual [R,W,3]).  The curtains do
+        not depend on the field; `field` is not modified."""
+        return self._plan_sweep(field, cfg, "high")
+
+    def plan_sweep_low(self, field, cfg):
+        return self._plan_sweep(field, cfg, "low")
+
+    def plan_empty_high(self, field, cfg):
+        """plan_empty (:396-439) only prepares the field visual (the reference then fails on an undefined
+        pts_planned_all): -> ([], field_visual)."""
+        self.field_visual = self._field_visual(field, "high", 2)
+        return [], self.field_visual
+
+    def plan_empty_low(self, field, cfg):
+        self.field_visual = self._field_visual(field, "low", 2)
+        return [], self.field_visual
+
+    def plan_m1_high(self, field, cfg):
+        raise NotImplementedError("plan_m1 (:505-644) draws its curtains with numpy's global RNG and lcsim's alglib "
+                                  "B-spline fit: not reproducible bit for bit, left out (DESIGN.md section 8)")
+
+    # ---- real-sensor measurement (light_curtain.py:1076-1089) --------------------------------------
+    def transform_measurement(self, output_lc, thickness_lc, rTc=None, intr_rgb=None, size_rgb=None):
+        """A light-curtain return [H,W,4] + thickness [H,W] in the LC camera -> sensed_arr [3,H_rgb,W_rgb] =
+        (depth, intensity, thickness) in the RGB camera (pylc.transformPoints with filtering 0)."""
+        P = self.PARAMS
+        rTc = P["rTc"] if rTc is None else rTc
+        intr = P["intr_rgb"] if intr_rgb is None else intr_rgb
+        size = P["size_rgb"] if size_rgb is None else size_rgb
+        pts = ops.f32(output_lc, self.device).reshape(1, -1, 4)
+        th = ops.f32(thickness_lc, self.device).reshape(1, -1)
+        return lcsim.transform_points(pts, th, intr, rTc, int(size[0]), int(size[1]), 0)[0]
+
     # ---- sensing (light_curtain.py:741-910) ---------------------------------------------------
     def _sense(self, depth_rgb, design_pts_lc, mode, noise=None):
         r = self.rig(mode)

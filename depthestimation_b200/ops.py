@@ -169,6 +169,17 @@ def plan_prepare(uf, flow, steps, R, umaps=None, argmax=None, field_pre=None):
     return umaps, argmax, field_pre
 
 
+def plan_field(uf, flow, R, flags=7):
+    """uf [B,D,W], flow [R,W,2] -> (field_range [B,R,W], field_pre [B,R,W]); flags = LC_FIELD_* (include/dpv_b200.h)."""
+    dev = _dev(uf)
+    uf, flow = f32(uf, dev), f32(flow, dev)
+    B, D, W = uf.shape
+    frange = torch.empty(B, int(R), W, device=dev, dtype=torch.float32)
+    pre = torch.empty(B, int(R), W, device=dev, dtype=torch.float32)
+    check(lib().lc_plan_field(ptr(uf), B, D, W, int(R), ptr(flow), int(flags), ptr(frange), ptr(pre), stream_ptr(dev)))
+    return frange, pre
+
+
 # --------------------------------------------------------------------------------------------------
 # callers either side of the fused path (SURVEY §8 rows a17-a19, (f)1)
 # --------------------------------------------------------------------------------------------------

@@ -110,6 +110,17 @@ int dpv_ufield(const float* dpv, const float* mean, const float* mask, int B, in
  */
 int lc_plan_prepare(const float* uf, int B, int D, int W, int R, const float* flow, const float* steps,
                     int nsteps, float* umaps, int32_t* argmax, float* field_pre, void* stream);
+/* The planning field alone (plan_sweep / plan_empty lc/light_curtain.py:396-503, plan_m1 :505-552, which do not run
+ * the DP on plan_default's three maps): uf [B,D,W] -> field_range [B,R,W] (polar-warped), field_pre [B,R,W] (before the
+ * warp).  LC_FIELD_DEFAULT reproduces plan_default's field.  Like the reference's 5x5 smoothing kernel (zeros
+ * outside its middle column, 0 * NaN = NaN), a column within two of one that still holds a NaN or an infinity turns
+ * NaN; without LC_FIELD_NORMALIZE that is applied to the whole neighbouring column, not only to the 5x5 window. */
+#define LC_FIELD_NAN_COLUMNS 1 /* a column holding a NaN becomes (eps,...,eps,1): :658-662, :517-521 */
+#define LC_FIELD_NORMALIZE 2   /* per-column min-max: :207-210 */
+#define LC_FIELD_NAN_TO_EPS 4  /* :681 */
+#define LC_FIELD_DEFAULT 7
+int lc_plan_field(const float* uf, int B, int D, int W, int R, const float* flow, int flags, float* field_range,
+                  float* field_pre, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * lcsim device model.  external/lcsim/python/sim.py:29-211 LCDevice,

@@ -107,6 +107,33 @@ class LightCurtainOracle:
         f[torch.isnan(f)] = O.EPS                                    # :681
         return f, flow_warp(f, self.flow())                          # :684
 
+    # ---- plan_sweep, light_curtain.py:441-503 (get_flat :262-266) ---------------------------
+    def plan_sweep(self, field, cfg):
+        """field [D,W] (mutated in place) -> (list of flat design-point arrays [2000,2], field_visual [R,W,3])."""
+        field[:, 0] = field[:, 1]                                    # :449-450
+        field[:, -1] = field[:, -2]
+        f = F.interpolate(field.unsqueeze(0).unsqueeze(0), size=[len(self.d_candi_up), self.W],
+                          mode="bilinear", align_corners=False)      # :453
+        k = torch.zeros(5, 5)
+        k[:, 2] = 1 / 5.0
+        f = F.conv2d(f, k.reshape(1, 1, 5, 5), padding=2).squeeze(0).squeeze(0)      # :456-458
+        lo, _ = f.unsqueeze(0).min(1)                                # :465 (NaN columns stay NaN: no :658-662 here)
+        hi, _ = f.unsqueeze(0).max(1)
+        f = ((f.unsqueeze(0) - lo) / (hi - lo)).squeeze(0)
+        fr = flow_warp(f, self.flow())                               # :470
+        fr[:, 0] = fr[:, 1]                                          # :476-477
+        fr[:, -1] = fr[:, -2]
+        vis = np.repeat(fr.numpy()[:, :, np.newaxis], 3, axis=2)     # :480
+        pts_all = []
+        for z in np.arange(cfg["start"], cfg["end"], cfg["step"]):   # :485-500
+            pts = np.array([[x, z] for x in np.arange(-10., 10., 0.01)]).astype(np.float32)
+            pts_all.append(pts)
+            pix = np.array([np.digitize(pts[:, 1], self.d_candi_up) - 1, range(0, pts.shape[0])]).T
+            keep = (pix[:, 0] < 256) & (pix[:, 0] >= 0) & (pix[:, 1] >= 0) & (pix[:, 1] < vis.shape[1])
+            pix = pix[keep]
+            vis[pix[:, 0], pix[:, 1], :] = [1, 0, 1]
+        return pts_all, vis
+
     def split_fields(self, frange, steps):
         """:695-708 -> list of umaps [main, (left_p, right_p) for p in steps], and the argmax row."""
         left, right = frange.clone(), frange.clone()

@@ -190,6 +190,38 @@ def case_light_curtain():
          angles=np.array(lc.fw_large.angles_output, np.float32))
 
 
+def case_plan_sweep():
+    """plan_sweep (light_curtain.py:441-503) on the unmodified reference: flat curtains + the field visual.  The
+    uncertainty field carries NaN columns (columns without band pixels), which this planner does not replace."""
+    _install_lcsim_stubs()
+    import lc.light_curtain as LC
+    g = torch.Generator().manual_seed(9)
+    D, H, W = 16, 32, 64
+    h, w = H // 4, W // 4
+    cfg = ref_shim.AttrDict({"data": {"dataset_path": "kitti", "exp_name": "golden"},
+                             "var": {"d_min": 5., "d_max": 40., "qpower": 1.0}})
+    d = IU.powerf(5., 40., D, 1.0)
+    d_up = IU.powerf(5., 40., 32, 1.0)
+    Klow, _ = intrinsics(w, h, hfov=16.0, vfov=10.0)
+    Kup = Klow * 4
+    Kup[2, 2] = 1
+    model_input = {"intrinsics_up": torch.tensor(Kup).unsqueeze(0), "intrinsics": torch.tensor(Klow).unsqueeze(0),
+                   "rgb": torch.zeros(1, 2, 3, H, W), "dmaps": torch.zeros(1, h, w), "masks": torch.ones(1, 1, h, w),
+                   "d_candi": d, "d_candi_up": d_up}
+    lc = LC.LightCurtain()
+    params = lc.expand_params(lc.gen_params_from_model_input(model_input), cfg, D, 32)
+    lc.init(params)
+    uf = torch.rand(D, W, generator=g)
+    uf = uf / uf.sum(0, keepdim=True)
+    uf[:, 20] = float("nan")
+    uf[3, 41] = float("nan")
+    uf[:, -1] = float("nan")
+    sweep_cfg = {"start": 6.0, "end": 30.0, "step": 4.5}
+    pts, vis = lc.plan_sweep_high(uf.clone(), sweep_cfg)
+    save("plan_sweep", uf=uf, d_candi=d, d_candi_up=d_up, Kup=Kup, start=6.0, end=30.0, step=4.5,
+         pts=np.stack(pts), field_visual=vis)
+
+
 def case_aux():
     """Rows a17 (gen_lc_dpv_true), a18 (inverse_warp), a19 (correlation_native twin) and compute_unc_rmse,
     run on the unmodified reference -> aux.npz."""
@@ -264,3 +296,4 @@ if __name__ == "__main__":
     case_light_curtain()
     case_lcsim_fixture()
     case_aux()
+    case_plan_sweep()

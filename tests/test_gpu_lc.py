@@ -177,6 +177,40 @@ def test_plan_prepare_and_paths_golden():
         close(out2["umaps"][0, i], um2[i], rtol=2e-5, atol=1e-6, what="p=0.75 umap %d" % i)
 
 
+def test_plan_sweep_golden():
+    """plan_sweep_high against the unmodified reference (tests/golden/plan_sweep.npz): the flat curtains are bit-exact,
+    the field visual (NaN columns kept, magenta curtain rows drawn) within 1e-5."""
+    from depthestimation_b200.lc.light_curtain import LightCurtain
+    g = load("plan_sweep")
+    D, W = g["uf"].shape
+    H = 32
+    eye = np.eye(4, dtype=np.float32)
+    lTc = eye.copy()
+    lTc[0, 3] = 0.2
+    P = {"intr_rgb": g["Kup"], "dist_rgb": [0.] * 5, "size_rgb": [W, H], "intr_lc": g["Kup"], "dist_lc": [0.] * 5,
+         "size_lc": [W, H], "rTc": eye, "lTc": lTc, "laser_fov": 80., "d_candi": g["d_candi"], "r_candi": g["d_candi"],
+         "d_candi_up": g["d_candi_up"], "r_candi_up": g["d_candi_up"], "name": "sweep", "laser_timestep": 3.5e-5,
+         "device": torch.device("cuda", 0), "expand_A": D, "expand_B": len(g["d_candi_up"])}
+    lc = LightCurtain()
+    lc.init(P)
+    uf = cu(g["uf"])
+    keep = uf.clone()
+    cfg = {"start": float(g["start"]), "end": float(g["end"]), "step": float(g["step"])}
+    pts, vis = lc.plan_sweep_high(uf, cfg)
+    assert torch.equal(torch.nan_to_num(uf), torch.nan_to_num(keep))          # the input field is not edited
+    np.testing.assert_array_equal(np.stack(pts), g["pts"])
+    np.testing.assert_array_equal(np.isnan(vis), np.isnan(g["field_visual"]))
+    close(vis, g["field_visual"], rtol=1e-5, atol=1e-6)
+    empty, vis2 = lc.plan_empty_high(uf, cfg)
+    assert empty == [] and vis2.shape == vis.shape
+    with pytest.raises(NotImplementedError):
+        lc.plan_m1_high(uf, cfg)
+    # the flat curtains go through the simulator like any design points
+    dev = lc.rig("high").dev
+    planes = dev.curtain_planes(cu(pts[1]).unsqueeze(0))
+    assert torch.isfinite(planes[0, W // 2, :4]).all()
+
+
 def test_lc_process_golden_and_oracle_trace():
     from depthestimation_b200 import dpv_head
     g = load("light_curtain")

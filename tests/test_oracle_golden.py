@@ -120,6 +120,18 @@ def real_sensor_likelihood(d_candi, sensed, std_div, peak=None):
     return lik.permute(2, 0, 1)
 
 
+def test_plan_sweep_against_reference():
+    """plan_sweep (lc/light_curtain.py:441-503): flat curtains and the field visual, NaN columns included."""
+    g = load("plan_sweep")
+    D, W = g["uf"].shape
+    lc = LO.LightCurtainOracle(g["Kup"], W, 32, g["d_candi"], g["d_candi_up"])
+    pts, vis = lc.plan_sweep(T(g["uf"]).clone(), {"start": float(g["start"]), "end": float(g["end"]),
+                                                 "step": float(g["step"])})
+    np.testing.assert_array_equal(np.stack(pts), g["pts"])
+    np.testing.assert_array_equal(np.isnan(vis), np.isnan(g["field_visual"]))
+    close(vis, g["field_visual"], rtol=1e-6, atol=1e-7)
+
+
 def test_aux_rows_against_reference():
     from oracle import aux_oracle as A
     g = load("aux")
