@@ -263,6 +263,8 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
   const float2 inv2 = splat2(1.f / group_sum<T>((a0.x + a0.y) + (a1.x + a1.y), gmask));
 
   // ---- clamp, (log), expectation, store (models.py:1119-1122) -------------------------------
+  // LC_FUSE_OUT_RAW: more curtains follow in another call -- the reference only clamps after the last one
+  const float floor_out = (flags & 8) ? 0.f : eps_floor();
   float2 m0 = splat2(0.f), m1 = splat2(0.f);
 #pragma unroll
   for (int k = 0; k < NP; k += 2) {
@@ -270,8 +272,8 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
     float2 c0v = __fmul2_rn(p.v[k], inv2), c1v = __fmul2_rn(p.v[k + 1], inv2);
     // clamp(., eps, 1): the upper bound cannot bind -- a sum of positive floats is >= each term, and
     // x * fl(1/x) <= 1 + 2^-24 rounds to 1 (ties to even)
-    c0v = make_float2(fmaxf(c0v.x, eps_floor()), fmaxf(c0v.y, eps_floor()));
-    c1v = make_float2(fmaxf(c1v.x, eps_floor()), fmaxf(c1v.y, eps_floor()));
+    c0v = make_float2(fmaxf(c0v.x, floor_out), fmaxf(c0v.y, floor_out));
+    c1v = make_float2(fmaxf(c1v.x, floor_out), fmaxf(c1v.y, floor_out));
     p.v[k] = c0v;
     p.v[k + 1] = c1v;
     m0 = __ffma2_rn(make_float2(q.x, q.y), c0v, m0);         // d_candi is 0 in the padding bins
@@ -307,8 +309,9 @@ extern "C" int lc_sense_fuse(const LcDevice* dev, const float* logp_in, const fl
               "lc_sense_fuse: spread_n=%d not in {1,3,5,7}", spread_n);
   DPV_REQUIRE(D <= 128, "lc_sense_fuse: D=%d > 128 unsupported", D);
   DPV_REQUIRE(((uintptr_t)planes & 15) == 0, "lc_sense_fuse: planes must be 16-byte aligned");
-  DPV_REQUIRE((flags & ~7) == 0, "lc_sense_fuse: unknown flags %d", flags);
+  DPV_REQUIRE((flags & ~15) == 0, "lc_sense_fuse: unknown flags %d", flags);
   DPV_REQUIRE(!(flags & 4) || (flags & 1), "lc_sense_fuse: LC_FUSE_IN_CLAMPED needs LC_FUSE_IN_PROB");
+  DPV_REQUIRE(!(flags & 8) || (flags & 2), "lc_sense_fuse: LC_FUSE_OUT_RAW needs LC_FUSE_OUT_PROB");
   const long long hw_img = (long long)dev->H * dev->W;
   DPV_REQUIRE(B <= 65535 && dev->H <= 65535 && hw_img * 32 < (1ll << 31), "lc_sense_fuse: B=%d or image too large", B);
   cudaStream_t st = (cudaStream_t)stream;

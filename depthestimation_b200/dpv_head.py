@@ -91,6 +91,57 @@ def lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n,
         trace[-1]["logp"] = torch.log(state.logp) if out_prob else state.logp.clone()
 
 
+def _lc_process_sweep(BV_cur_all, model_input, lc, mode, iterations, params, noise, trace):
+    """lc_process with planner == "sweep" (models.py:1054-1055; plan_sweep light_curtain.py:441-503): every iteration
+    senses the same flat curtains at depths arange(start, end, step).  The curtains do not depend on the field, so
+    their plane coefficients are built once and neither the uncertainty field nor the DP planner runs; the fused
+    kernel takes the curtains eight at a time, the volume staying clamped probability between its calls."""
+    get = (lambda k: params[k]) if isinstance(params, dict) else (lambda k: getattr(params, k))
+    spread_iter, spread_n = int(get("spread_iter")), int(get("spread_n"))
+    zs = np.arange(get("start"), get("end"), get("step"))
+    dev = BV_cur_all.device
+    B = BV_cur_all.shape[0]
+    if mode == "high":
+        depth = torch.nn.functional.interpolate(model_input["dmaps"].to(dev).float().unsqueeze(1), scale_factor=4,
+                                                mode="nearest").squeeze(1).contiguous()
+    elif mode == "low":
+        depth = model_input["dmaps"].to(dev).float().contiguous()
+    else:
+        raise Exception("lc_process: unknown mode " + str(mode))
+    rig = lc.rig(mode)
+    final = BV_cur_all.detach()
+    D_in = final.shape[1]
+    if D_in != lc.expand_A:
+        final = ops.resample_depth(final, lc.expand_A, bv_log=True)
+    vol = final.clone()
+    if len(zs) == 0 or iterations == 0:
+        return (ops.resample_depth(vol, D_in, bv_log=True) if vol.shape[1] != D_in else vol), [[] for _ in range(B)]
+    flats = torch.from_numpy(np.stack([lc.get_flat(z) for z in zs])).to(dev)            # [nc,2000,2]
+    planes = rig.dev.curtain_planes(flats)                                               # [nc,W,12]
+    chunks = [planes[c:c + 8].unsqueeze(0).expand(B, -1, -1, -1).contiguous() for c in range(0, len(zs), 8)]
+    mean = torch.empty(B, vol.shape[2], vol.shape[3], device=dev, dtype=torch.float32)
+    first = True
+    for i in range(iterations):
+        for j, pl in enumerate(chunks):
+            ncc = pl.shape[1]
+            last_chunk = j == len(chunks) - 1
+            last = last_chunk and i == iterations - 1
+            nz = None
+            if noise is not None:
+                nz = noise[i].reshape(B, len(zs), *vol.shape[2:])[:, 8 * j:8 * j + ncc].contiguous()
+            elif rig.dev.hit_noise > 0:
+                nz = rig.dev.noise_like(B * ncc)
+            rig.dev.sense_fuse(vol, depth, pl.view(B * ncc, -1, 12), ncc, lc.d_candi, spread_iter if last_chunk else 0,
+                               spread_n, noise=nz, out=vol, mean=mean, in_prob=not first, out_prob=not last,
+                               in_clamped=not first, out_raw=not last_chunk)
+            first = False
+        if trace is not None:
+            trace.append(dict(logp=torch.log(vol) if i < iterations - 1 else vol.clone()))
+    if vol.shape[1] != D_in:
+        vol = ops.resample_depth(vol, D_in, bv_log=True)
+    return vol, [[] for _ in range(B)]
+
+
 def lc_process(BV_cur_all, model_input, lc, mode="low", iterations=5, viz=False, score=False, planner="default",
                params=None, cfg=None, noise=None, trace=None, state=None):
     """BaseModel.lc_process (models/models.py:980-1129) for the whole batch at once.
@@ -99,11 +150,14 @@ def lc_process(BV_cur_all, model_input, lc, mode="low", iterations=5, viz=False,
     params has .step / ["step"], spread_iter, spread_n.  noise: optional [iterations, B*nc, H, W] intensity noise
     (the reference draws unseeded N(0, 0.01)); None uses the device's hit_noise setting.
     Returns (fused log-DPV [B,D,H,W], unc_scores list) like the reference."""
-    if planner != "default":
-        raise NotImplementedError("planner %r: only 'default' is on the B200 path (plan_m1 / plan_sweep are next)"
-                                  % planner)
+    if planner not in ("default", "sweep"):
+        raise NotImplementedError("planner %r: 'default' and 'sweep' are on the B200 path (plan_m1 is not: numpy RNG + "
+                                  "alglib spline fit, DESIGN.md section 8)" % planner)
     get = (lambda k: params[k]) if isinstance(params, dict) else (lambda k: getattr(params, k))
-    steps, spread_iter, spread_n = list(get("step")), int(get("spread_iter")), int(get("spread_n"))
+    spread_iter, spread_n = int(get("spread_iter")), int(get("spread_n"))
+    if planner == "sweep":
+        return _lc_process_sweep(BV_cur_all, model_input, lc, mode, iterations, params, noise, trace)
+    steps = list(get("step"))
     dev = BV_cur_all.device
     B = BV_cur_all.shape[0]
     if mode == "high":                                                        # models.py:985-989

@@ -164,16 +164,18 @@ class LCDevice:
         return lik
 
     def sense_fuse(self, logp, depth, planes, nc, d_candi, spread_iter, spread_n, noise=None, out=None, mean=None,
-                   in_prob=False, out_prob=False, in_clamped=False):
+                   in_prob=False, out_prob=False, in_clamped=False, out_raw=False):
         """One LC iteration's sensing + Bayesian update (models/models.py:1064-1122), in place if out is logp.
-        in_clamped: the probability volume passed in is a previous call's out_prob output (already in [eps, 1])."""
+        in_clamped: the probability volume passed in is a previous call's out_prob output (already in [eps, 1], or
+        raw); out_raw: more curtains of the same iteration follow in another call (no final clamp)."""
         from .ops import d_candi_tensor
         B, D = logp.shape[0], logp.shape[1]
         dc = d_candi_tensor(d_candi, self.device)
         out = torch.empty_like(logp) if out is None else out
         mean = torch.empty(B, self.H, self.W, device=self.device, dtype=torch.float32) if mean is None else mean
         check(lib().lc_sense_fuse(self._h, ptr(logp), ptr(depth), ptr(planes), ptr(noise), B, nc, ptr(dc), D,
-                                  int(spread_iter), int(spread_n), (1 if in_prob else 0) | (2 if out_prob else 0) | (4 if in_clamped else 0),
+                                  int(spread_iter), int(spread_n), (1 if in_prob else 0) | (2 if out_prob else 0) | (4 if in_clamped else 0) |
+                                  (8 if out_raw else 0),
                                   ptr(out), ptr(mean), stream_ptr(self.device)))
         return out, mean
 

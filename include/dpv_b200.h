@@ -175,6 +175,10 @@ int lc_sense_likelihood(const LcDevice* dev, const float* planes, const float* d
 #define LC_FUSE_IN_PROB 1
 #define LC_FUSE_OUT_PROB 2
 #define LC_FUSE_IN_CLAMPED 4
+/* with LC_FUSE_OUT_PROB: store the normalised probabilities without the final clamp of models.py:1119, for a call
+ * that hands the volume to another call with more curtains of the same iteration (that call takes it with
+ * LC_FUSE_IN_PROB | LC_FUSE_IN_CLAMPED, i.e. without an entry clamp either; spread_iter goes to the last call) */
+#define LC_FUSE_OUT_RAW 8
 int lc_sense_fuse(const LcDevice* dev, const float* logp_in, const float* depth, const float* planes,
                   const float* noise, int B, int nc, const float* d_candi, int D, int spread_iter,
                   int spread_n, int flags, float* logp_out, float* mean_out, void* stream);

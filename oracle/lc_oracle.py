@@ -162,10 +162,10 @@ class LightCurtainOracle:
         return O.curtain_likelihood(self.d_candi, depth_gt, img[:, :, 2], img[:, :, 3], th), img, th
 
 
-def lc_loop(logp, depth_gt, lc, K_up, uf_par, iterations, steps, spread_iter, spread_n, trace=None):
-    """BaseModel.lc_process body for ONE sample, mode='high', planner='default'
-    (models/models.py:1010-1127).  logp [1,D,H,W] log-DPV; depth_gt [H,W] numpy (already x4 nearest).
-    Returns fused log-DPV [1,D,H,W]."""
+def lc_loop(logp, depth_gt, lc, K_up, uf_par, iterations, steps, spread_iter, spread_n, trace=None, sweep=None):
+    """BaseModel.lc_process body for ONE sample, mode='high', planner='default' -- or planner='sweep' when `sweep`
+    = dict(start, end, step) is given (models/models.py:1010-1127).  logp [1,D,H,W] log-DPV; depth_gt [H,W] numpy
+    (already x4 nearest).  Returns fused log-DPV [1,D,H,W]."""
     K = torch.as_tensor(K_up).float()
     start = logp
     final = logp.detach().clone()
@@ -174,6 +174,13 @@ def lc_loop(logp, depth_gt, lc, K_up, uf_par, iterations, steps, spread_iter, sp
     for it in range(iterations):
         uf, _ = O.ufield(final, lc.d_candi, K, uf_par, BV_log=True)           # :1029
         uf_rec = uf.clone() if trace is not None else None                    # plan() edits uf in place (:654-662)
+        if sweep is not None:                                                 # :1054-1055
+            flats, _ = lc.plan_sweep(uf.squeeze(0), sweep)
+            liks = [lc.sense(depth_gt, p)[0] for p in flats]
+            final = O.bayes_fuse(final, liks, spread_iter, spread_n)
+            if trace is not None:
+                trace.append(dict(uf=uf_rec, logp=final))
+            continue
         paths, umaps, idx = lc.plan(uf.squeeze(0), steps, return_indices=True)  # :1050
         liks = [lc.sense(depth_gt, p[0])[0] for p in paths]                    # :1066
         final = O.bayes_fuse(final, liks, spread_iter, spread_n)              # :1097-1122

@@ -211,6 +211,29 @@ def test_plan_sweep_golden():
     assert torch.isfinite(planes[0, W // 2, :4]).all()
 
 
+def test_lc_process_sweep_planner_against_oracle():
+    """lc_process(planner="sweep") (models.py:1054-1055): nine flat curtains per iteration (two calls of the fused
+    kernel: eight curtains + one) against the oracle's per-curtain likelihood volumes and Bayesian update."""
+    from depthestimation_b200 import dpv_head
+    g = load("light_curtain")
+    lc = _golden_lc(g)
+    H, W = g["logp"].shape[2:]
+    mi = {"dmaps": cu(g["dmaps"]).unsqueeze(0), "intrinsics_up": cu(g["Kup"]).unsqueeze(0)}
+    prm = {"start": 8.0, "end": 30.0, "step": 2.5, "spread_iter": 2, "spread_n": 5}
+    trace = []
+    fused, _ = dpv_head.lc_process(cu(g["logp"]), mi, lc, mode="high", iterations=2, planner="sweep", params=prm,
+                                   cfg="kitti", trace=trace)
+    olc = LO.LightCurtainOracle(g["Kup"], W, H, g["d_candi"], g["d_candi_up"])
+    otrace = []
+    depth = np.repeat(np.repeat(g["dmaps"], 4, 0), 4, 1).astype(np.float32)
+    exp = LO.lc_loop(torch.tensor(g["logp"]), depth, olc, g["Kup"], O.uf_params("kitti"), 2, None, 2, 5, trace=otrace,
+                     sweep=prm)
+    for it in range(2):
+        close(trace[it]["logp"], otrace[it]["logp"], atol=1e-5, what="sweep logp it %d" % it)
+    close(fused, exp, atol=1e-5)
+    assert float((fused.cpu() - torch.tensor(g["logp"])).abs().max()) > 0.1      # the curtains did change the DPV
+
+
 def test_lc_process_golden_and_oracle_trace():
     from depthestimation_b200 import dpv_head
     g = load("light_curtain")
