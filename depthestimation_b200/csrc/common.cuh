@@ -26,6 +26,38 @@ inline int check_launch(const char* what) {
   return DPV_OK;
 }
 
+// The device's highest kernel scheduling priority.  The latency-bound kernels of the light-curtain loop (a few CTAs,
+// hundreds of microseconds of dependent work) are launched with it: when other streams keep the GPU full of
+// streaming kernels with tens of thousands of blocks, the block scheduler then hands freed SM resources to these
+// CTAs first instead of after the streaming kernel's last wave.
+inline int high_priority() {
+  static int greatest = [] {
+    int least = 0, g = 0;
+    if (cudaDeviceGetStreamPriorityRange(&least, &g) != cudaSuccess) {
+      (void)cudaGetLastError();
+      g = 0;
+    }
+    return g;
+  }();
+  return greatest;
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_high_priority(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                                        Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributePriority;
+  attr[0].val.priority = high_priority();
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 #define DPV_REQUIRE(cond, ...)      \
   do {                              \
     if (!(cond)) {                  \

@@ -51,5 +51,8 @@ struct LcPlanner {
   // lc_planner_solve's producer -> consumer log (grown on demand; one solve at a time per handle)
   unsigned char* d_log = nullptr;
   size_t log_bytes = 0;
-  int epoch = 0;
+  // device-side solve counter {epoch, CTAs finished}: the tag of a solve's log entries comes from it, so a launch
+  // captured in a CUDA graph tags every replay differently
+  unsigned* d_epoch = nullptr;
+  int last_n = 0;
 };

@@ -435,7 +435,7 @@ extern "C" int lc_curtain_planes(const LcDevice* dev, const float* xz, const int
   if (smem > 48 * 1024)
     DPV_CUDA(cudaFuncSetAttribute(dpv::curtain_planes_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid(n, (dev->W + dpv::kPlaneCols - 1) / dpv::kPlaneCols);
-  dpv::curtain_planes_kernel<<<grid, dpv::kPlaneThreads, smem, (cudaStream_t)stream>>>(dev->view, xz, counts, npts,
-                                                                                       planes, design);
+  dpv::launch_high_priority(dpv::curtain_planes_kernel, grid, dim3(dpv::kPlaneThreads), smem, (cudaStream_t)stream,
+                            dev->view, xz, counts, npts, planes, design);
   return dpv::check_launch("lc_curtain_planes");
 }

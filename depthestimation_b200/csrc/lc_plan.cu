@@ -247,10 +247,12 @@ extern "C" int lc_plan_prepare(const float* uf, int B, int D, int W, int R, cons
     DPV_CUDA(cudaFuncSetAttribute(plan_prep_columns_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
   if (sm2 > 40 * 1024)
     DPV_CUDA(cudaFuncSetAttribute(plan_prep_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
-  plan_prep_columns_kernel<<<grid, kPrepCols * kPrepWarps, sm1, st>>>(uf, D, W, R, 1 | 2 | 4, field_pre);
+  launch_high_priority(plan_prep_columns_kernel, grid, dim3(kPrepCols * kPrepWarps), sm1, st, uf, D, W, R, 1 | 2 | 4,
+                       field_pre);
   int rc = check_launch("lc_plan_prepare/columns");
   if (rc) return rc;
-  plan_prep_warp_kernel<<<grid, kPrepCols * kWarpWarps, sm2, st>>>(field_pre, flow, W, R, is, umaps, argmax);
+  launch_high_priority(plan_prep_warp_kernel, grid, dim3(kPrepCols * kWarpWarps), sm2, st, field_pre, flow, W, R, is,
+                       umaps, argmax);
   return check_launch("lc_plan_prepare/warp");
 }
 

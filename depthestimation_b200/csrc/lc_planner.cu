@@ -87,6 +87,8 @@ int lc_planner_create(const LcDevice* dev, const float* ranges, int R, LcPlanner
   if ((e = cudaMalloc(&p->d_theta, th.size() * 4)) != cudaSuccess ||
       (e = cudaMalloc(&p->d_xz, xz.size() * 4)) != cudaSuccess ||
       (e = cudaMalloc(&p->d_win, win.size())) != cudaSuccess ||
+      (e = cudaMalloc(&p->d_epoch, 2 * sizeof(unsigned))) != cudaSuccess ||
+      (e = cudaMemset(p->d_epoch, 0, 2 * sizeof(unsigned))) != cudaSuccess ||
       (e = cudaMemcpy(p->d_theta, th.data(), th.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess ||
       (e = cudaMemcpy(p->d_xz, xz.data(), xz.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess ||
       (e = cudaMemcpy(p->d_win, win.data(), win.size(), cudaMemcpyHostToDevice)) != cudaSuccess) {
@@ -104,6 +106,7 @@ void lc_planner_destroy(LcPlanner* p) {
   cudaFree(p->d_xz);
   cudaFree(p->d_win);
   cudaFree(p->d_log);
+  cudaFree(p->d_epoch);
   delete p;
 }
 

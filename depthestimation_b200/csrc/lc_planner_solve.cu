@@ -369,16 +369,27 @@ template <int LANES, int NQL>
 __global__ void __launch_bounds__(1024)
 planner_solve_kernel(const float* __restrict__ umaps, int W, int R, const float* __restrict__ theta,
                      const float* __restrict__ node_xz, const uint8_t* __restrict__ win, unsigned long long* log_base,
-                     size_t log_per_map, unsigned tag, int32_t* __restrict__ ks, float* __restrict__ xz,
-                     int32_t* __restrict__ counts) {
+                     size_t log_per_map, unsigned* __restrict__ epoch, int32_t* __restrict__ ks,
+                     float* __restrict__ xz, int32_t* __restrict__ counts) {
   constexpr int RP = 4 * LANES * NQL;
   static_assert(RP % 128 == 0, "ray length must fill whole warps in part B");
   extern __shared__ __align__(16) unsigned char smraw[];
   const int map = blockIdx.x >> 1;
   const float* umap = umaps + (size_t)map * R * W;
   unsigned long long* lg = log_base + (size_t)map * log_per_map;
+  // The tag of this solve's log entries: 1..65535 from the handle's device-side solve counter (never 0 = "written
+  // by no solve"; differs from the previous solve's, whose entries are the only stale ones a reader can meet).
+  // The last CTA of the grid to finish advances the counter, after every CTA has read it.
+  const unsigned tag = (*reinterpret_cast<volatile unsigned*>(epoch) % 65535u) + 1u;
   if ((blockIdx.x & 1) == 0) planner_part_a<LANES, NQL>(smraw, umap, W, R, win, lg, tag);
   else planner_part_b<RP / 128>(smraw, umap, W, R, theta, node_xz, win, lg, tag, map, ks, xz, counts);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (atomicAdd(epoch + 1, 1u) == gridDim.x - 1) {
+      epoch[1] = 0;
+      epoch[0] = epoch[0] + 1;
+    }
+  }
 }
 
 }  // namespace dpv
@@ -402,12 +413,14 @@ int launch_solve(LcPlanner* p, const float* umaps, int n, int warps, int32_t* ks
     p->log_bytes = 0;
     DPV_CUDA(cudaMalloc(&p->d_log, per_map * n * 8));
     p->log_bytes = per_map * n * 8;
-    p->epoch = 0;
+    p->last_n = 0;
   }
-  p->epoch += 1;
-  if (p->epoch > 0xffff) p->epoch = 1;
-  if (p->epoch == 1)                                              // tag 0 = "written by no solve"; also on tag wrap-around
+  if (n != p->last_n) {
+    // a different number of maps than the previous solve: the regions of maps that sat out keep older tags, which a
+    // wrapped-around 16-bit tag could meet again -- back to tag 0 = "written by no solve" everywhere
     DPV_CUDA(cudaMemsetAsync(p->d_log, 0, p->log_bytes, st));
+    p->last_n = n;
+  }
   const size_t smem_b = (size_t)9 * RP * 4 + (size_t)2 * RP * 16 + (size_t)2 * RP * 4 + (size_t)((W + 7) & ~7) * 2 +
                         (size_t)W * R;
   const size_t smem_a = (size_t)2 * (RP + 2 * (RP / 4)) * 4;
@@ -425,15 +438,17 @@ int launch_solve(LcPlanner* p, const float* umaps, int n, int warps, int32_t* ks
   cfg.blockDim = dim3((unsigned)threads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributePriority;                       // see high_priority(): 48 CTAs, 0.76 ms of serial work
+  attr[1].val.priority = high_priority();
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = 2;
   DPV_CUDA(cudaLaunchKernelEx(&cfg, kern, umaps, W, R, (const float*)p->d_theta, (const float*)p->d_xz,
-                              (const uint8_t*)p->d_win, (unsigned long long*)p->d_log, per_map, (unsigned)p->epoch, ks, xz,
+                              (const uint8_t*)p->d_win, (unsigned long long*)p->d_log, per_map, p->d_epoch, ks, xz,
                               counts));
   return DPV_OK;
 }

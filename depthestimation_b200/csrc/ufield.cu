@@ -246,11 +246,12 @@ extern "C" int dpv_ufield(const float* dpv_, const float* mean, const float* mas
   int launches = 0;
   if (a.prm.quash) {
     DPV_CUDA(cudaMemsetAsync(cmin, 0x7f, (size_t)B * W * sizeof(float), st));     // 0x7f7f7f7f = 3.39e38
-    ufield_colmin_kernel<<<gpix, kUfCols * kUfWarps, 0, st>>>(a, cmin);
+    launch_high_priority(ufield_colmin_kernel, gpix, dim3(kUfCols * kUfWarps), 0, st, a, cmin);
     launches++;
   }
-  ufield_mask_kernel<<<gpix, kUfCols * kUfWarps, 0, st>>>(a, cmin, words, count);
-  ufield_sum_kernel<<<dim3(G, (D + kUfWarps - 1) / kUfWarps, B), kUfCols * kUfWarps, 0, st>>>(a, words, count);
+  launch_high_priority(ufield_mask_kernel, gpix, dim3(kUfCols * kUfWarps), 0, st, a, cmin, words, count);
+  launch_high_priority(ufield_sum_kernel, dim3(G, (D + kUfWarps - 1) / kUfWarps, B), dim3(kUfCols * kUfWarps), 0, st, a,
+                       words, count);
   launches++;
   const int rc = check_launch("dpv_ufield");
   if (rc == DPV_OK) count_launch(launches);
