@@ -120,7 +120,14 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
   const int gbase = lane & ~(T - 1);
   constexpr unsigned gmask = 0xffffffffu;
   const int d0 = t * DPT;
-  const float4* dc4 = reinterpret_cast<const float4*>(dc + t * STR);
+  // this lane's slice of d_candi as a 32-bit shared-memory address held in a register (a generic pointer is
+  // re-derived from the CTA's shared window inside every loop that is not unrolled)
+  const unsigned dc_addr = (unsigned)__cvta_generic_to_shared(dc + t * STR);
+  auto dc4_at = [&](int i) -> float4 {                       // i is a compile-time constant after unrolling
+    float4 q;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(q.x), "=f"(q.y), "=f"(q.z), "=f"(q.w) : "r"(dc_addr + 16u * i));
+    return q;
+  };
   const int b = blockIdx.z;
   const size_t pix = (size_t)b * HW + hw;
   const size_t base = ((size_t)b * D + d0) * HW + hw;
@@ -187,7 +194,7 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
       float2 a0 = splat2(0.f), a1 = splat2(0.f);
 #pragma unroll
       for (int k = 0; k < NP; k += 2) {
-        const float4 q = dc4[k >> 1];
+        const float4 q = dc4_at(k >> 1);
         float2 e0 = __fadd2_rn(make_float2(q.x, q.y), nz2), e1 = __fadd2_rn(make_float2(q.z, q.w), nz2);
         e0 = __fmul2_rn(__fmul2_rn(e0, e0), kk2);
         e1 = __fmul2_rn(__fmul2_rn(e1, e1), kk2);
@@ -268,7 +275,7 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
   float2 m0 = splat2(0.f), m1 = splat2(0.f);
 #pragma unroll
   for (int k = 0; k < NP; k += 2) {
-    const float4 q = dc4[k >> 1];
+    const float4 q = dc4_at(k >> 1);
     float2 c0v = __fmul2_rn(p.v[k], inv2), c1v = __fmul2_rn(p.v[k + 1], inv2);
     // clamp(., eps, 1): the upper bound cannot bind -- a sum of positive floats is >= each term, and
     // x * fl(1/x) <= 1 + 2^-24 rounds to 1 (ties to even)
@@ -323,8 +330,8 @@ extern "C" int lc_sense_fuse(const LcDevice* dev, const float* logp_in, const fl
           dev->view, logp_in, depth, planes, noise, nc, d_candi, D, spread_iter, flags, logp_out, mean_out)
 #define LAUNCH3(DPT, T, HALF)                        \
   do {                                               \
-    if (D == DPT * T) LAUNCH4(DPT, T, HALF, true);   \
-    else LAUNCH4(DPT, T, HALF, false);               \
+    if (D == DPT * T) { LAUNCH4(DPT, T, HALF, true); }   \
+    else { LAUNCH4(DPT, T, HALF, false); }               \
   } while (0)
 #define LAUNCH(DPT, T)                       \
   do {                                       \

@@ -365,11 +365,11 @@ __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float
 }
 
 // grid = 2 CTAs per umap, launched as clusters of two so that the producer and its consumer are co-resident
-template <int LANES, int NQL>
+template <int LANES, int NQL, bool DEVTAG>
 __global__ void __launch_bounds__(1024)
 planner_solve_kernel(const float* __restrict__ umaps, int W, int R, const float* __restrict__ theta,
                      const float* __restrict__ node_xz, const uint8_t* __restrict__ win, unsigned long long* log_base,
-                     size_t log_per_map, unsigned* __restrict__ epoch, int32_t* __restrict__ ks,
+                     size_t log_per_map, unsigned host_tag, unsigned* __restrict__ epoch, int32_t* __restrict__ ks,
                      float* __restrict__ xz, int32_t* __restrict__ counts) {
   constexpr int RP = 4 * LANES * NQL;
   static_assert(RP % 128 == 0, "ray length must fill whole warps in part B");
@@ -377,17 +377,22 @@ planner_solve_kernel(const float* __restrict__ umaps, int W, int R, const float*
   const int map = blockIdx.x >> 1;
   const float* umap = umaps + (size_t)map * R * W;
   unsigned long long* lg = log_base + (size_t)map * log_per_map;
-  // The tag of this solve's log entries: 1..65535 from the handle's device-side solve counter (never 0 = "written
-  // by no solve"; differs from the previous solve's, whose entries are the only stale ones a reader can meet).
-  // The last CTA of the grid to finish advances the counter, after every CTA has read it.
-  const unsigned tag = (*reinterpret_cast<volatile unsigned*>(epoch) % 65535u) + 1u;
+  // The tag of this solve's log entries.  Launched directly, it is a kernel parameter the host counts up (1..32767;
+  // as a constant-bank operand it costs the per-entry code nothing).  Captured in a CUDA graph the parameter would be
+  // frozen, so that variant takes it from the handle's device-side solve counter instead (32768..65535: disjoint
+  // from the host's range, and the last CTA of the grid to finish advances the counter after every CTA has read it).
+  // Either way it is never 0 = "written by no solve" and differs from the previous solve's tag, whose entries are
+  // the only stale ones a reader can meet (every solve rewrites all entries of its maps).
+  const unsigned tag = DEVTAG ? 32768u + (*reinterpret_cast<volatile unsigned*>(epoch) & 32767u) : host_tag;
   if ((blockIdx.x & 1) == 0) planner_part_a<LANES, NQL>(smraw, umap, W, R, win, lg, tag);
   else planner_part_b<RP / 128>(smraw, umap, W, R, theta, node_xz, win, lg, tag, map, ks, xz, counts);
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    if (atomicAdd(epoch + 1, 1u) == gridDim.x - 1) {
-      epoch[1] = 0;
-      epoch[0] = epoch[0] + 1;
+  if (DEVTAG) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      if (atomicAdd(epoch + 1, 1u) == gridDim.x - 1) {
+        epoch[1] = 0;
+        epoch[0] = epoch[0] + 1;
+      }
     }
   }
 }
@@ -426,7 +431,14 @@ int launch_solve(LcPlanner* p, const float* umaps, int n, int warps, int32_t* ks
   const size_t smem_a = (size_t)2 * (RP + 2 * (RP / 4)) * 4;
   const size_t smem = smem_a > smem_b ? smem_a : smem_b;
   DPV_REQUIRE(smem <= 227 * 1024, "lc_planner_solve: W*R = %d*%d back-pointers exceed shared memory", W, R);
-  auto kern = planner_solve_kernel<LANES, NQL>;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cap) != cudaSuccess) {
+    (void)cudaGetLastError();
+    cap = cudaStreamCaptureStatusNone;
+  }
+  const bool devtag = cap != cudaStreamCaptureStatusNone;
+  p->host_epoch = p->host_epoch % 32767 + 1;                      // 1..32767
+  auto kern = devtag ? planner_solve_kernel<LANES, NQL, true> : planner_solve_kernel<LANES, NQL, false>;
   DPV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int threads = ((R * LANES + 31) / 32) * 32;                     // part A: LANES threads per node
   if (warps < 1) warps = 1;                                       // part B: one warp per tie node
@@ -448,7 +460,7 @@ int launch_solve(LcPlanner* p, const float* umaps, int n, int warps, int32_t* ks
   cfg.attrs = attr;
   cfg.numAttrs = 2;
   DPV_CUDA(cudaLaunchKernelEx(&cfg, kern, umaps, W, R, (const float*)p->d_theta, (const float*)p->d_xz,
-                              (const uint8_t*)p->d_win, (unsigned long long*)p->d_log, per_map, p->d_epoch, ks, xz,
+                              (const uint8_t*)p->d_win, (unsigned long long*)p->d_log, per_map, (unsigned)p->host_epoch, p->d_epoch, ks, xz,
                               counts));
   return DPV_OK;
 }
