@@ -26,6 +26,13 @@ struct LcDeviceView {
   LcMat4 cam_to_laser, laser_to_cam_inv;
 };
 
+// The four transforms of calculateSurface (dprocessor.cpp:841-857) that do not depend on the column: laser sheet
+// offset by +-thickness/2 and rotated by -+divergence.  Built once on the host with the same routine the kernel used
+// to run per column (30 double-precision sin / cos per column otherwise).
+struct LcPlaneConsts {
+  LcMat4 off_l, div_l, off_r, div_r;
+};
+
 struct LcDevice {
   int W = 0, H = 0;
   float K[9];
@@ -38,6 +45,7 @@ struct LcDevice {
   float t_max = 0.f;
   float* d_tables = nullptr;   // one device allocation holding all tables
   LcDeviceView view;
+  LcPlaneConsts plane_consts;
 };
 
 // DP planner handle (lc_planner.cu builds it, lc_planner_solve.cu uses it)

@@ -51,6 +51,21 @@ __host__ __device__ inline LcMat4 transform_matrix(float yaw, float pitch, float
   return r;
 }
 
+// transform_matrix(0, pitch, 0, 0, 0, 0) with the zero angles' cos = 1, sin = 0 written in (same expressions, so the
+// same values and zero signs; two trigonometric calls instead of six)
+__host__ __device__ inline LcMat4 transform_matrix_pitch(float pitch) {
+  float eulerY = (float)(pitch * M_PI / 180.);
+  const float ci = 1.f, ch = 1.f, si = 0.f, sh = 0.f;
+  float cj = cos_cr(eulerY), sj = sin_cr(eulerY);
+  float cc = ci * ch, cs = ci * sh, sc = si * ch, ss = si * sh;
+  LcMat4 r = mat4_identity();
+  r.m[0][0] = cj * ch;  r.m[0][1] = sj * sc - cs;  r.m[0][2] = sj * cc + ss;
+  r.m[1][0] = cj * sh;  r.m[1][1] = sj * ss + cc;  r.m[1][2] = sj * cs - sc;
+  r.m[2][0] = -sj;      r.m[2][1] = cj * si;       r.m[2][2] = cj * ci;
+  r.m[0][3] = 0.f; r.m[1][3] = 0.f; r.m[2][3] = 0.f;
+  return r;
+}
+
 // (M^-1)^T (1,0,0,0) for a rigid M: the laser-frame plane (dprocessor.cpp:781-797, 845-857)
 __host__ __device__ inline void rigid_inverse_row0(const LcMat4& M, float out[4]) {
   out[0] = M.m[0][0];
@@ -229,6 +244,10 @@ int lc_device_create(int W, int H, const float* K, const float* lTc, float fov, 
   v.mid_x = d->d_tables + o_mx; v.mid_z = d->d_tables + o_mz; v.angles = d->d_tables + o_an;
   v.hit_lut = d->d_tables + o_lut;
   v.hit_N = d->hit_N; v.hit_mode = hit_mode; v.limit = limit; v.thickness = thickness; v.divergence = divergence;
+  d->plane_consts.off_l = transform_matrix(0, 0, 0, (thickness / 2), 0, 0);        // dprocessor.cpp:845-857
+  d->plane_consts.div_l = transform_matrix(0, -divergence, 0, 0, 0, 0);
+  d->plane_consts.off_r = transform_matrix(0, 0, 0, -(thickness / 2), 0, 0);
+  d->plane_consts.div_r = transform_matrix(0, divergence, 0, 0, 0, 0);
   v.cam_to_laser = d->cam_to_laser;
   v.laser_to_cam_inv = d->laser_to_cam_inv;
   *out = d;
@@ -269,8 +288,9 @@ __device__ __forceinline__ float point_angle(float x, float z) {
 }
 
 __global__ void __launch_bounds__(kPlaneThreads)
-curtain_planes_kernel(LcDeviceView dv, const float* __restrict__ xz, const int32_t* __restrict__ counts, int npts,
-                      float* __restrict__ planes, float* __restrict__ design) {
+curtain_planes_kernel(LcDeviceView dv, LcPlaneConsts pc, const float* __restrict__ xz,
+                      const int32_t* __restrict__ counts, int npts, float* __restrict__ planes,
+                      float* __restrict__ design) {
   extern __shared__ float sm[];
   float* px = sm;                       // [npts]
   float* pz = px + npts;                // [npts]
@@ -403,15 +423,13 @@ curtain_planes_kernel(LcDeviceView dv, const float* __restrict__ xz, const int32
     float out[12];
     for (int k = 0; k < 12; k++) out[k] = 0.f;
     float lf[4], cf[4];
-    LcMat4 M = transform_matrix(0, an, 0, 0, 0, 0);
+    LcMat4 M = transform_matrix_pitch(an);
     rigid_inverse_row0(M, lf);
     plane_to_cam(dv.laser_to_cam_inv, lf, cf);
     for (int k = 0; k < 4; k++) out[k] = cf[k];
     if (!(an != an)) {
-      LcMat4 Ml = mat4_mul(mat4_mul(M, transform_matrix(0, 0, 0, (dv.thickness / 2), 0, 0)),
-                           transform_matrix(0, -dv.divergence, 0, 0, 0, 0));
-      LcMat4 Mr = mat4_mul(mat4_mul(M, transform_matrix(0, 0, 0, -(dv.thickness / 2), 0, 0)),
-                           transform_matrix(0, dv.divergence, 0, 0, 0, 0));
+      LcMat4 Ml = mat4_mul(mat4_mul(M, pc.off_l), pc.div_l);
+      LcMat4 Mr = mat4_mul(mat4_mul(M, pc.off_r), pc.div_r);
       rigid_inverse_row0(Ml, lf);
       plane_to_cam(dv.laser_to_cam_inv, lf, cf);
       for (int k = 0; k < 4; k++) out[4 + k] = cf[k];
@@ -436,6 +454,6 @@ extern "C" int lc_curtain_planes(const LcDevice* dev, const float* xz, const int
     DPV_CUDA(cudaFuncSetAttribute(dpv::curtain_planes_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid(n, (dev->W + dpv::kPlaneCols - 1) / dpv::kPlaneCols);
   dpv::launch_high_priority(dpv::curtain_planes_kernel, grid, dim3(dpv::kPlaneThreads), smem, (cudaStream_t)stream,
-                            dev->view, xz, counts, npts, planes, design);
+                            dev->view, dev->plane_consts, xz, counts, npts, planes, design);
   return dpv::check_launch("lc_curtain_planes");
 }

@@ -10,7 +10,7 @@ namespace dpv {
 
 constexpr int kPrepCols = 32;
 constexpr int kPrepWarps = 4;
-constexpr int kWarpWarps = 32;      // plan_prep_warp_kernel: one row per warp and pass (short dependent chains)
+constexpr int kWarpWarps = 16;      // plan_prep_warp_kernel: one row per warp and pass (short dependent chains)
 
 // ---------------------------------------------------------------------------------------------
 // P1 (column-local): side fix -> NaN columns -> bilinear row upsample D->R -> 5-tap depth mean ->
