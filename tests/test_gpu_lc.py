@@ -309,3 +309,36 @@ def test_pipeline_step_replays_as_cuda_graph():
     for k in eager1:
         assert torch.equal(got[k], eager2[k]), k
     assert not torch.equal(got["logp_lc"], eager1["logp_lc"])
+
+
+@pytest.mark.parametrize("W,H,D,nsweep", [(72, 20, 24, 2), (44, 12, 40, 5), (100, 16, 64, 1), (36, 8, 100, 3)])
+def test_sense_fuse_ragged_shapes_against_oracle(W, H, D, nsweep):
+    """Widths that are not a multiple of the 32 columns a CTA covers, depth counts that do not fill the lanes
+    (zero-padded bins), 1 to 5 curtains: one fused sense + update step against the oracle's per-curtain likelihood
+    volumes and Bayesian update."""
+    from depthestimation_b200.lc.light_curtain import LightCurtain
+    rng = np.random.default_rng(W * 1000 + D)
+    d_candi = np.linspace(5., 40., D).astype(np.float32)
+    d_up = np.linspace(5., 40., 32).astype(np.float32)
+    fx = (W / 2) / np.tan(np.radians(8.0))
+    K = np.array([[fx, 0, W / 2], [0, fx, H / 2], [0, 0, 1]], np.float32)
+    eye = np.eye(4, dtype=np.float32)
+    P = {"intr_rgb": K, "dist_rgb": [0.] * 5, "size_rgb": [W, H], "intr_lc": K, "dist_lc": [0.] * 5, "size_lc": [W, H],
+         "rTc": eye, "lTc": _lTc(), "laser_fov": 80., "d_candi": d_candi, "r_candi": d_candi, "d_candi_up": d_up,
+         "r_candi_up": d_up, "name": "ragged", "laser_timestep": 3.5e-5, "device": torch.device("cuda", 0),
+         "expand_A": D, "expand_B": 32, "hit_noise": 0.0}
+    lc = LightCurtain()
+    lc.init(P)
+    depth = (8. + 6. * rng.random((H, W)) + 10. * (np.arange(W)[None, :] > W // 2)).astype(np.float32)
+    logp = torch.log_softmax(torch.tensor(rng.normal(size=(1, D, H, W)).astype(np.float32)) * 2.0, 1)
+    zs = [9.0 + 4.5 * i for i in range(nsweep)]
+    flats = np.stack([lc.get_flat(z) for z in zs])
+    dev = lc.rig("high").dev
+    planes = dev.curtain_planes(cu(flats))
+    out, mean = dev.sense_fuse(logp.cuda(), cu(depth).unsqueeze(0), planes, nsweep, d_candi, 2, 5)
+    olc = LO.LightCurtainOracle(K, W, H, d_candi, d_up)
+    liks = [olc.sense(depth, f)[0] for f in flats]
+    exp = O.bayes_fuse(logp, liks, 2, 5)
+    close(out, exp, atol=1e-5)
+    close(mean, O.dpv_expectation(exp, d_candi, True), atol=1e-4)
+    assert float((exp - logp).abs().max()) > 0.1
