@@ -7,6 +7,8 @@
 // the channel loop streams ref once and gathers src through L1/L2 (the 3.3 MB view is L2-resident;
 // lanes of a warp are 32 consecutive x at the same plane, so their taps fall on 1-2 lines per row),
 // and the only HBM write is the [D,h,w] cost.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace dpv {
@@ -52,6 +54,60 @@ __device__ __forceinline__ Taps make_taps(const float kt[3], const float krp[3],
   T.o10 = cy1 * w + cx0;
   T.o11 = cy1 * w + cx1;
   return T;
+}
+
+// The same taps as a 2 x 2 block anchored at (bx, by) with 0 <= bx <= w-2, 0 <= by <= h-2 (needs w, h >= 2): a tap that
+// falls outside the image has weight 0 (zeros padding), so when the block's natural anchor (x0, y0) is -1 or
+// w-1 / h-1 the anchor moves one pixel inside and the surviving weights move to the other column / row.  Every tap
+// then reads anchor + {0,1} + {0,1} * w: two offset registers per plane and immediate offsets instead of four
+// offsets (the plane-sweep kernel keeps DC planes' taps in registers: 6 instead of 8 registers per plane).
+struct TapsB {
+  int o0, o1;                    // offsets of the block's two rows
+  float w00, w01, w10, w11;
+};
+
+__device__ __forceinline__ TapsB make_taps_block(const float kt[3], const float krp[3], float d, float cu, float cv,
+                                                 int h, int w) {
+  float px = __fadd_rn(kt[0], __fmul_rn(krp[0], d));
+  float py = __fadd_rn(kt[1], __fmul_rn(krp[1], d));
+  float pz = __fadd_rn(kt[2], __fmul_rn(krp[2], d));
+  float z = __fadd_rn(pz, 1e-10f);
+  float u = __fdiv_rn(px, z), v = __fdiv_rn(py, z);
+  float gx = __fdiv_rn(__fsub_rn(u, cu), cu);
+  float gy = __fdiv_rn(__fsub_rn(v, cv), cv);
+  float ix = gs_unnormalize(gx, w), iy = gs_unnormalize(gy, h);
+  float fx0 = floorf(ix), fy0 = floorf(iy);
+  float tx = __fsub_rn(ix, fx0), ty = __fsub_rn(iy, fy0);
+  float ux = __fsub_rn(__fadd_rn(fx0, 1.f), ix), uy = __fsub_rn(__fadd_rn(fy0, 1.f), iy);
+  TapsB T;
+  T.w00 = __fmul_rn(ux, uy);
+  T.w01 = __fmul_rn(tx, uy);
+  T.w10 = __fmul_rn(ux, ty);
+  T.w11 = __fmul_rn(tx, ty);
+  bool finite = (ix > -2.f) && (ix < (float)(w + 1)) && (iy > -2.f) && (iy < (float)(h + 1));
+  int x0 = finite ? (int)fx0 : -2, y0 = finite ? (int)fy0 : -2;
+  const bool vx0 = x0 >= 0 && x0 < w, vx1 = x0 + 1 >= 0 && x0 + 1 < w;
+  const bool vy0 = y0 >= 0 && y0 < h, vy1 = y0 + 1 >= 0 && y0 + 1 < h;
+  if (!(vx0 && vy0)) T.w00 = 0.f;
+  if (!(vx1 && vy0)) T.w01 = 0.f;
+  if (!(vx0 && vy1)) T.w10 = 0.f;
+  if (!(vx1 && vy1)) T.w11 = 0.f;
+  const int bx = min(max(x0, 0), w - 2), by = min(max(y0, 0), h - 2);
+  if (x0 == bx + 1) { T.w01 = T.w00; T.w11 = T.w10; T.w00 = 0.f; T.w10 = 0.f; }       // x0 = w-1: only column x0 lives
+  else if (x0 == bx - 1) { T.w00 = T.w01; T.w10 = T.w11; T.w01 = 0.f; T.w11 = 0.f; }  // x0 = -1: only column 0 lives
+  if (y0 == by + 1) { T.w10 = T.w00; T.w11 = T.w01; T.w00 = 0.f; T.w01 = 0.f; }
+  else if (y0 == by - 1) { T.w00 = T.w10; T.w01 = T.w11; T.w10 = 0.f; T.w11 = 0.f; }
+  T.o0 = by * w + bx;
+  T.o1 = T.o0 + w;
+  return T;
+}
+
+__device__ __forceinline__ float tap_sample(const float* __restrict__ plane, const TapsB& T) {
+  float a = __ldg(plane + T.o0) * T.w00;
+  a += __ldg(plane + T.o0 + 1) * T.w01;
+  a += __ldg(plane + T.o1) * T.w10;
+  a += __ldg(plane + T.o1 + 1) * T.w11;
+  return a;
 }
 
 __device__ __forceinline__ float tap_sample(const float* __restrict__ plane, const Taps& T) {
@@ -130,6 +186,64 @@ plane_sweep_kernel(const float* __restrict__ ref, const float* __restrict__ src,
     if (d0 + j < D) cost[((size_t)b * D + d0 + j) * hw + pix] = acc[j];
 }
 
+#ifndef DPV_SWEEP_MINB
+#define DPV_SWEEP_MINB 8
+#endif
+
+// plane_sweep_kernel on 2 x 2 tap blocks (images of at least 2 x 2 pixels): fewer registers, more resident warps.
+// The gathers go through L1 at its wavefront rate (32 consecutive x read ~32 consecutive words of a source row that
+// straddle two 128-byte lines), so what helps is resident warps, not work per thread: 4 planes per thread at 64
+// registers (32 warps per SM) measured 0.517 ms at C2 against 0.598 ms for 8 planes at 252 registers; staging the
+// source footprint of a 32 x 4 tile in shared memory instead was slower (0.76 ms: the copy and the same number of
+// wavefronts, now on the shared-memory side of the same pipe).
+template <int DC, int METRIC>
+__global__ void __launch_bounds__(128, DPV_SWEEP_MINB)
+plane_sweep_block_kernel(const float* __restrict__ ref, const float* __restrict__ src, int V, int C, int h, int w,
+                   const float* __restrict__ K, const float* __restrict__ R, const float* __restrict__ t,
+                   const float* __restrict__ rays, long long rays_bstride, const float* __restrict__ center,
+                   const float* __restrict__ d_candi, int D, float sigma, float* __restrict__ cost) {
+  const int hw = h * w;
+  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
+  const int d0 = blockIdx.y * DC;
+  const int b = blockIdx.z;
+  if (pix >= hw) return;
+  const float cu = center[b * 2 + 0], cv = center[b * 2 + 1];
+  const float* ray = rays + (size_t)b * rays_bstride;
+  const float r0 = ray[pix], r1 = ray[hw + pix], r2 = ray[2 * hw + pix];
+  float acc[DC];
+#pragma unroll
+  for (int j = 0; j < DC; j++) acc[j] = 0.f;
+  const float* refp = ref + (size_t)b * C * hw + pix;
+  for (int v = 0; v < V; v++) {
+    float M[9], kt[3], krp[3];
+    pose_terms(K + b * 9, R + ((size_t)b * V + v) * 9, t + ((size_t)b * V + v) * 3, M, kt);
+#pragma unroll
+    for (int i = 0; i < 3; i++) krp[i] = fmaf(M[i * 3 + 2], r2, fmaf(M[i * 3 + 1], r1, M[i * 3 + 0] * r0));
+    TapsB T[DC];
+#pragma unroll
+    for (int j = 0; j < DC; j++) T[j] = make_taps_block(kt, krp, d_candi[min(d0 + j, D - 1)], cu, cv, h, w);
+    const float* sp = src + ((size_t)b * V + v) * C * hw;
+    float dist[DC];
+#pragma unroll
+    for (int j = 0; j < DC; j++) dist[j] = 0.f;
+#pragma unroll 2
+    for (int c = 0; c < C; c++) {
+      const float r = __ldg(refp + (size_t)c * hw);
+      const float* plane = sp + (size_t)c * hw;
+#pragma unroll
+      for (int j = 0; j < DC; j++) {
+        float diff = tap_sample(plane, T[j]) - r;
+        dist[j] += METRIC == 0 ? diff * diff : fabsf(diff);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < DC; j++) acc[j] += dist[j] / sigma;       // homography.py:129
+  }
+#pragma unroll
+  for (int j = 0; j < DC; j++)
+    if (d0 + j < D) cost[((size_t)b * D + d0 + j) * hw + pix] = acc[j];
+}
+
 // out[b,v,i,y,x] = bilinear(src[b,v,i], H_{d_i} p): thread = (pixel, plane i, view v, frame b).
 __global__ void __launch_bounds__(128)
 warp_feature_kernel(const float* __restrict__ src, int T_, int C, int h, int w, const float* __restrict__ K,
@@ -168,9 +282,20 @@ int dpv_plane_sweep(const float* ref, const float* src, int B, int V, int C, int
   // homography.py:84-86: raise Exception('undefined metric for feature distance ...')
   DPV_REQUIRE(metric == 0 || metric == 1, "undefined metric for feature distance ...");
   cudaStream_t st = (cudaStream_t)stream;
-  constexpr int DC = 8;
+#ifndef DPV_SWEEP_DC
+#define DPV_SWEEP_DC 4
+#endif
+  constexpr int DC = DPV_SWEEP_DC;
   dim3 grid((h * w + 127) / 128, (D + DC - 1) / DC, B);
-  if (metric == 0)
+  static const bool block_taps = !(getenv("DPV_SWEEP_BLOCK") && atoi(getenv("DPV_SWEEP_BLOCK")) == 0);   // tuning aid
+  if (block_taps && w >= 2 && h >= 2) {
+    if (metric == 0)
+      plane_sweep_block_kernel<DC, 0><<<grid, 128, 0, st>>>(ref, src, V, C, h, w, K, R, t, rays, rays_batch_stride,
+                                                           center, d_candi, D, sigma, cost);
+    else
+      plane_sweep_block_kernel<DC, 1><<<grid, 128, 0, st>>>(ref, src, V, C, h, w, K, R, t, rays, rays_batch_stride,
+                                                           center, d_candi, D, sigma, cost);
+  } else if (metric == 0)
     plane_sweep_kernel<DC, 0><<<grid, 128, 0, st>>>(ref, src, V, C, h, w, K, R, t, rays, rays_batch_stride, center,
                                                    d_candi, D, sigma, cost);
   else
