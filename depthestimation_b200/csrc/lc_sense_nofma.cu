@@ -65,6 +65,34 @@ sense_likelihood_kernel(LcDeviceView dv, const float* __restrict__ planes, const
     if (d < D) st_stream(o + (size_t)d * HW, mix_value(soft_g(dc[d], L), sg, L) / sm);
 }
 
+// The tail of sense_high / sense_low (lc/light_curtain.py:869-888) on maps that have already been brought into the
+// RGB camera by transformPoints (the rTc != I branch, :850-858): maps [n,3,H,W] = (depth, intensity, thickness).
+template <int DPT>
+__global__ void __launch_bounds__(kSenseThreads)
+likelihood_maps_kernel(const float* __restrict__ maps, const float* __restrict__ depth, int per_depth, long long npix,
+                       size_t HW, const float* __restrict__ d_candi, int D, float* __restrict__ lik) {
+  __shared__ float dc[DPT];
+  for (int i = threadIdx.x; i < DPT; i += blockDim.x) dc[i] = i < D ? d_candi[i] : 0.f;
+  __syncthreads();
+  const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pix >= npix) return;
+  const size_t cu = (size_t)(pix / (long long)HW), hw = (size_t)(pix - (long long)cu * HW);
+  const float* m = maps + cu * 3 * HW + hw;
+  Ret r;
+  r.x = r.y = 0.f;                                    // not NaN: the maps carry 0 where nothing was sensed
+  r.z = m[0];
+  r.inten = m[HW];
+  r.thick = m[2 * HW];
+  const float gt = depth[(cu / per_depth) * HW + hw];
+  Lik L = lik_params(r, gt, D);
+  float sg, sm;
+  lik_sums<DPT>(dc, D, L, sg, sm);
+  float* o = lik + cu * D * HW + hw;
+#pragma unroll
+  for (int d = 0; d < DPT; d++)
+    if (d < D) st_stream(o + (size_t)d * HW, mix_value(soft_g(dc[d], L), sg, L) / sm);
+}
+
 }  // namespace dpv
 
 using namespace dpv;
@@ -97,6 +125,24 @@ int lc_sense_likelihood(const LcDevice* dev, const float* planes, const float* d
   else LAUNCH(128);
 #undef LAUNCH
   return check_launch("lc_sense_likelihood");
+}
+
+int lc_likelihood_maps(const float* maps, const float* depth, int B, int nc, int H, int W, const float* d_candi, int D,
+                       float* lik, void* stream) {
+  DPV_REQUIRE(maps && depth && d_candi && lik, "lc_likelihood_maps: null pointer");
+  DPV_REQUIRE(B > 0 && nc > 0 && H > 0 && W > 0 && D > 0, "lc_likelihood_maps: bad shape");
+  DPV_REQUIRE(D <= 128, "lc_likelihood_maps: D=%d > 128 unsupported", D);
+  const size_t HW = (size_t)H * W;
+  const long long npix = (long long)B * nc * (long long)HW;
+  const unsigned g = (unsigned)((npix + kSenseThreads - 1) / kSenseThreads);
+  cudaStream_t st = (cudaStream_t)stream;
+#define LAUNCH(DPT) likelihood_maps_kernel<DPT><<<g, kSenseThreads, 0, st>>>(maps, depth, nc, npix, HW, d_candi, D, lik)
+  if (D <= 16) LAUNCH(16);
+  else if (D <= 32) LAUNCH(32);
+  else if (D <= 64) LAUNCH(64);
+  else LAUNCH(128);
+#undef LAUNCH
+  return check_launch("lc_likelihood_maps");
 }
 
 }  // extern "C"

@@ -75,9 +75,11 @@ class LightCurtain:
 
     def init(self, PARAMS):
         self.PARAMS = PARAMS
-        if not np.all(np.equal(np.asarray(PARAMS["rTc"]), np.eye(4))) or \
-                PARAMS["size_rgb"][0] != PARAMS["size_lc"][0] or PARAMS["size_rgb"][1] != PARAMS["size_lc"][1]:
-            raise NotImplementedError("rTc != I / differing LC camera (transformPoints path) is a 'next' row")
+        # light_curtain.py:324-329.  With a separately posed / sized LC camera, sensing re-projects through
+        # transformPoints (:824-858, built); planning needs FieldWarp.transformZTheta (:118-165), which is not.
+        self.transform_needed = bool(
+            not np.all(np.equal(np.asarray(PARAMS["rTc"]), np.eye(4))) or
+            PARAMS["size_rgb"][0] != PARAMS["size_lc"][0] or PARAMS["size_rgb"][1] != PARAMS["size_lc"][1])
         if np.any(np.asarray(PARAMS["dist_lc"]) != 0) or np.any(np.asarray(PARAMS["dist_rgb"]) != 0):
             raise NotImplementedError("lens distortion is out of scope")
         self.d_candi = PARAMS["d_candi"]
@@ -88,7 +90,6 @@ class LightCurtain:
         self.expand_A = PARAMS["expand_A"]
         self.expand_B = PARAMS["expand_B"]
         self.device = torch.device(PARAMS["device"])
-        self.transform_needed = False
         self.hit_noise = PARAMS.get("hit_noise", 0.01)             # light_curtain.py:275-276
         self._rigs = {}
         self.initialized = True
@@ -132,8 +133,14 @@ class LightCurtain:
                 "name": "default", "laser_timestep": 3.5e-5, "device": model_input["intrinsics"].device}
 
     # ---- planning (light_curtain.py:646-739) --------------------------------------------------
+    def _no_field_transform(self):
+        if self.transform_needed:
+            raise NotImplementedError("planning with rTc != I / a differently sized LC camera needs "
+                                      "FieldWarp.transformZTheta (lc/light_curtain.py:118-165): not built")
+
     def plan_batched(self, uf, steps, mode="high"):
         """uf [B,D,W] -> dict(xz [B,nc,W,2], ks [B,nc,W] int32, counts [B,nc] int32, umaps, argmax, field_pre)."""
+        self._no_field_transform()
         r = self.rig(mode)
         R = len(self.r_candi_up)
         umaps, amax, pre = ops.plan_prepare(uf, r.flow, steps, R)
@@ -166,6 +173,7 @@ class LightCurtain:
     def _field_visual(self, field, mode, flags):
         """The polar planning field as the reference's [R,W,3] visual (:475-480): the warp runs on the GPU, the
         side columns are copied from their neighbours afterwards."""
+        self._no_field_transform()
         r = self.rig(mode)
         fr, _ = ops.plan_field(field.unsqueeze(0), r.flow, len(self.r_candi_up), flags)
         fr = fr[0]
@@ -224,12 +232,33 @@ class LightCurtain:
     # ---- sensing (light_curtain.py:741-910) ---------------------------------------------------
     def _sense(self, depth_rgb, design_pts_lc, mode, noise=None):
         r = self.rig(mode)
-        depth = ops.f32(depth_rgb, self.device).reshape(1, r.dev.H, r.dev.W)
         pts = ops.f32(design_pts_lc, self.device)[:, :2].contiguous().unsqueeze(0)
         planes = r.dev.curtain_planes(pts)
         if noise is None:
             noise = r.dev.noise_like(1)
-        lik = r.dev.sense_likelihood(planes, depth, 1, self.d_candi, noise)
+        if not self.transform_needed:
+            depth = ops.f32(depth_rgb, self.device).reshape(1, r.dev.H, r.dev.W)
+            lik = r.dev.sense_likelihood(planes, depth, 1, self.d_candi, noise)
+            return lik[0], None, {}
+        # rTc != I (light_curtain.py:824-858 / :744-770): the RGB depth map is re-projected into the LC camera
+        # (z-buffer, outlier filter 2), sensed there, and the return re-projected into the RGB camera
+        P = self.PARAMS
+        sc = 1.0 if mode == "high" else 0.25
+        K_rgb = np.asarray(P["intr_rgb"], np.float32) if mode == "high" else intr_scale_unit(P["intr_rgb"], sc)
+        K_lc = np.asarray(P["intr_lc"], np.float32) if mode == "high" else intr_scale_unit(P["intr_lc"], sc)
+        size_rgb = (int(P["size_rgb"][0] * sc), int(P["size_rgb"][1] * sc))
+        depth = ops.f32(depth_rgb, self.device).reshape(size_rgb[1], size_rgb[0])
+        xyz = img_utils.depth_to_pts(depth.unsqueeze(0), K_rgb)                              # [3,H,W]
+        pts_rgb = torch.cat([xyz.reshape(3, -1), torch.ones(1, depth.numel(), device=self.device)]).t().contiguous()
+        depth_lc = lcsim.transform_points(pts_rgb.unsqueeze(0), torch.ones(1, depth.numel(), device=self.device),
+                                          K_lc, P["cTr"], r.dev.W, r.dev.H, 2)[:, 0].contiguous()
+        img, th = r.dev.sense_image(planes, depth_lc, 1, noise)
+        dead = torch.isnan(img[..., 0])                                                      # :847-848
+        img[dead] = 0
+        th[torch.isnan(th)] = 0
+        maps = lcsim.transform_points(img.reshape(1, -1, 4), th.reshape(1, -1), K_rgb, P["rTc"], size_rgb[0],
+                                      size_rgb[1], 0)
+        lik = ops.likelihood_maps(maps, depth.unsqueeze(0), 1, self.d_candi)
         return lik[0], None, {}
 
     def sense_high(self, depth_rgb, design_pts_lc, visualizer=None, noise=None):

@@ -169,6 +169,21 @@ def plan_prepare(uf, flow, steps, R, umaps=None, argmax=None, field_pre=None):
     return umaps, argmax, field_pre
 
 
+def likelihood_maps(maps, depth, nc, d_candi):
+    """maps [B*nc,3,H,W] (lc_transform_points output), depth [B,H,W] -> lik [B*nc,D,H,W] (sense_high tail, :869-888)."""
+    maps = f32(maps)
+    dev = maps.device
+    depth = f32(depth, dev)
+    n, _, H, W = maps.shape
+    B = n // int(nc)
+    dc = d_candi_tensor(d_candi, dev)
+    lik = torch.empty(n, dc.numel(), H, W, device=dev, dtype=torch.float32)
+    with torch.cuda.device(dev):
+        check(lib().lc_likelihood_maps(ptr(maps), ptr(depth), B, int(nc), H, W, ptr(dc), dc.numel(), ptr(lik),
+                                       stream_ptr(dev)))
+    return lik
+
+
 def plan_field(uf, flow, R, flags=7):
     """uf [B,D,W], flow [R,W,2] -> (field_range [B,R,W], field_pre [B,R,W]); flags = LC_FIELD_* (include/dpv_b200.h)."""
     dev = _dev(uf)

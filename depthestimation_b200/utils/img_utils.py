@@ -63,6 +63,22 @@ def gen_ufield(dpv_predicted, d_candi, intr_up, visualizer=None, img=None, BV_lo
     return uf, dz
 
 
+def depth_to_pts(depthf, intr):                                      # img_utils.py:269-293
+    """depthf [1,H,W] (CUDA) -> point cloud [3,H,W] = ((u - cx) / fx * d, (v - cy) / fy * d, d); the reference's own
+    elementwise torch expressions, evaluated on the GPU."""
+    if depthf.shape[0] != 1:
+        raise Exception('Unable to handle this case')
+    depth = depthf[0, :, :]
+    intr = np.asarray(intr.cpu() if torch.is_tensor(intr) else intr, dtype=np.float32)
+    fx, cx, fy, cy = intr[0, 0], intr[0, 2], intr[1, 1], intr[1, 2]
+    yfield, xfield = torch.meshgrid([torch.arange(0, depth.shape[0]).float().to(depthf.device),
+                                     torch.arange(0, depth.shape[1]).float().to(depthf.device)], indexing="ij")
+    yfield = (yfield - float(cy)) / float(fy)
+    xfield = (xfield - float(cx)) / float(fx)
+    return torch.cat([torch.mul(xfield, depth).unsqueeze(0), torch.mul(yfield, depth).unsqueeze(0),
+                      depth.unsqueeze(0)], 0)
+
+
 def gen_dpv_withmask(dmaps, masks, d_candi, var=0.3):                # img_utils.py:567-582
     return ops.truth_dpv(dmaps, masks, d_candi, var)
 

@@ -195,6 +195,11 @@ size_t lc_transform_points_scratch_bytes(int n, int width, int height, int filte
 int lc_transform_points(const float* pts, const float* thick, int n, int N, const float* intr, const float* M,
                         int width, int height, int filtering, float* maps, void* scratch, size_t scratch_bytes,
                         void* stream);
+/* The tail of sense_high / sense_low (lc/light_curtain.py:869-888) for a sensor whose returns had to be re-projected
+ * (rTc != I, :850-858): maps [B*nc,3,H,W] = lc_transform_points output in the RGB camera, depth [B,H,W] (the
+ * ground-truth depth whose > 0 mask gates the pixel)  ->  lik [B*nc,D,H,W], the same mixture as lc_sense_likelihood. */
+int lc_likelihood_maps(const float* maps, const float* depth, int B, int nc, int H, int W, const float* d_candi, int D,
+                       float* lik, void* stream);
 /* BaseModel.lc_process_real's sampling of a recorded sweep (models/models.py:924-927):
  * sampling_depth [B,nc,H,W], feat_z / feat_int [B,K,H,W] -> out [B,nc,H,W] = feat_int at the slice whose depth is
  * nearest to sampling_depth (torch.argmin semantics: first minimum, NaN first), inds (nullable) [B,nc,H,W]. */

@@ -162,6 +162,35 @@ class LightCurtainOracle:
         return O.curtain_likelihood(self.d_candi, depth_gt, img[:, :, 2], img[:, :, 3], th), img, th
 
 
+def sense_transformed(depth_rgb, pts, K_rgb, size_rgb, K_lc, size_lc, rTc, lTc, d_candi, laser_fov=80.0,
+                      laser_timestep=3.5e-5):
+    """sense_high for a separately posed / sized LC camera (lc/light_curtain.py:824-888, the rTc != I branch):
+    RGB depth -> points (img_utils.depth_to_pts :269-293) -> LC depth map (transformPoints, filtering 2) -> curtain
+    return -> back into the RGB camera (transformPoints, filtering 0) -> mixture likelihood.  -> DPV [D,H,W]."""
+    depth_rgb = np.asarray(depth_rgb, np.float32)
+    Wr, Hr = int(size_rgb[0]), int(size_rgb[1])
+    Wl, Hl = int(size_lc[0]), int(size_lc[1])
+    K_rgb, K_lc = np.asarray(K_rgb, np.float32), np.asarray(K_lc, np.float32)
+    d = torch.tensor(depth_rgb)
+    yf, xf = torch.meshgrid([torch.arange(0, Hr).float(), torch.arange(0, Wr).float()], indexing="ij")
+    yf = (yf - K_rgb[1, 2]) / K_rgb[1, 1]
+    xf = (xf - K_rgb[0, 2]) / K_rgb[0, 0]
+    cloud = torch.cat([(xf * d).unsqueeze(0), (yf * d).unsqueeze(0), d.unsqueeze(0)], 0).reshape(3, -1)
+    pts_rgb = torch.cat([cloud, torch.ones(1, cloud.shape[1])]).numpy().T
+    cTr = np.linalg.inv(np.asarray(rTc))                              # :318
+    depth_lc, _, _ = lcsim.transformPoints(pts_rgb, np.ones((pts_rgb.shape[0], 1), np.float32), K_lc, cTr, Wl, Hl,
+                                           {"filtering": 2})           # :831-833
+    dev = lcsim.LCDevice(CAMERA_PARAMS=dict(width=Wl, height=Hl, matrix=K_lc, distortion=[0.] * 5, hit_mode=1,
+                                            hit_noise=0.0),
+                         LASER_PARAMS=dict(lTc=lTc, fov=laser_fov, laser_timestep=laser_timestep))
+    img, th = dev.get_return(depth_lc, np.asarray(pts, np.float32), True)
+    img[np.isnan(img[:, :, 0])] = 0                                   # :847-848
+    th[np.isnan(th)] = 0
+    ds, it, ts = lcsim.transformPoints(img.reshape(-1, 4), th.flatten(), K_rgb, np.asarray(rTc), Wr, Hr,
+                                       {"filtering": 0})               # :851-858
+    return O.curtain_likelihood(d_candi, depth_rgb, ds, it, ts)
+
+
 def lc_loop(logp, depth_gt, lc, K_up, uf_par, iterations, steps, spread_iter, spread_n, trace=None, sweep=None):
     """BaseModel.lc_process body for ONE sample, mode='high', planner='default' -- or planner='sweep' when `sweep`
     = dict(start, end, step) is given (models/models.py:1010-1127).  logp [1,D,H,W] log-DPV; depth_gt [H,W] numpy

@@ -222,6 +222,40 @@ def case_plan_sweep():
          pts=np.stack(pts), field_visual=vis)
 
 
+def case_sense_transformed():
+    """sense_high with a separately posed, differently sized LC camera (rTc != I: lc/light_curtain.py:824-858, the
+    transformPoints branch) on the unmodified reference (lcsim restated) -> sense_rtc.npz."""
+    _install_lcsim_stubs()
+    import lc.light_curtain as LC
+    g = torch.Generator().manual_seed(21)
+    D = 16
+    Wr, Hr, Wl, Hl = 64, 32, 80, 40
+    d = IU.powerf(5., 40., D, 1.0)
+    d_up = IU.powerf(5., 40., 32, 1.0)
+    K_rgb = np.array([[150., 0., 32.], [0., 150., 16.], [0., 0., 1.]], np.float32)
+    K_lc = np.array([[170., 0., 40.], [0., 170., 20.], [0., 0., 1.]], np.float32)
+    a = np.radians(2.0)
+    rTc = np.eye(4, dtype=np.float32)
+    rTc[:3, :3] = np.array([[np.cos(a), 0., np.sin(a)], [0., 1., 0.], [-np.sin(a), 0., np.cos(a)]], np.float32)
+    rTc[:3, 3] = [0.06, -0.03, 0.02]
+    lTc = np.eye(4, dtype=np.float32)
+    lTc[0, 3] = 0.2
+    P = {"intr_rgb": K_rgb, "dist_rgb": [0.] * 5, "size_rgb": [Wr, Hr], "intr_lc": K_lc, "dist_lc": [0.] * 5,
+         "size_lc": [Wl, Hl], "rTc": rTc, "lTc": lTc, "laser_fov": 80., "d_candi": d, "r_candi": d,
+         "d_candi_up": d_up, "r_candi_up": d_up, "name": "golden_rtc", "laser_timestep": 3.5e-5,
+         "device": torch.device("cpu"), "expand_A": D, "expand_B": 32}
+    lc = LC.LightCurtain()
+    lc.init(P)
+    lc.lightcurtain_large.hit_noise = 0.0 if hasattr(lc.lightcurtain_large, "hit_noise") else None
+    depth = (9. + 5. * torch.rand(Hr, Wr, generator=g)).numpy().astype(np.float32)
+    depth[:, 40:] += 9.
+    depth[3:6, 5:9] = 0.                                     # masked-out pixels (depth_rgb > 0)
+    pts = np.array([[x, 11.0 + 0.05 * x] for x in np.arange(-6., 6., 0.02)], np.float32)
+    dpv, _, _ = lc.sense_high(depth, pts, None)
+    save("sense_rtc", K_rgb=K_rgb, K_lc=K_lc, size_rgb=np.array([Wr, Hr]), size_lc=np.array([Wl, Hl]), rTc=rTc,
+         lTc=lTc, d_candi=d, d_candi_up=d_up, depth=depth, pts=pts, dpv=dpv)
+
+
 def case_aux():
     """Rows a17 (gen_lc_dpv_true), a18 (inverse_warp), a19 (correlation_native twin) and compute_unc_rmse,
     run on the unmodified reference -> aux.npz."""
@@ -297,3 +331,4 @@ if __name__ == "__main__":
     case_lcsim_fixture()
     case_aux()
     case_plan_sweep()
+    case_sense_transformed()

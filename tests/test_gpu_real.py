@@ -111,3 +111,35 @@ def test_sweep_sample_bit_exact(nc):
     ref, rinds = A.sweep_sample(sd, fz, fi)
     np.testing.assert_array_equal(inds.cpu().numpy(), rinds.numpy().astype(np.int32))
     np.testing.assert_array_equal(out.cpu().numpy(), ref.numpy())
+
+
+def test_sense_high_with_separate_lc_camera_golden():
+    """LightCurtain.sense_high for rTc != I and a differently sized LC camera (lc/light_curtain.py:824-888): RGB depth
+    -> LC camera (z-buffer + outlier filter) -> simulated return -> RGB camera (z-buffer) -> mixture likelihood, all on
+    the GPU, against the unmodified reference's output (tests/golden/sense_rtc.npz) and the oracle."""
+    import os
+    from depthestimation_b200.lc.light_curtain import LightCurtain
+    from oracle import lc_oracle as LO
+    g = dict(np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "sense_rtc.npz")))
+    P = {"intr_rgb": g["K_rgb"], "dist_rgb": [0.] * 5, "size_rgb": [int(v) for v in g["size_rgb"]],
+         "intr_lc": g["K_lc"], "dist_lc": [0.] * 5, "size_lc": [int(v) for v in g["size_lc"]], "rTc": g["rTc"],
+         "lTc": g["lTc"], "laser_fov": 80., "d_candi": g["d_candi"], "r_candi": g["d_candi"],
+         "d_candi_up": g["d_candi_up"], "r_candi_up": g["d_candi_up"], "name": "rtc", "laser_timestep": 3.5e-5,
+         "device": torch.device("cuda", 0), "expand_A": len(g["d_candi"]), "expand_B": len(g["d_candi_up"]),
+         "hit_noise": 0.0}
+    lc = LightCurtain()
+    lc.init(P)
+    assert lc.transform_needed
+    dpv, _, _ = lc.sense_high(g["depth"], torch.as_tensor(g["pts"]).cuda())
+    ref = g["dpv"]
+    got = dpv.cpu().numpy()
+    # a point that projects within float rounding of a pixel border may land in the neighbouring pixel of the
+    # z-buffer: such pixels are counted, not compared (none are expected at this size)
+    bad = np.abs(got - ref).max(0) > 1e-4 * np.maximum(np.abs(ref).max(0), 1e-3)
+    assert bad.mean() < 0.005, bad.mean()
+    np.testing.assert_allclose(got[:, ~bad], ref[:, ~bad], rtol=1e-4, atol=1e-6)
+    exp = LO.sense_transformed(g["depth"], g["pts"], g["K_rgb"], g["size_rgb"], g["K_lc"], g["size_lc"], g["rTc"],
+                               g["lTc"], g["d_candi"]).numpy()
+    np.testing.assert_allclose(got[:, ~bad], exp[:, ~bad], rtol=1e-4, atol=1e-6)
+    with pytest.raises(NotImplementedError):               # planning needs FieldWarp.transformZTheta: not built
+        lc.plan_default_high(torch.rand(len(g["d_candi"]), int(g["size_rgb"][0])).cuda(), {"step": [0.5]})

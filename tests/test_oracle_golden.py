@@ -132,6 +132,14 @@ def test_plan_sweep_against_reference():
     close(vis, g["field_visual"], rtol=1e-6, atol=1e-7)
 
 
+def test_sense_with_separate_lc_camera_against_reference():
+    """sense_high's rTc != I branch (lc/light_curtain.py:824-888) restated on top of the restated transformPoints."""
+    g = load("sense_rtc")
+    dpv = LO.sense_transformed(g["depth"], g["pts"], g["K_rgb"], g["size_rgb"], g["K_lc"], g["size_lc"], g["rTc"],
+                               g["lTc"], g["d_candi"])
+    close(dpv, g["dpv"], rtol=1e-6, atol=1e-7)
+
+
 def test_aux_rows_against_reference():
     from oracle import aux_oracle as A
     g = load("aux")
