@@ -44,6 +44,8 @@ SIGNATURES = {
                            ctypes.POINTER(DpvUfieldParams), c_fp, c_fp, c_vp, ctypes.c_size_t, c_vp]),
     "lc_plan_prepare": (c_int, [c_fp, c_int, c_int, c_int, c_int, c_fp, c_fp, c_int, c_fp, c_ip, c_fp, c_vp]),
     "lc_plan_field": (c_int, [c_fp, c_int, c_int, c_int, c_int, c_fp, c_int, c_fp, c_fp, c_vp]),
+    "lc_plan_prepare_transformed": (c_int, [c_fp, c_int, c_int, c_int, c_int, c_int, c_fp, c_fp, c_fp, c_int, c_int,
+                                            c_fp, c_ip, c_fp, c_fp, c_vp]),
     "lc_device_create": (c_int, [c_int, c_int, c_fp, c_fp, c_f, c_f, c_f, c_f, c_f, c_int, c_f,
                                  ctypes.POINTER(c_vp)]),
     "lc_device_destroy": (None, [c_vp]),

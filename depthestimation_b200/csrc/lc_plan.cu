@@ -116,6 +116,144 @@ plan_prep_columns_kernel(const float* __restrict__ uf, int D, int W, int R, int 
 }
 
 // ---------------------------------------------------------------------------------------------
+// P1 for an LC camera whose width differs from the field's (FieldWarp.preprocess :79-85 resizes BOTH axes):
+// side fix -> NaN columns -> bilinear [D,Win] -> [R,Wout] -> 5-tap depth mean.  Normalisation comes after the
+// RGB->LC warp (:676-681), in field_normalize_kernel.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ int side_fixed(int c, int W) {          // field[:,0]=field[:,1]; field[:,-1]=field[:,-2]
+  if (c == 0 || W == 2) return 1;
+  if (c == W - 1) return W - 2;
+  return c;
+}
+
+__device__ __forceinline__ void resize_taps(int x, float scale, int Win, int& x0, int& x1, float& l0, float& l1) {
+  const float s = fmaxf(scale * ((float)x + 0.5f) - 0.5f, 0.f);    // ATen area_pixel_compute_source_index
+  x0 = min((int)s, Win - 1);
+  x1 = x0 + (x0 < Win - 1 ? 1 : 0);
+  if (scale == 1.f) x1 = x0;                     // ATen leaves an axis that keeps its size alone (no 0 * NaN from x+1)
+  l1 = s - (float)x0;
+  l0 = 1.f - l1;
+}
+
+__global__ void __launch_bounds__(kPrepCols* kPrepWarps)
+plan_prep_resize_kernel(const float* __restrict__ uf, int D, int Win, int R, int Wout, int flags,
+                        float* __restrict__ out) {
+  extern __shared__ float sm[];
+  float* u = sm;                                 // [D][32] x-interpolated columns
+  float* f0 = sm + (size_t)D * kPrepCols;        // [R][32]
+  __shared__ int nan0[kPrepCols], nan1[kPrepCols];
+  __shared__ int has_bad[kPrepCols + 4];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int b = blockIdx.y;
+  const int x = blockIdx.x * kPrepCols + lane;
+  const bool xin = x < Wout;
+  const float* f = uf + (size_t)b * D * Win;
+  const float scale_w = (float)Win / (float)Wout;
+  int x0, x1;
+  float lx0, lx1;
+  resize_taps(xin ? x : 0, scale_w, Win, x0, x1, lx0, lx1);
+  const int c0 = side_fixed(x0, Win), c1 = side_fixed(x1, Win);
+  if (threadIdx.x < kPrepCols) nan0[threadIdx.x] = nan1[threadIdx.x] = 0;
+  if (threadIdx.x < kPrepCols + 4) has_bad[threadIdx.x] = 0;
+  __syncthreads();
+  bool n0 = false, n1 = false, i0 = false, i1 = false;
+  for (int d = warp; d < D; d += kPrepWarps) {
+    const float a = f[(size_t)d * Win + c0], c = f[(size_t)d * Win + c1];
+    n0 |= (a != a);
+    n1 |= (c != c);
+    i0 |= (fabsf(a) == INFINITY);
+    i1 |= (fabsf(c) == INFINITY);
+  }
+  if (n0) nan0[lane] = 1;
+  if (n1) nan1[lane] = 1;
+  if (xin && (i0 || i1 || ((n0 || n1) && !(flags & 1)))) has_bad[lane + 2] = 1;
+  if (lane < 4) {                                // the two output columns either side of this block's 32
+    const int hx = blockIdx.x * kPrepCols + (lane < 2 ? lane - 2 : kPrepCols + lane - 2);
+    if (hx >= 0 && hx < Wout) {
+      int h0, h1;
+      float t0, t1;
+      resize_taps(hx, scale_w, Win, h0, h1, t0, t1);
+      h0 = side_fixed(h0, Win);
+      h1 = side_fixed(h1, Win);
+      bool bad = false;
+      for (int d = warp; d < D; d += kPrepWarps) {
+        const float a = f[(size_t)d * Win + h0], c = f[(size_t)d * Win + h1];
+        bad |= (fabsf(a) == INFINITY) || (fabsf(c) == INFINITY) || ((a != a || c != c) && !(flags & 1));
+      }
+      if (bad) has_bad[lane < 2 ? lane : kPrepCols + lane] = 1;
+    }
+  }
+  __syncthreads();
+  const bool r0 = (flags & 1) && nan0[lane], r1 = (flags & 1) && nan1[lane];        // :658-662
+  for (int d = warp; d < D; d += kPrepWarps) {
+    const float fill = (d == D - 1) ? 1.0f : eps_floor();
+    const float a = r0 ? fill : f[(size_t)d * Win + c0];
+    const float c = r1 ? fill : f[(size_t)d * Win + c1];
+    u[d * kPrepCols + lane] = lx0 * a + lx1 * c;
+  }
+  __syncthreads();
+  const float scale = (float)D / (float)R;
+  for (int r = warp; r < R; r += kPrepWarps) {
+    float s = fmaxf(scale * ((float)r + 0.5f) - 0.5f, 0.f);
+    int j0 = (int)s;
+    int j1 = j0 + (j0 < D - 1 ? 1 : 0);
+    float l1 = s - (float)j0, l0 = 1.f - l1;
+    f0[r * kPrepCols + lane] = l0 * u[j0 * kPrepCols + lane] + l1 * u[j1 * kPrepCols + lane];
+  }
+  __syncthreads();
+  const bool spread = has_bad[lane] | has_bad[lane + 1] | has_bad[lane + 3] | has_bad[lane + 4];
+  for (int r = warp; r < R; r += kPrepWarps) {
+    float s = 0.f;
+#pragma unroll
+    for (int j = -2; j <= 2; j++) {
+      int rr = r + j;
+      if (rr >= 0 && rr < R) s += 0.2f * f0[rr * kPrepCols + lane];
+    }
+    if (spread) s = NAN;                         // same 5x5-kernel spread as plan_prep_columns_kernel
+    if (xin) out[((size_t)b * R + r) * Wout + x] = s;
+  }
+}
+
+// normalize (:207-210) and NaN -> eps (:681) of an [R,W] field, one column per lane.
+__global__ void __launch_bounds__(kPrepCols* kPrepWarps)
+field_normalize_kernel(const float* __restrict__ in, int W, int R, int flags, float* __restrict__ out) {
+  __shared__ float lo_s[kPrepWarps][kPrepCols], hi_s[kPrepWarps][kPrepCols];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int b = blockIdx.y;
+  const int x = blockIdx.x * kPrepCols + lane;
+  const bool xin = x < W;
+  const float* f = in + (size_t)b * R * W;
+  float lo = INFINITY, hi = -INFINITY;
+  bool any_nan = false;
+  for (int r = warp; r < R; r += kPrepWarps) {
+    const float s = xin ? f[(size_t)r * W + x] : 0.f;
+    lo = fminf(lo, s);
+    hi = fmaxf(hi, s);
+    any_nan |= (s != s);
+  }
+  if (any_nan) lo = hi = NAN;
+  lo_s[warp][lane] = lo;
+  hi_s[warp][lane] = hi;
+  __syncthreads();
+  lo = lo_s[0][lane];
+  hi = hi_s[0][lane];
+#pragma unroll
+  for (int k = 1; k < kPrepWarps; k++) {
+    float a = lo_s[k][lane], c = hi_s[k][lane];
+    lo = (a != a || lo != lo) ? NAN : fminf(lo, a);
+    hi = (c != c || hi != hi) ? NAN : fmaxf(hi, c);
+  }
+  const float span = hi - lo;
+  if (!xin) return;
+  for (int r = warp; r < R; r += kPrepWarps) {
+    float v = f[(size_t)r * W + x];
+    if (flags & 2) v = (v - lo) / span;
+    if ((flags & 4) && v != v) v = eps_floor();
+    out[((size_t)b * R + r) * W + x] = v;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // P2: polar z->range warp (FieldWarp.warp :47-58, bilinear grid_sample, zeros, align_corners=False)
 // -> per-column argmax (:698) -> left / right peak split (:700-703) -> invert(x,p) (:221-225).
 // ---------------------------------------------------------------------------------------------
@@ -280,4 +418,55 @@ extern "C" int lc_plan_field(const float* uf, int B, int D, int W, int R, const 
   if (rc) return rc;
   plan_prep_warp_kernel<<<grid, kPrepCols * kWarpWarps, sm2, st>>>(field_pre, flow, W, R, is, field_range, nullptr);
   return check_launch("lc_plan_field/warp");
+}
+
+// plan_default / plan_sweep input preparation when the LC camera is posed or sized differently from the RGB camera
+// (light_curtain.py:665-685 with the :675-676 branch taken): resize [D,Win] -> [R,Wout] + 5-tap mean ->
+// FieldWarp.transformZTheta warp by flow_T (:118-155; skipped when flow_T is null: rTc = I, sizes differ) ->
+// [normalise] -> [NaN -> eps] -> polar warp by flow -> split / invert.  nsteps = 0 gives the polar field alone
+// (umaps [B,1,R,Wout]).  scratch: 2 * B * R * Wout floats.
+extern "C" int lc_plan_prepare_transformed(const float* uf, int B, int D, int Win, int R, int Wout,
+                                           const float* flow_T, const float* flow, const float* steps, int nsteps,
+                                           int flags, float* umaps, int32_t* argmax, float* field_pre,
+                                           float* scratch, void* stream) {
+  DPV_REQUIRE(uf && flow && umaps && field_pre && scratch, "lc_plan_prepare_transformed: null pointer");
+  DPV_REQUIRE(B > 0 && D > 1 && Win >= 4 && Wout >= 4 && R > 1, "lc_plan_prepare_transformed: bad shape");
+  DPV_REQUIRE(nsteps >= 0 && nsteps <= 8 && (nsteps == 0 || steps), "lc_plan_prepare_transformed: nsteps=%d not in [0,8]",
+              nsteps);
+  DPV_REQUIRE((flags & ~7) == 0 && B <= 65535, "lc_plan_prepare_transformed: unknown flags %d or B too large", flags);
+  cudaStream_t st = (cudaStream_t)stream;
+  InvertSteps none, is;
+  none.n = 0;
+  is.n = nsteps;
+  for (int i = 0; i < nsteps; i++) {
+    double p = (double)steps[i];
+    is.p[i] = (float)p;
+    is.den[i] = (float)(std::pow(p, p) * std::pow(1.0 - p, 1.0 - p));
+  }
+  dim3 grid((Wout + kPrepCols - 1) / kPrepCols, B);
+  size_t sm1 = (size_t)(D + R) * kPrepCols * sizeof(float);
+  size_t sm2 = (size_t)R * kPrepCols * sizeof(float);
+  DPV_REQUIRE(sm1 <= 200 * 1024, "lc_plan_prepare_transformed: D + R too large for shared memory");
+  if (sm1 > 40 * 1024)
+    DPV_CUDA(cudaFuncSetAttribute(plan_prep_resize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
+  if (sm2 > 40 * 1024)
+    DPV_CUDA(cudaFuncSetAttribute(plan_prep_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
+  float* s0 = scratch;
+  float* s1 = scratch + (size_t)B * R * Wout;
+  plan_prep_resize_kernel<<<grid, kPrepCols * kPrepWarps, sm1, st>>>(uf, D, Win, R, Wout, flags, s0);
+  int rc = check_launch("lc_plan_prepare_transformed/resize");
+  if (rc) return rc;
+  const float* before_norm = s0;
+  if (flow_T) {
+    plan_prep_warp_kernel<<<grid, kPrepCols * kWarpWarps, sm2, st>>>(s0, flow_T, Wout, R, none, s1, nullptr);
+    rc = check_launch("lc_plan_prepare_transformed/transform");
+    if (rc) return rc;
+    before_norm = s1;
+  }
+  field_normalize_kernel<<<grid, kPrepCols * kPrepWarps, 0, st>>>(before_norm, Wout, R, flags, field_pre);
+  rc = check_launch("lc_plan_prepare_transformed/normalize");
+  if (rc) return rc;
+  plan_prep_warp_kernel<<<grid, kPrepCols * kWarpWarps, sm2, st>>>(field_pre, flow, Wout, R, is, umaps,
+                                                                    nsteps ? argmax : nullptr);
+  return check_launch("lc_plan_prepare_transformed/warp");
 }

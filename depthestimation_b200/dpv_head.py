@@ -153,6 +153,10 @@ def lc_process(BV_cur_all, model_input, lc, mode="low", iterations=5, viz=False,
     if planner not in ("default", "sweep"):
         raise NotImplementedError("planner %r: 'default' and 'sweep' are on the B200 path (plan_m1 is not: numpy RNG + "
                                   "alglib spline fit, DESIGN.md section 8)" % planner)
+    if getattr(lc, "transform_needed", False):
+        raise NotImplementedError("lc_process fuses sensing and the update for an LC camera that IS the RGB camera "
+                                  "(rTc = I, equal sizes: the KITTI-sim set-up); with a separate LC camera use "
+                                  "LightCurtain.plan_default_* / sense_* step by step")
     get = (lambda k: params[k]) if isinstance(params, dict) else (lambda k: getattr(params, k))
     spread_iter, spread_n = int(get("spread_iter")), int(get("spread_n"))
     if planner == "sweep":

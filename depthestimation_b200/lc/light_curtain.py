@@ -23,6 +23,14 @@ def intr_scale_unit(intr, scale):
     return out
 
 
+def intr_scale(intr, raw_img_size, img_size):
+    """utils/img_utils.py:255-261: rows 0 / 1 scaled by the width / height ratio, dtype kept."""
+    out = np.array(intr).copy()
+    out[0, :] *= float(img_size[0]) / float(raw_img_size[0])
+    out[1, :] *= float(img_size[1]) / float(raw_img_size[1])
+    return out
+
+
 def digitize_soft(values, array):
     """FieldWarp.digitize_soft (light_curtain.py:60-77), vectorised over `values` (float64)."""
     array = np.asarray(array, dtype=np.float64)
@@ -55,6 +63,30 @@ def polar_flowfield(angles, d_candi, r_candi):
     return flow
 
 
+def transform_flowfield(angles_input, d_candi_input, angles_output, d_candi_output, output2input):
+    """FieldWarp._transformZTheta (light_curtain.py:118-155) without the double loop: for every (depth row, LC
+    column) the point on the LC ray is moved into the RGB camera and located in its (depth, angle) grid.  float64
+    throughout: pylc hands its float angles to Python as Python floats."""
+    th_out = np.asarray(angles_output, dtype=np.float64)
+    z_out = np.asarray(d_candi_output, dtype=np.float64)
+    M = np.asarray(output2input)
+    R, W = len(z_out), len(th_out)
+    s = np.sin(np.radians(th_out))                                   # :133-134
+    rng = np.sqrt(np.power(z_out, 2)[:, None] / (1 - np.power(s, 2))[None, :])
+    xval = rng * s[None, :]
+    zval = np.broadcast_to(z_out[:, None], (R, W))
+    pt = np.stack([xval, np.zeros((R, W)), zval, np.ones((R, W))], 0).reshape(4, -1)
+    tpt = np.matmul(M, pt)                                           # :139
+    rng2 = np.sqrt(tpt[0] * tpt[0] + tpt[1] * tpt[1] + tpt[2] * tpt[2])
+    theta = np.degrees(np.arcsin(tpt[0] / rng2))
+    zbin = digitize_soft(tpt[2], d_candi_input).reshape(R, W)
+    thetabin = digitize_soft(theta, angles_input).reshape(R, W)
+    flow = np.zeros((R, W, 2), np.float32)
+    flow[:, :, 0] = (np.arange(W, dtype=np.float64)[None, :] - thetabin).astype(np.float32)
+    flow[:, :, 1] = (np.arange(R, dtype=np.float64)[:, None] - zbin).astype(np.float32)
+    return flow
+
+
 class _Rig:
     """One (device, planner, polar flow) triple: the reference's *_large or *_small members."""
 
@@ -65,6 +97,19 @@ class _Rig:
         self.planner = lcsim.PlannerRT(self.dev, r_candi_up, width)
         self.angles = np.array(lcsim.generateCameraAngles(K, None, width, height), np.float32)
         self.flow = torch.from_numpy(polar_flowfield(self.angles, d_candi_up, r_candi_up)).to(device)
+        self.width = int(width)
+        self.flow_T = None
+
+    def set_input_camera(self, intr_rgb, size_rgb, rTc, d_candi_up):
+        """FieldWarp.__init__ (:31-42) + transformZTheta (:178-187): the RGB camera rescaled to the LC image size,
+        its column angles, and the RGB -> LC field warp (only when rTc != I, :675-676)."""
+        if np.all(np.equal(np.asarray(rTc), np.eye(4))):
+            return
+        size_lc = (self.dev.W, self.dev.H)
+        K = intr_scale(intr_rgb, size_rgb, size_lc)
+        ang_in = np.array(lcsim.generateCameraAngles(K, None, size_lc[0], size_lc[1]), np.float32)
+        self.flow_T = torch.from_numpy(transform_flowfield(ang_in, d_candi_up, self.angles, d_candi_up, rTc)) \
+            .to(self.flow.device)
 
 
 class LightCurtain:
@@ -76,7 +121,7 @@ class LightCurtain:
     def init(self, PARAMS):
         self.PARAMS = PARAMS
         # light_curtain.py:324-329.  With a separately posed / sized LC camera, sensing re-projects through
-        # transformPoints (:824-858, built); planning needs FieldWarp.transformZTheta (:118-165), which is not.
+        # transformPoints (:824-858) and planning warps the field RGB -> LC (FieldWarp.transformZTheta :118-165).
         self.transform_needed = bool(
             not np.all(np.equal(np.asarray(PARAMS["rTc"]), np.eye(4))) or
             PARAMS["size_rgb"][0] != PARAMS["size_lc"][0] or PARAMS["size_rgb"][1] != PARAMS["size_lc"][1])
@@ -107,6 +152,13 @@ class LightCurtain:
                          P["lTc"], P["laser_fov"], P["laser_timestep"] * 4, self.d_candi_up, self.r_candi_up,
                          self.device)
             r.dev.hit_noise = float(self.hit_noise)
+            if self.transform_needed:                               # fw_large / fw_small, :306-311
+                if mode == "high":
+                    r.set_input_camera(P["intr_rgb"], P["size_rgb"], P["rTc"], self.d_candi_up)
+                else:
+                    r.set_input_camera(intr_scale_unit(P["intr_rgb"], 1 / 4.),
+                                       (int(P["size_rgb"][0] / 4), int(P["size_rgb"][1] / 4)), P["rTc"],
+                                       self.d_candi_up)
             self._rigs[mode] = r
         return r
 
@@ -133,20 +185,17 @@ class LightCurtain:
                 "name": "default", "laser_timestep": 3.5e-5, "device": model_input["intrinsics"].device}
 
     # ---- planning (light_curtain.py:646-739) --------------------------------------------------
-    def _no_field_transform(self):
-        if self.transform_needed:
-            raise NotImplementedError("planning with rTc != I / a differently sized LC camera needs "
-                                      "FieldWarp.transformZTheta (lc/light_curtain.py:118-165): not built")
-
     def plan_batched(self, uf, steps, mode="high"):
         """uf [B,D,W] -> dict(xz [B,nc,W,2], ks [B,nc,W] int32, counts [B,nc] int32, umaps, argmax, field_pre)."""
-        self._no_field_transform()
         r = self.rig(mode)
         R = len(self.r_candi_up)
-        umaps, amax, pre = ops.plan_prepare(uf, r.flow, steps, R)
+        if self.transform_needed:                                   # :665-685 with the RGB -> LC warp
+            umaps, amax, pre = ops.plan_prepare_transformed(uf, r.flow_T, r.flow, steps, R, r.width)
+        else:
+            umaps, amax, pre = ops.plan_prepare(uf, r.flow, steps, R)
         B, nc = umaps.shape[0], umaps.shape[1]
         ks, xz, counts = r.planner.solve(umaps.reshape(B * nc, R, -1))
-        W = uf.shape[2]
+        W = r.width
         return dict(xz=xz.reshape(B, nc, W, 2), ks=ks.reshape(B, nc, W), counts=counts.reshape(B, nc), umaps=umaps,
                     argmax=amax, field_pre=pre)
 
@@ -173,10 +222,14 @@ class LightCurtain:
     def _field_visual(self, field, mode, flags):
         """The polar planning field as the reference's [R,W,3] visual (:475-480): the warp runs on the GPU, the
         side columns are copied from their neighbours afterwards."""
-        self._no_field_transform()
         r = self.rig(mode)
-        fr, _ = ops.plan_field(field.unsqueeze(0), r.flow, len(self.r_candi_up), flags)
-        fr = fr[0]
+        if self.transform_needed:
+            um, _, _ = ops.plan_prepare_transformed(field.unsqueeze(0), r.flow_T, r.flow, [], len(self.r_candi_up),
+                                                    r.width, flags)
+            fr = um[0, 0]
+        else:
+            fr, _ = ops.plan_field(field.unsqueeze(0), r.flow, len(self.r_candi_up), flags)
+            fr = fr[0]
         fr[:, 0] = fr[:, 1]
         fr[:, -1] = fr[:, -2]
         return np.repeat(fr.cpu().numpy()[:, :, np.newaxis], 3, axis=2)

@@ -195,6 +195,27 @@ def plan_field(uf, flow, R, flags=7):
     return frange, pre
 
 
+def plan_prepare_transformed(uf, flow_T, flow, steps, R, W_out, flags=7):
+    """uf [B,D,Win] of the RGB camera, flow_T [R,Wout,2] (RGB -> LC field warp, or None), flow [R,Wout,2] (polar warp)
+    -> (umaps [B,1+2n,R,Wout], argmax [B,Wout] int32, field_pre [B,R,Wout]).  light_curtain.py:665-708 with the
+    rTc != I / size_lc != size_rgb branch; steps = [] gives the polar field alone in umaps[:,0]."""
+    dev = _dev(uf)
+    uf, flow = f32(uf, dev), f32(flow, dev)
+    flow_T = None if flow_T is None else f32(flow_T, dev)
+    B, D, Win = uf.shape
+    R, W = int(R), int(W_out)
+    n = len(steps)
+    st = (ctypes.c_float * max(n, 1))(*[float(s) for s in steps])
+    umaps = torch.empty(B, 1 + 2 * n, R, W, device=dev, dtype=torch.float32)
+    argmax = torch.empty(B, W, device=dev, dtype=torch.int32)
+    pre = torch.empty(B, R, W, device=dev, dtype=torch.float32)
+    scratch = torch.empty(2, B, R, W, device=dev, dtype=torch.float32)
+    check(lib().lc_plan_prepare_transformed(ptr(uf), B, D, Win, R, W, None if flow_T is None else ptr(flow_T),
+                                            ptr(flow), ctypes.cast(st, ctypes.c_void_p), n, int(flags), ptr(umaps),
+                                            ptr(argmax), ptr(pre), ptr(scratch), stream_ptr(dev)))
+    return umaps, argmax, pre
+
+
 # --------------------------------------------------------------------------------------------------
 # callers either side of the fused path (SURVEY §8 rows a17-a19, (f)1)
 # --------------------------------------------------------------------------------------------------

@@ -121,6 +121,14 @@ int lc_plan_prepare(const float* uf, int B, int D, int W, int R, const float* fl
 #define LC_FIELD_DEFAULT 7
 int lc_plan_field(const float* uf, int B, int D, int W, int R, const float* flow, int flags, float* field_range,
                   float* field_pre, void* stream);
+/* The same preparation for an LC camera posed or sized differently from the RGB camera (lc/light_curtain.py:665-685
+ * with the :675-676 branch): uf [B,D,Win] is resized on BOTH axes to [R,Wout] (FieldWarp.preprocess :79-85), smoothed,
+ * warped RGB -> LC by flow_T [R,Wout,2] (FieldWarp.transformZTheta :118-155 / :178-187; NULL skips it), then
+ * normalised / NaN-filled per `flags` (LC_FIELD_*), polar-warped by flow [R,Wout,2] and split like lc_plan_prepare.
+ * nsteps = 0: umaps [B,1,R,Wout] is the polar field alone (argmax unused).  scratch: 2*B*R*Wout floats (device). */
+int lc_plan_prepare_transformed(const float* uf, int B, int D, int Win, int R, int Wout, const float* flow_T,
+                                const float* flow, const float* steps, int nsteps, int flags, float* umaps,
+                                int32_t* argmax, float* field_pre, float* scratch, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * lcsim device model.  external/lcsim/python/sim.py:29-211 LCDevice,

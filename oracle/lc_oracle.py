@@ -44,6 +44,33 @@ def polar_flowfield(angles, d_candi, r_candi):
     return flow
 
 
+def intr_scale(intr, raw_img_size, img_size):
+    """utils/img_utils.py:255-261."""
+    out = np.array(intr).copy()
+    out[0, :] *= float(img_size[0]) / float(raw_img_size[0])
+    out[1, :] *= float(img_size[1]) / float(raw_img_size[1])
+    return out
+
+
+def transform_flowfield(angles_input, d_candi_input, angles_output, d_candi_output, output2input):
+    """FieldWarp._transformZTheta, light_curtain.py:118-151: flow [1,R,W,2] (float32 store), scalar by scalar."""
+    R, W = len(d_candi_output), len(angles_output)
+    flow = np.zeros((1, R, W, 2), np.float32)
+    for r in range(R):
+        for c in range(W):
+            zval = d_candi_output[r]
+            theta = angles_output[c]
+            rng = np.sqrt((np.power(zval, 2)) / (1 - np.power(np.sin(np.radians(theta)), 2)))
+            xval = rng * np.sin(np.radians(theta))
+            pt = np.array([xval, 0, zval, 1.]).reshape((4, 1))
+            tpt = np.matmul(output2input, pt)[:, 0]
+            rng = np.sqrt(tpt[0] * tpt[0] + tpt[1] * tpt[1] + tpt[2] * tpt[2])
+            theta = np.degrees(np.arcsin(tpt[0] / rng))
+            flow[0, r, c, 0] = c - digitize_soft(theta, angles_input)
+            flow[0, r, c, 1] = r - digitize_soft(tpt[2], d_candi_input)
+    return flow
+
+
 def flow_warp(field, flow):
     """FieldWarp.warp, light_curtain.py:47-58."""
     ax = torch.arange(0, field.shape[0]).float()
@@ -81,6 +108,20 @@ class LightCurtainOracle:
         self.planner = lcsim.PlannerRT(self.dev, self.r_candi_up, self.W)
         self.angles = np.array(lcsim.generateCameraAngles(self.K, None, self.W, self.H))
         self._flow = None
+        self.flow_T = None
+
+    def set_input_camera(self, K_rgb, size_rgb, rTc):
+        """FieldWarp.__init__ :31-42 and transformZTheta :178-187 for an RGB camera that is not the LC camera: the
+        field is resized to the LC width (prepare_field already does) and, when rTc != I, warped RGB -> LC."""
+        if np.all(np.equal(np.asarray(rTc), np.eye(4))):
+            return
+        K = intr_scale(K_rgb, size_rgb, (self.W, self.H))
+        ang_in = lcsim.generateCameraAngles(K, None, self.W, self.H)
+        self.flow_T = torch.from_numpy(
+            transform_flowfield(ang_in, list(self.d_candi_up), self.angles, list(self.d_candi_up), rTc))
+
+    def _rgb_to_lc(self, f):
+        return f if self.flow_T is None else flow_warp(f, self.flow_T)             # :675-676
 
     def flow(self):
         if self._flow is None:
@@ -101,6 +142,7 @@ class LightCurtainOracle:
         k = torch.zeros(5, 5)
         k[:, 2] = 1 / 5.0                                            # create_mean_kernel :213-218
         f = F.conv2d(f, k.reshape(1, 1, 5, 5), padding=2).squeeze(0).squeeze(0)
+        f = self._rgb_to_lc(f)
         lo, _ = f.unsqueeze(0).min(1)                                # normalize :207-210
         hi, _ = f.unsqueeze(0).max(1)
         f = ((f.unsqueeze(0) - lo) / (hi - lo)).squeeze(0)
@@ -117,6 +159,7 @@ class LightCurtainOracle:
         k = torch.zeros(5, 5)
         k[:, 2] = 1 / 5.0
         f = F.conv2d(f, k.reshape(1, 1, 5, 5), padding=2).squeeze(0).squeeze(0)      # :456-458
+        f = self._rgb_to_lc(f)                                       # :461-462
         lo, _ = f.unsqueeze(0).min(1)                                # :465 (NaN columns stay NaN: no :658-662 here)
         hi, _ = f.unsqueeze(0).max(1)
         f = ((f.unsqueeze(0) - lo) / (hi - lo)).squeeze(0)

@@ -1,3 +1,2 @@
 mkdir -p gpurun_out
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 20 --warmup 3 > gpurun_out/bench_2gpu.log 2>&1; echo "rc=$?"; tail -1 gpurun_out/bench_2gpu.log | cut -c1-900
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 bench.py --impl reference --gpus 2 --steps 1 --warmup 1 > gpurun_out/bench_ref_2gpu.log 2>&1; echo "rc=$?"; tail -1 gpurun_out/bench_ref_2gpu.log | cut -c1-300
+timeout 1200 python -m pytest tests -m gpu -x -q 2>&1 | tail -25

@@ -256,6 +256,48 @@ def case_sense_transformed():
          lTc=lTc, d_candi=d, d_candi_up=d_up, depth=depth, pts=pts, dpv=dpv)
 
 
+def case_plan_transformed():
+    """plan_default_high / plan_sweep_high with a separately posed, differently sized LC camera on the unmodified
+    reference (lcsim restated): FieldWarp.preprocess resizes both axes (:79-85) and FieldWarp.transformZTheta warps
+    the field RGB -> LC (:118-155, :675-676) -> plan_rtc.npz."""
+    _install_lcsim_stubs()
+    import lc.light_curtain as LC
+    g = torch.Generator().manual_seed(33)
+    D = 16
+    Wr, Hr, Wl, Hl = 64, 32, 80, 40
+    d = IU.powerf(5., 40., D, 1.0)
+    d_up = IU.powerf(5., 40., 32, 1.0)
+    K_rgb = np.array([[150., 0., 32.], [0., 150., 16.], [0., 0., 1.]], np.float32)
+    K_lc = np.array([[170., 0., 40.], [0., 170., 20.], [0., 0., 1.]], np.float32)
+    a = np.radians(2.0)
+    rTc = np.eye(4, dtype=np.float32)
+    rTc[:3, :3] = np.array([[np.cos(a), 0., np.sin(a)], [0., 1., 0.], [-np.sin(a), 0., np.cos(a)]], np.float32)
+    rTc[:3, 3] = [0.06, -0.03, 0.02]
+    lTc = np.eye(4, dtype=np.float32)
+    lTc[0, 3] = 0.2
+    P = {"intr_rgb": K_rgb, "dist_rgb": [0.] * 5, "size_rgb": [Wr, Hr], "intr_lc": K_lc, "dist_lc": [0.] * 5,
+         "size_lc": [Wl, Hl], "rTc": rTc, "lTc": lTc, "laser_fov": 80., "d_candi": d, "r_candi": d,
+         "d_candi_up": d_up, "r_candi_up": d_up, "name": "golden_plan_rtc", "laser_timestep": 3.5e-5,
+         "device": torch.device("cpu"), "expand_A": D, "expand_B": 32}
+    lc = LC.LightCurtain()
+    lc.init(P)
+    # a smooth ridge (the planner follows it) + noise, one NaN column and one NaN at the far right edge
+    col = torch.arange(Wr).float()
+    ridge = 6. + 4. * torch.sin(col / 9.0)
+    uf = torch.exp(-((torch.arange(D).float().reshape(D, 1) - ridge.reshape(1, Wr)) ** 2) / 6.0) \
+        + 0.05 * torch.rand(D, Wr, generator=g)
+    uf = uf / uf.sum(0, keepdim=True)
+    uf[:, 23] = float("nan")
+    uf[:, -1] = float("nan")
+    paths, vis = lc.plan_default_high(uf.clone(), {"step": [0.5]})
+    flow_T = lc.fw_large.flowfields["transform_high"].clone().numpy()
+    flow = lc.fw_large.flowfields["z2rwarp_high"].clone().numpy()
+    _, vis_sweep = lc.plan_sweep_high(uf.clone(), {"start": 6.0, "end": 30.0, "step": 9.0})
+    save("plan_rtc", K_rgb=K_rgb, K_lc=K_lc, size_rgb=np.array([Wr, Hr]), size_lc=np.array([Wl, Hl]), rTc=rTc, lTc=lTc,
+         d_candi=d, d_candi_up=d_up, uf=uf, flow_T=flow_T, flow=flow, path0=paths[0], path1=paths[1], path2=paths[2],
+         field_visual=vis, field_visual_sweep=vis_sweep)
+
+
 def case_aux():
     """Rows a17 (gen_lc_dpv_true), a18 (inverse_warp), a19 (correlation_native twin) and compute_unc_rmse,
     run on the unmodified reference -> aux.npz."""
@@ -332,3 +374,4 @@ if __name__ == "__main__":
     case_aux()
     case_plan_sweep()
     case_sense_transformed()
+    case_plan_transformed()

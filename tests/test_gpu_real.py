@@ -141,5 +141,95 @@ def test_sense_high_with_separate_lc_camera_golden():
     exp = LO.sense_transformed(g["depth"], g["pts"], g["K_rgb"], g["size_rgb"], g["K_lc"], g["size_lc"], g["rTc"],
                                g["lTc"], g["d_candi"]).numpy()
     np.testing.assert_allclose(got[:, ~bad], exp[:, ~bad], rtol=1e-4, atol=1e-6)
-    with pytest.raises(NotImplementedError):               # planning needs FieldWarp.transformZTheta: not built
-        lc.plan_default_high(torch.rand(len(g["d_candi"]), int(g["size_rgb"][0])).cuda(), {"step": [0.5]})
+    from depthestimation_b200 import dpv_head
+    with pytest.raises(NotImplementedError):               # the fused loop is for an LC camera that is the RGB camera
+        dpv_head.lc_process(torch.zeros(1, len(g["d_candi"]), 32, 64).cuda(), {}, lc, mode="high",
+                            params={"step": [0.5], "spread_iter": 2, "spread_n": 5})
+
+
+def _rtc_params(g):
+    return {"intr_rgb": g["K_rgb"], "dist_rgb": [0.] * 5, "size_rgb": [int(v) for v in g["size_rgb"]],
+            "intr_lc": g["K_lc"], "dist_lc": [0.] * 5, "size_lc": [int(v) for v in g["size_lc"]], "rTc": g["rTc"],
+            "lTc": g["lTc"], "laser_fov": 80., "d_candi": g["d_candi"], "r_candi": g["d_candi"],
+            "d_candi_up": g["d_candi_up"], "r_candi_up": g["d_candi_up"], "name": "rtc", "laser_timestep": 3.5e-5,
+            "device": torch.device("cuda", 0), "expand_A": len(g["d_candi"]), "expand_B": len(g["d_candi_up"]),
+            "hit_noise": 0.0}
+
+
+def test_plan_with_separate_lc_camera_golden():
+    """plan_default_high / plan_sweep_high for rTc != I and a differently sized LC camera (lc/light_curtain.py:665-708
+    with the :675-676 branch): the field is resized on both axes, warped RGB -> LC, normalised, polar-warped and split
+    on the GPU; against the unmodified reference (tests/golden/plan_rtc.npz) and the oracle."""
+    import os
+    from depthestimation_b200.lc.light_curtain import LightCurtain
+    from oracle import lc_oracle as LO
+    g = dict(np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "plan_rtc.npz")))
+    lc = LightCurtain()
+    lc.init(_rtc_params(g))
+    assert lc.transform_needed
+    Wl, Hl = [int(v) for v in g["size_lc"]]
+    uf = torch.as_tensor(g["uf"]).cuda()
+    keep = uf.clone()
+    out = lc.plan_batched(uf.unsqueeze(0), [0.5])
+    assert torch.equal(torch.nan_to_num(uf), torch.nan_to_num(keep))
+    assert out["umaps"].shape == (1, 3, len(g["d_candi_up"]), Wl)
+    # the planning field against the reference's visual (pixels the reference did not paint over)
+    vis = g["field_visual"]
+    undrawn = (vis[:, :, 0] == vis[:, :, 1]) & (vis[:, :, 1] == vis[:, :, 2])
+    pre = out["field_pre"][0].cpu().numpy()
+    np.testing.assert_allclose(pre[undrawn], vis[:, :, 0][undrawn], rtol=1e-4, atol=2e-6)
+    # field, split maps and argmax against the oracle
+    olc = LO.LightCurtainOracle(g["K_lc"], Wl, Hl, g["d_candi"], g["d_candi_up"])
+    olc.set_input_camera(g["K_rgb"], [int(v) for v in g["size_rgb"]], g["rTc"])
+    pre_o, fr_o = olc.prepare_field(torch.as_tensor(g["uf"]).clone())
+    um_o, idx_o = olc.split_fields(fr_o, [0.5])
+    np.testing.assert_allclose(pre, pre_o.numpy(), rtol=1e-4, atol=2e-6)
+    for i in range(3):
+        np.testing.assert_allclose(out["umaps"][0, i].cpu().numpy(), um_o[i].numpy(), rtol=1e-4, atol=2e-6,
+                                   err_msg="umap %d" % i)
+    np.testing.assert_array_equal(out["argmax"][0].cpu().numpy(), idx_o.numpy())
+    # the planned curtains: the DP is index work, bit-exact on equal maps; on the GPU's own maps (1e-4 away) a tie
+    # between two nodes may resolve differently, so the design points are compared per column
+    paths, _ = lc.plan_default_high(uf, {"step": [0.5]})
+    for i in range(3):
+        got, ref = paths[i].cpu().numpy(), g["path%d" % i]
+        assert got.shape == ref.shape, (i, got.shape, ref.shape)
+        same = np.all(got == ref, axis=1)
+        assert same.mean() > 0.9, (i, same.mean())
+    # the DP on the oracle's maps is bit-exact
+    ks, xz, counts = lc.rig("high").planner.solve(torch.stack(um_o).cuda())
+    for i in range(3):
+        np.testing.assert_array_equal(xz[i, :int(counts[i])].cpu().numpy(), g["path%d" % i])
+    # plan_sweep's visual with the same transform (NaN columns kept)
+    _, vs = lc.plan_sweep_high(uf, {"start": 6.0, "end": 30.0, "step": 9.0})
+    ref = g["field_visual_sweep"]
+    np.testing.assert_array_equal(np.isnan(vs), np.isnan(ref))
+    np.testing.assert_allclose(vs, ref, rtol=1e-4, atol=2e-6, equal_nan=True)
+
+
+def test_plan_resize_without_pose_change_against_oracle():
+    """size_lc != size_rgb with rTc = I: only FieldWarp.preprocess's two-axis resize applies (no transformZTheta)."""
+    import os
+    from depthestimation_b200.lc.light_curtain import LightCurtain
+    from oracle import lc_oracle as LO
+    g = dict(np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "plan_rtc.npz")))
+    P = _rtc_params(g)
+    P["rTc"] = np.eye(4, dtype=np.float32)
+    lc = LightCurtain()
+    lc.init(P)
+    assert lc.transform_needed and lc.rig("high").flow_T is None
+    Wl, Hl = [int(v) for v in g["size_lc"]]
+    olc = LO.LightCurtainOracle(g["K_lc"], Wl, Hl, g["d_candi"], g["d_candi_up"])
+    rng = np.random.default_rng(5)
+    for Win in (64, 80, 131):                       # narrower, equal, wider than the LC camera
+        uf = rng.uniform(0.01, 1.0, size=(16, Win)).astype(np.float32)
+        uf[:, Win // 3] = np.nan
+        uf[2, Win // 2] = np.inf
+        out = lc.plan_batched(torch.as_tensor(uf).cuda().unsqueeze(0), [0.75])
+        pre_o, fr_o = olc.prepare_field(torch.as_tensor(uf).clone())
+        um_o, idx_o = olc.split_fields(fr_o, [0.75])
+        np.testing.assert_allclose(out["field_pre"][0].cpu().numpy(), pre_o.numpy(), rtol=1e-4, atol=2e-6,
+                                   err_msg="Win %d" % Win)
+        for i in range(3):
+            np.testing.assert_allclose(out["umaps"][0, i].cpu().numpy(), um_o[i].numpy(), rtol=1e-4, atol=2e-6,
+                                       err_msg="Win %d umap %d" % (Win, i))

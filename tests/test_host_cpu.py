@@ -43,6 +43,23 @@ def test_polar_flowfield_matches_reference_golden():
     np.testing.assert_array_equal(flow, g["flow"][0])
 
 
+def test_transform_flowfield_matches_reference_golden():
+    """FieldWarp._transformZTheta (lc/light_curtain.py:118-155), vectorised in the host mirror, against the flow field
+    the unmodified reference stored (tests/golden/plan_rtc.npz)."""
+    from depthestimation_b200 import lcsim
+    from depthestimation_b200.lc.light_curtain import intr_scale, transform_flowfield
+    g = np.load(os.path.join(G, "plan_rtc.npz"))
+    Wl, Hl = [int(v) for v in g["size_lc"]]
+    ang_out = lcsim.generateCameraAngles(g["K_lc"], None, Wl, Hl)
+    ang_in = lcsim.generateCameraAngles(intr_scale(g["K_rgb"], g["size_rgb"], g["size_lc"]), None, Wl, Hl)
+    flow = transform_flowfield(ang_in, g["d_candi_up"], ang_out, g["d_candi_up"], g["rTc"])
+    ref = g["flow_T"][0]
+    big = np.abs(ref) > 1e7                                   # out-of-grid markers (digitize_soft :70-73)
+    np.testing.assert_array_equal(np.abs(flow) > 1e7, big)
+    np.testing.assert_allclose(flow[~big], ref[~big], rtol=0, atol=2e-6)
+    assert (flow[~big] == ref[~big]).mean() > 0.99
+
+
 def test_no_cpu_fallback():
     """The product path refuses CPU tensors instead of silently computing somewhere else."""
     from depthestimation_b200 import _lib, ops

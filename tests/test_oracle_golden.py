@@ -178,3 +178,30 @@ def test_depth_errors_restatement_properties():
     np.testing.assert_allclose(e[6], 0.0, atol=1e-3)                                 # scale invariant
     np.testing.assert_allclose(e[7], 1.0, rtol=1e-6)                                 # abs relative
     np.testing.assert_allclose(e[8], 1.0, rtol=1e-6)                                 # squared relative: e^2 / gt^2
+
+
+def _rtc_oracle(g):
+    Wl, Hl = [int(v) for v in g["size_lc"]]
+    lc = LO.LightCurtainOracle(g["K_lc"], Wl, Hl, g["d_candi"], g["d_candi_up"])
+    lc.set_input_camera(g["K_rgb"], [int(v) for v in g["size_rgb"]], g["rTc"])
+    return lc
+
+
+def test_plan_with_separate_lc_camera_against_reference():
+    """plan_default_high / plan_sweep_high with rTc != I and size_lc != size_rgb (lc/light_curtain.py:665-685 with
+    the :675-676 branch): both flow fields, the planning field and the three planned curtains."""
+    g = load("plan_rtc")
+    lc = _rtc_oracle(g)
+    close(lc.flow_T, g["flow_T"], rtol=0, atol=0)
+    close(lc.flow(), g["flow"], rtol=0, atol=0)
+    pre, _ = lc.prepare_field(T(g["uf"]).clone())
+    vis = g["field_visual"]
+    undrawn = (vis[:, :, 0] == vis[:, :, 1]) & (vis[:, :, 1] == vis[:, :, 2])
+    assert undrawn.mean() > 0.8
+    close(pre.numpy()[undrawn], vis[:, :, 0][undrawn], rtol=1e-6, atol=1e-7)
+    paths, _, _ = lc.plan(T(g["uf"]).clone(), [0.5])
+    for i, p in enumerate(paths):
+        np.testing.assert_array_equal(p, g["path%d" % i])
+    _, vs = lc.plan_sweep(T(g["uf"]).clone(), {"start": 6.0, "end": 30.0, "step": 9.0})
+    np.testing.assert_array_equal(np.isnan(vs), np.isnan(g["field_visual_sweep"]))
+    close(vs, g["field_visual_sweep"], rtol=1e-6, atol=1e-7)
