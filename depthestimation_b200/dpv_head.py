@@ -142,6 +142,52 @@ def _lc_process_sweep(BV_cur_all, model_input, lc, mode, iterations, params, noi
     return vol, [[] for _ in range(B)]
 
 
+def _lc_process_separate_camera(BV_cur_all, model_input, lc, mode, iterations, planner, params, cfg, trace):
+    """lc_process for an LC camera posed or sized differently from the RGB camera (rTc != I / size_lc != size_rgb):
+    the fused sense+update kernel does not apply (a curtain return lands on other pixels than it was sensed on), so
+    the loop is the reference's own composition (models.py:1027-1122) of GPU steps: uncertainty field -> planning field
+    resized and warped RGB -> LC -> DP planner -> per curtain: depth re-projected into the LC camera, sensed,
+    re-projected back, likelihood -> Bayesian update (dpv_bayes_fuse)."""
+    get = (lambda k: params[k]) if isinstance(params, dict) else (lambda k: getattr(params, k))
+    spread_iter, spread_n = int(get("spread_iter")), int(get("spread_n"))
+    dev = BV_cur_all.device
+    B = BV_cur_all.shape[0]
+    if mode == "high":
+        K = model_input["intrinsics_up"].to(dev).float().reshape(B, 3, 3)
+        depth = torch.nn.functional.interpolate(model_input["dmaps"].to(dev).float().unsqueeze(1), scale_factor=4,
+                                                mode="nearest").squeeze(1).contiguous()
+    elif mode == "low":
+        K = model_input["intrinsics"].to(dev).float().reshape(B, 3, 3)
+        depth = model_input["dmaps"].to(dev).float().contiguous()
+    else:
+        raise Exception("lc_process: unknown mode " + str(mode))
+    uf_par = img_utils.uf_params(cfg if cfg is not None else "kitti")
+    final = BV_cur_all.detach().float().contiguous()
+    D_in = final.shape[1]
+    if D_in != lc.expand_A:
+        final = ops.resample_depth(final, lc.expand_A, bv_log=True)
+    for it in range(iterations):
+        mean = ops.expectation(final, lc.d_candi, True)
+        uf, _ = ops.ufield(final, mean, K, lc.d_candi, uf_par, bv_log=True, want_depth=False)
+        per_sample = []
+        for b in range(B):
+            if planner == "default":
+                paths, _ = lc._plan_default(uf[b], {"step": list(get("step"))}, mode)
+            else:
+                flat, _ = lc._plan_sweep(uf[b], {k: get(k) for k in ("start", "end", "step")}, mode)
+                paths = [torch.as_tensor(f, device=dev) for f in flat]
+            per_sample.append(torch.stack([lc._sense(depth[b], p, mode)[0] for p in paths]))
+            if trace is not None:
+                trace.append(dict(it=it, b=b, uf=uf[b].clone(), paths=[p.clone() for p in paths],
+                                  liks=per_sample[-1].clone()))
+        if len({int(l.shape[0]) for l in per_sample}) != 1:
+            raise RuntimeError("lc_process: samples planned different numbers of curtains")
+        final, _ = ops.bayes_fuse(final, torch.stack(per_sample), lc.d_candi, spread_iter, spread_n)
+    if final.shape[1] != D_in:
+        final = ops.resample_depth(final, D_in, bv_log=True)
+    return final, [[] for _ in range(B)]
+
+
 def lc_process(BV_cur_all, model_input, lc, mode="low", iterations=5, viz=False, score=False, planner="default",
                params=None, cfg=None, noise=None, trace=None, state=None):
     """BaseModel.lc_process (models/models.py:980-1129) for the whole batch at once.
@@ -154,9 +200,7 @@ def lc_process(BV_cur_all, model_input, lc, mode="low", iterations=5, viz=False,
         raise NotImplementedError("planner %r: 'default' and 'sweep' are on the B200 path (plan_m1 is not: numpy RNG + "
                                   "alglib spline fit, DESIGN.md section 8)" % planner)
     if getattr(lc, "transform_needed", False):
-        raise NotImplementedError("lc_process fuses sensing and the update for an LC camera that IS the RGB camera "
-                                  "(rTc = I, equal sizes: the KITTI-sim set-up); with a separate LC camera use "
-                                  "LightCurtain.plan_default_* / sense_* step by step")
+        return _lc_process_separate_camera(BV_cur_all, model_input, lc, mode, iterations, planner, params, cfg, trace)
     get = (lambda k: params[k]) if isinstance(params, dict) else (lambda k: getattr(params, k))
     spread_iter, spread_n = int(get("spread_iter")), int(get("spread_n"))
     if planner == "sweep":

@@ -109,10 +109,13 @@ class LightCurtainOracle:
         self.angles = np.array(lcsim.generateCameraAngles(self.K, None, self.W, self.H))
         self._flow = None
         self.flow_T = None
+        self.rgb = None
+        self.lTc, self.laser_fov, self.laser_timestep = lTc, laser_fov, laser_timestep
 
     def set_input_camera(self, K_rgb, size_rgb, rTc):
         """FieldWarp.__init__ :31-42 and transformZTheta :178-187 for an RGB camera that is not the LC camera: the
         field is resized to the LC width (prepare_field already does) and, when rTc != I, warped RGB -> LC."""
+        self.rgb = dict(K=np.asarray(K_rgb, np.float32), size=[int(v) for v in size_rgb], rTc=np.asarray(rTc))
         if np.all(np.equal(np.asarray(rTc), np.eye(4))):
             return
         K = intr_scale(K_rgb, size_rgb, (self.W, self.H))
@@ -199,6 +202,10 @@ class LightCurtainOracle:
 
     # ---- sense_high, light_curtain.py:820-910 (rTc = I) -----------------------------------
     def sense(self, depth_gt, pts, noise=None):
+        if self.rgb is not None:                                     # :824-858, a separate LC camera
+            return (sense_transformed(depth_gt, pts, self.rgb["K"], self.rgb["size"], self.K, (self.W, self.H),
+                                      self.rgb["rTc"], self.lTc, self.d_candi, self.laser_fov, self.laser_timestep),
+                    None, None)
         img, th = self.dev.get_return(depth_gt, pts, True, noise=noise)
         img[np.isnan(img[:, :, 0])] = 0                              # :847-848
         th[np.isnan(th)] = 0

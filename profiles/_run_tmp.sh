@@ -1,2 +1,2 @@
 mkdir -p gpurun_out
-timeout 1200 python -m pytest tests -m gpu -x -q 2>&1 | tail -25
+timeout 1200 python -m pytest tests -m gpu -q 2>&1 | tail -60

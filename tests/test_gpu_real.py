@@ -141,10 +141,6 @@ def test_sense_high_with_separate_lc_camera_golden():
     exp = LO.sense_transformed(g["depth"], g["pts"], g["K_rgb"], g["size_rgb"], g["K_lc"], g["size_lc"], g["rTc"],
                                g["lTc"], g["d_candi"]).numpy()
     np.testing.assert_allclose(got[:, ~bad], exp[:, ~bad], rtol=1e-4, atol=1e-6)
-    from depthestimation_b200 import dpv_head
-    with pytest.raises(NotImplementedError):               # the fused loop is for an LC camera that is the RGB camera
-        dpv_head.lc_process(torch.zeros(1, len(g["d_candi"]), 32, 64).cuda(), {}, lc, mode="high",
-                            params={"step": [0.5], "spread_iter": 2, "spread_n": 5})
 
 
 def _rtc_params(g):
@@ -233,3 +229,45 @@ def test_plan_resize_without_pose_change_against_oracle():
         for i in range(3):
             np.testing.assert_allclose(out["umaps"][0, i].cpu().numpy(), um_o[i].numpy(), rtol=1e-4, atol=2e-6,
                                        err_msg="Win %d umap %d" % (Win, i))
+
+
+def test_lc_process_with_separate_lc_camera_against_oracle():
+    """lc_process for rTc != I and size_lc != size_rgb: two Bayesian iterations of plan (field resized and warped
+    RGB -> LC) + sense (re-projection both ways) + update, every step a GPU kernel, against the oracle's composition of
+    the reference's steps (models/models.py:1027-1122)."""
+    import os
+    from depthestimation_b200 import dpv_head
+    from depthestimation_b200.lc.light_curtain import LightCurtain
+    from oracle import dpv_oracle as O
+    from oracle import lc_oracle as LO
+    g = dict(np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "plan_rtc.npz")))
+    lc = LightCurtain()
+    lc.init(_rtc_params(g))
+    Wr, Hr = [int(v) for v in g["size_rgb"]]
+    Wl, Hl = [int(v) for v in g["size_lc"]]
+    D = len(g["d_candi"])
+    gen = torch.Generator().manual_seed(12)
+    d = torch.tensor(np.asarray(g["d_candi"], np.float32))
+    col = torch.arange(Wr).float()
+    gt = (14. + 6. * torch.sin(col / 11.0)).reshape(1, Wr).repeat(Hr // 4, 1)[:, ::4].contiguous()    # [h,w]
+    gt_up = torch.nn.functional.interpolate(gt.reshape(1, 1, Hr // 4, Wr // 4), scale_factor=4, mode="nearest")[0, 0]
+    logits = -((d.reshape(D, 1, 1) - (gt_up * 1.08 + 0.7)) ** 2) / 40.0 + 0.2 * torch.randn(D, Hr, Wr, generator=gen)
+    logp = torch.log_softmax(logits, 0).unsqueeze(0)
+    model_input = {"intrinsics_up": torch.tensor(g["K_rgb"]).unsqueeze(0), "dmaps": gt.unsqueeze(0)}
+    prm = {"step": [0.5], "spread_iter": 1, "spread_n": 5}
+    trace = []
+    fused, _ = dpv_head.lc_process(logp.cuda(), model_input, lc, mode="high", iterations=2, planner="default",
+                                   params=prm, trace=trace)
+    assert len(trace) == 2 and trace[0]["liks"].shape == (3, D, Hr, Wr)
+    olc = LO.LightCurtainOracle(g["K_lc"], Wl, Hl, g["d_candi"], g["d_candi_up"])
+    olc.set_input_camera(g["K_rgb"], [Wr, Hr], g["rTc"])
+    otrace = []
+    exp = LO.lc_loop(logp, gt_up.numpy(), olc, g["K_rgb"], O.uf_params("kitti"), 2, [0.5], 1, 5, trace=otrace)
+    # iteration 0: same field -> same curtains (up to DP ties on maps 1e-5 apart) -> same likelihoods
+    np.testing.assert_allclose(trace[0]["uf"].cpu().numpy(), otrace[0]["uf"][0].numpy(), rtol=1e-4, atol=1e-6,
+                               equal_nan=True)
+    got, ref = fused.cpu().numpy(), exp.numpy()
+    bad = np.abs(got - ref).max(1) > 1e-3 * np.maximum(np.abs(ref).max(1), 1.0)
+    assert bad.mean() < 0.02, bad.mean()               # pixels whose curtain point moved by a DP tie / z-buffer border
+    keep = ~bad[0]
+    np.testing.assert_allclose(got[0][:, keep], ref[0][:, keep], rtol=1e-3, atol=2e-3)
