@@ -72,6 +72,8 @@ SIGNATURES = {
     "dpv_correlation_shape": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_int, ctypes.POINTER(c_int),
                                       ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
     "dpv_correlation": (c_int, [c_fp, c_fp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_fp, c_vp]),
+    "dpv_correlation_backward": (c_int, [c_fp, c_fp, c_fp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                         c_fp, c_fp, c_vp]),
     "dpv_depth_errors": (c_int, [c_fp, c_fp, c_int, c_int, c_int, c_fp, c_vp]),
     "dpv_unc_rmse": (c_int, [c_fp, c_fp, c_int, c_int, c_fp, c_fp, c_vp]),
 }

@@ -193,6 +193,56 @@ __global__ void correlation_kernel(const float* __restrict__ in1, const float* _
   out[id] = acc / (float)(ksize * ksize * C);
 }
 
+// a19 backward (correlation_cuda_kernel.cu:116-303, stride1 = 1): one thread per input element gathers, for
+// every displacement, the outputs whose kernel window covers it.  No atomics: both gradients are pure gathers.
+__global__ void correlation_backward_kernel(const float* __restrict__ gout, const float* __restrict__ in1,
+                                            const float* __restrict__ in2, int B, int C, int H, int W, int pad,
+                                            int ksize, int max_disp, int stride2, int outH, int outW,
+                                            float* __restrict__ gin1, float* __restrict__ gin2) {
+  const int krad = (ksize - 1) / 2, drad = max_disp / stride2, dsize = 2 * drad + 1;
+  const int outC = dsize * dsize;
+  const long long n = (long long)B * C * H * W;
+  const long long id = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (id >= n) return;
+  const int x = (int)(id % W), y = (int)((id / W) % H);
+  const int b = (int)(id / ((long long)W * H * C));
+  const size_t HW = (size_t)H * W, oHW = (size_t)outH * outW;
+  const size_t plane = (size_t)(id / HW) * HW;                     // (b, c) plane of the inputs
+  const float* g = gout + (size_t)b * outC * oHW;
+  const int py = y + pad, px = x + pad;                            // the reference's padded coordinates
+  const float nel = (float)(ksize * ksize * C);
+  // d/d in1[y,x]: outputs (j,i) with j + max_disp - krad <= py <= j + max_disp + krad  (:135-159)
+  float acc1 = 0.f;
+  {
+    const int ymin = max(0, py - krad - max_disp), ymax = min(outH - 1, py + krad - max_disp);
+    const int xmin = max(0, px - krad - max_disp), xmax = min(outW - 1, px + krad - max_disp);
+    if (ymin <= ymax && xmin <= xmax)
+      for (int tc = 0; tc < outC; tc++) {
+        const int j2 = (tc / dsize - drad) * stride2, i2 = (tc % dsize - drad) * stride2;
+        const int y2 = y + j2, x2 = x + i2;
+        if (y2 < 0 || y2 >= H || x2 < 0 || x2 >= W) continue;      // the zero frame of rInput2
+        const float v2 = in2[plane + (size_t)y2 * W + x2];
+        for (int j = ymin; j <= ymax; j++)
+          for (int i = xmin; i <= xmax; i++) acc1 += g[(size_t)tc * oHW + (size_t)j * outW + i] * v2;
+      }
+  }
+  gin1[id] = acc1 / nel;
+  // d/d in2[y,x]: the same window shifted by the displacement (:254-287)
+  float acc2 = 0.f;
+  for (int tc = 0; tc < outC; tc++) {
+    const int j2 = (tc / dsize - drad) * stride2, i2 = (tc % dsize - drad) * stride2;
+    const int ymin = max(0, py - krad - max_disp - j2), ymax = min(outH - 1, py + krad - max_disp - j2);
+    const int xmin = max(0, px - krad - max_disp - i2), xmax = min(outW - 1, px + krad - max_disp - i2);
+    if (ymin > ymax || xmin > xmax) continue;
+    const int y1 = y - j2, x1 = x - i2;
+    if (y1 < 0 || y1 >= H || x1 < 0 || x1 >= W) continue;          // the zero frame of rInput1
+    const float v1 = in1[plane + (size_t)y1 * W + x1];
+    for (int j = ymin; j <= ymax; j++)
+      for (int i = xmin; i <= xmax; i++) acc2 += g[(size_t)tc * oHW + (size_t)j * outW + i] * v1;
+  }
+  gin2[id] = acc2 / nel;
+}
+
 // ---------------------------------------------------------------------------------------------
 // (f)1: KITTI depth error metrics, one CTA per image pair; sums in double (the reference's sequential
 // float sums are only reproducible to ~1e-5 relative anyway)
@@ -342,6 +392,27 @@ int dpv_correlation(const float* in1, const float* in2, int B, int C, int H, int
   correlation_kernel<<<aux_blocks(n), kAuxThreads, 0, (cudaStream_t)stream>>>(
       in1, in2, B, C, H, W, pad_size, kernel_size, max_displacement, stride1, stride2, oh, ow, out);
   return check_launch("dpv_correlation");
+}
+
+int dpv_correlation_backward(const float* grad_out, const float* in1, const float* in2, int B, int C, int H, int W,
+                             int pad_size, int kernel_size, int max_displacement, int stride1, int stride2,
+                             float* grad_in1, float* grad_in2, void* stream) {
+  DPV_REQUIRE(grad_out && in1 && in2 && grad_in1 && grad_in2, "dpv_correlation_backward: null pointer");
+  DPV_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, "dpv_correlation_backward: bad shape B=%d C=%d H=%d W=%d", B, C, H, W);
+  // correlation_cuda_kernel.cu:130-131,486: the reference launches one block per INPUT pixel but places it at
+  // blockIdx * stride1, so its backward is only defined for stride1 = 1 (it writes out of bounds otherwise)
+  DPV_REQUIRE(stride1 == 1, "dpv_correlation_backward: stride1 = %d (the reference's backward is defined for 1)", stride1);
+  int oc, oh, ow;
+  const int rc = dpv_correlation_shape(H, W, pad_size, kernel_size, max_displacement, stride1, stride2, &oc, &oh, &ow);
+  if (rc != DPV_OK) return rc;
+  const int krad = (kernel_size - 1) / 2;
+  DPV_REQUIRE((oh - 1) * stride1 + 2 * max_displacement + krad < H + 2 * pad_size &&
+                  (ow - 1) * stride1 + 2 * max_displacement + krad < W + 2 * pad_size,
+              "dpv_correlation_backward: taps leave the padded frame (pad_size %d too small)", pad_size);
+  const long long n = (long long)B * C * H * W;
+  correlation_backward_kernel<<<aux_blocks(n), kAuxThreads, 0, (cudaStream_t)stream>>>(
+      grad_out, in1, in2, B, C, H, W, pad_size, kernel_size, max_displacement, stride2, oh, ow, grad_in1, grad_in2);
+  return check_launch("dpv_correlation_backward");
 }
 
 int dpv_depth_errors(const float* pred, const float* gt, int n_images, int H, int W, float* out, void* stream) {

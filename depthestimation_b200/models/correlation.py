@@ -1,10 +1,28 @@
-"""Drop-ins for the reference's two correlation layers (forward): models/correlation_package/correlation.py:47-61
-(FlowNet-style, any pad / kernel / displacement / strides) and its torch twin models/correlation_native.py:6-23
-(kernel 1, strides 1, pad = max_displacement).  Both run the sm_100a kernel behind dpv_correlation.
-Inference only: the reference's backward kernels (training) are outside the hot path."""
+"""Drop-ins for the reference's two correlation layers: models/correlation_package/correlation.py:6-61
+(FlowNet-style CorrelationFunction / Correlation, any pad / kernel / displacement / strides) and its torch twin
+models/correlation_native.py:6-23 (kernel 1, strides 1, pad = max_displacement).  Forward and backward run the sm_100a
+kernels behind dpv_correlation / dpv_correlation_backward; the backward is defined for stride1 = 1 like the
+reference's (its launch writes out of bounds otherwise, correlation_cuda_kernel.cu:130-131,486)."""
 import torch
 
 from .. import ops
+
+
+class CorrelationFunction(torch.autograd.Function):
+    """correlation.py:6-45 as a new-style autograd Function: apply(input1, input2, pad_size, kernel_size,
+    max_displacement, stride1, stride2)."""
+
+    @staticmethod
+    def forward(ctx, input1, input2, pad_size, kernel_size, max_displacement, stride1, stride2):
+        ctx.save_for_backward(input1, input2)
+        ctx.cfg = (pad_size, kernel_size, max_displacement, stride1, stride2)
+        return ops.correlation(input1, input2, pad_size, kernel_size, max_displacement, stride1, stride2)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        input1, input2 = ctx.saved_tensors
+        g1, g2 = ops.correlation_backward(grad_output.contiguous(), input1, input2, *ctx.cfg)
+        return g1, g2, None, None, None, None, None
 
 
 class Correlation(torch.nn.Module):
@@ -18,10 +36,8 @@ class Correlation(torch.nn.Module):
         self.corr_multiply = corr_multiply          # accepted and, as in the reference's kernels, not used
 
     def forward(self, input1, input2):
-        if input1.requires_grad or input2.requires_grad:
-            raise NotImplementedError("Correlation: forward only (no autograd) in the B200 path")
-        return ops.correlation(input1, input2, self.pad_size, self.kernel_size, self.max_displacement, self.stride1,
-                               self.stride2)
+        return CorrelationFunction.apply(input1, input2, self.pad_size, self.kernel_size, self.max_displacement,
+                                         self.stride1, self.stride2)
 
 
 class CorrelationNative(torch.nn.Module):
@@ -34,6 +50,4 @@ class CorrelationNative(torch.nn.Module):
         self.pad_size = self.max_displacement
 
     def forward(self, x1, x2):
-        if x1.requires_grad or x2.requires_grad:
-            raise NotImplementedError("Correlation: forward only (no autograd) in the B200 path")
-        return ops.correlation(x1, x2, self.pad_size, 1, self.max_displacement, 1, 1)
+        return CorrelationFunction.apply(x1, x2, self.pad_size, 1, self.max_displacement, 1, 1)

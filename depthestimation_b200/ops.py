@@ -286,6 +286,20 @@ def correlation(x1, x2, pad_size, kernel_size, max_displacement, stride1, stride
     return out
 
 
+def correlation_backward(grad_out, x1, x2, pad_size, kernel_size, max_displacement, stride1, stride2):
+    """grad_out [B,outC,outH,outW], x1, x2 [B,C,H,W] -> (grad_x1, grad_x2) (correlation_cuda_kernel.cu:116-303)."""
+    a = f32(x1)
+    b = f32(x2, a.device)
+    g = f32(grad_out, a.device)
+    B, C, H, W = a.shape
+    g1, g2 = torch.empty_like(a), torch.empty_like(a)
+    with torch.cuda.device(_dev(a)):
+        check(lib().dpv_correlation_backward(ptr(g), ptr(a), ptr(b), B, C, H, W, pad_size, kernel_size,
+                                             max_displacement, stride1, stride2, ptr(g1), ptr(g2),
+                                             stream_ptr(a.device)))
+    return g1, g2
+
+
 def depth_errors(pred, gt):
     """pred, gt [n,H,W] (gt < 0 invalid) -> [n,10] (9 KITTI metrics + valid-pixel count)."""
     p = f32(pred)

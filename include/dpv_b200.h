@@ -240,6 +240,11 @@ int dpv_correlation_shape(int H, int W, int pad_size, int kernel_size, int max_d
                           int stride2, int* outC, int* outH, int* outW);
 int dpv_correlation(const float* in1, const float* in2, int B, int C, int H, int W, int pad_size, int kernel_size,
                     int max_displacement, int stride1, int stride2, float* out, void* stream);
+/* correlation_cuda_kernel.cu:116-303 backward (stride1 = 1, the only stride the reference's launch :486 supports):
+ * grad_out [B,outC,outH,outW], in1, in2 [B,C,H,W] -> grad_in1, grad_in2 [B,C,H,W]. */
+int dpv_correlation_backward(const float* grad_out, const float* in1, const float* in2, int B, int C, int H, int W,
+                             int pad_size, int kernel_size, int max_displacement, int stride1, int stride2,
+                             float* grad_in1, float* grad_in2, void* stream);
 /* depthError (external/deval_lib/src/evaluate_depth.h:20-118): pred, gt [n,H,W] (gt < 0 = invalid)
  *   -> out [n,10]: mae, rmse, inverse mae, inverse rmse, log mae, log rmse, scale invariant log, abs relative,
  *      squared relative, number of valid pixels. */

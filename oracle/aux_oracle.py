@@ -81,6 +81,48 @@ def correlation(x1, x2, pad_size, kernel_size, max_displacement, stride1, stride
     return out
 
 
+def correlation_backward(grad_out, x1, x2, pad_size, kernel_size, max_displacement, stride1, stride2):
+    """correlation_cuda_kernel.cu:116-303 for stride1 = 1 (the launch :486 places one block per input pixel at
+    blockIdx * stride1, so other strides write out of bounds in the reference): for every input element, the sum over
+    the displacements and over the outputs whose kernel window covers it of grad_out * the partner element of the
+    other (zero-padded) input, divided by kernel^2 * C.  -> (grad_x1, grad_x2) numpy [B,C,H,W]."""
+    if stride1 != 1:
+        raise NotImplementedError("the reference's correlation backward is defined for stride1 = 1")
+    a = np.asarray(x1, np.float32)
+    b = np.asarray(x2, np.float32)
+    g = np.asarray(grad_out, np.float32)
+    B, C, H, W = a.shape
+    oc, oh, ow = correlation_shape(H, W, pad_size, kernel_size, max_displacement, stride1, stride2)
+    krad = (kernel_size - 1) // 2
+    drad = max_displacement // stride2
+    dsize = 2 * drad + 1
+    nel = np.float32(kernel_size * kernel_size * C)
+    g1 = np.zeros_like(a)
+    g2 = np.zeros_like(a)
+
+    def window_sum(gc, lo_y, hi_y, lo_x, hi_x):                       # sum of gc [B,oh,ow] over a clipped box
+        lo_y, hi_y, lo_x, hi_x = max(0, lo_y), min(oh - 1, hi_y), max(0, lo_x), min(ow - 1, hi_x)
+        if lo_y > hi_y or lo_x > hi_x:
+            return None
+        return gc[:, lo_y:hi_y + 1, lo_x:hi_x + 1].sum((1, 2), dtype=np.float32)
+
+    for y in range(H):
+        for x in range(W):
+            py, px = y + pad_size, x + pad_size
+            for tc in range(oc):
+                j2 = (tc // dsize - drad) * stride2
+                i2 = (tc % dsize - drad) * stride2
+                s = window_sum(g[:, tc], py - krad - max_displacement, py + krad - max_displacement,
+                               px - krad - max_displacement, px + krad - max_displacement)       # :135-159
+                if s is not None and 0 <= y + j2 < H and 0 <= x + i2 < W:
+                    g1[:, :, y, x] += s[:, None] * b[:, :, y + j2, x + i2]
+                s = window_sum(g[:, tc], py - krad - max_displacement - j2, py + krad - max_displacement - j2,
+                               px - krad - max_displacement - i2, px + krad - max_displacement - i2)  # :254-277
+                if s is not None and 0 <= y - j2 < H and 0 <= x - i2 < W:
+                    g2[:, :, y, x] += s[:, None] * a[:, :, y - j2, x - i2]
+    return g1 / nel, g2 / nel
+
+
 # --------------------------------------------------------------------------
 # (f)1: external/deval_lib/src/evaluate_depth.h depthError, utils/img_utils.py depth_error / compute_unc_rmse
 # --------------------------------------------------------------------------

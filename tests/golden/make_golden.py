@@ -298,6 +298,22 @@ def case_plan_transformed():
          field_visual=vis, field_visual_sweep=vis_sweep)
 
 
+def case_correlation_backward():
+    """Gradients of the reference's torch twin of the correlation layer (models/correlation_native.py:6-23, the only
+    implementation of it that runs here) through autograd -> corr_bwd.npz."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("ref_corr_native", "/root/reference/models/correlation_native.py")
+    cn = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(cn)
+    g = torch.Generator().manual_seed(17)
+    x1 = torch.randn(2, 5, 9, 11, generator=g).requires_grad_()
+    x2 = torch.randn(2, 5, 9, 11, generator=g).requires_grad_()
+    out = cn.Correlation(max_displacement=3)(x1, x2)
+    gout = torch.randn(out.shape, generator=g)
+    out.backward(gout)
+    save("corr_bwd", x1=x1.detach(), x2=x2.detach(), grad_out=gout, grad_x1=x1.grad, grad_x2=x2.grad)
+
+
 def case_aux():
     """Rows a17 (gen_lc_dpv_true), a18 (inverse_warp), a19 (correlation_native twin) and compute_unc_rmse,
     run on the unmodified reference -> aux.npz."""
@@ -375,3 +391,4 @@ if __name__ == "__main__":
     case_plan_sweep()
     case_sense_transformed()
     case_plan_transformed()
+    case_correlation_backward()

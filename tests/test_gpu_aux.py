@@ -118,8 +118,32 @@ def test_correlation_golden_and_general():
         close(out, ref, atol=2e-6, what="correlation pad=%d k=%d md=%d s=%d/%d" % (pad, k, md, s1, s2))
     with pytest.raises(Exception):
         Correlation(0, 1, 20, 1, 1)(a.cuda(), b.cuda())             # displacement larger than the frame: empty output
-    with pytest.raises(NotImplementedError):
-        Correlation(4, 1, 4, 1, 1)(a.cuda().requires_grad_(), b.cuda())
+    with pytest.raises(Exception):
+        Correlation(4, 3, 4, 2, 2)(a.cuda().requires_grad_(), b.cuda()).sum().backward()   # backward: stride1 = 1 only
+
+
+def test_correlation_backward_golden_and_general():
+    """dpv_correlation_backward through autograd: against the gradients of the reference's torch twin
+    (tests/golden/corr_bwd.npz) and, for other pads / kernels / displacement strides, against the oracle's restatement
+    of correlation_cuda_kernel.cu:116-303."""
+    from depthestimation_b200.models.correlation import Correlation, CorrelationNative
+    g = load("corr_bwd")
+    for layer in (CorrelationNative(max_displacement=3), Correlation(3, 1, 3, 1, 1)):
+        x1, x2 = cu(g["x1"]).requires_grad_(), cu(g["x2"]).requires_grad_()
+        layer(x1, x2).backward(cu(g["grad_out"]))
+        close(x1.grad, g["grad_x1"], atol=2e-6, what="grad x1 (twin)")
+        close(x2.grad, g["grad_x2"], atol=2e-6, what="grad x2 (twin)")
+    gen = torch.Generator().manual_seed(8)
+    a = torch.randn(2, 7, 14, 19, generator=gen)
+    b = torch.randn(2, 7, 14, 19, generator=gen)
+    for pad, k, md, s2 in [(4, 1, 4, 1), (8, 1, 8, 2), (5, 3, 4, 2), (6, 3, 4, 1), (2, 1, 4, 1)]:
+        x1, x2 = a.cuda().requires_grad_(), b.cuda().requires_grad_()
+        out = Correlation(pad, k, md, 1, s2)(x1, x2)
+        gout = torch.randn(out.shape, generator=gen)
+        out.backward(gout.cuda())
+        r1, r2 = A.correlation_backward(gout.numpy(), a.numpy(), b.numpy(), pad, k, md, 1, s2)
+        close(x1.grad, r1, atol=5e-6, what="grad x1 pad=%d k=%d md=%d s2=%d" % (pad, k, md, s2))
+        close(x2.grad, r2, atol=5e-6, what="grad x2 pad=%d k=%d md=%d s2=%d" % (pad, k, md, s2))
 
 
 def test_depth_error_and_eval_errors():

@@ -196,6 +196,23 @@ def test_plan_with_separate_lc_camera_golden():
     ks, xz, counts = lc.rig("high").planner.solve(torch.stack(um_o).cuda())
     for i in range(3):
         np.testing.assert_array_equal(xz[i, :int(counts[i])].cpu().numpy(), g["path%d" % i])
+    # the quarter-resolution rig (lightcurtain_small / fw_small, lc/light_curtain.py:279-311) against the oracle
+    def quarter(K):
+        K = np.array(K, np.float32).copy()
+        K[0, :] *= 0.25
+        K[1, :] *= 0.25
+        return K
+    olow = LO.LightCurtainOracle(quarter(g["K_lc"]), Wl // 4, Hl // 4, g["d_candi"], g["d_candi_up"],
+                                 laser_timestep=3.5e-5 * 4)
+    olow.set_input_camera(quarter(g["K_rgb"]), [int(v) // 4 for v in g["size_rgb"]], g["rTc"])
+    uf_low = torch.as_tensor(g["uf"])[:, ::4].contiguous()
+    low = lc.plan_batched(uf_low.cuda().unsqueeze(0), [0.5], mode="low")
+    pre_l, fr_l = olow.prepare_field(uf_low.clone())
+    um_l, _ = olow.split_fields(fr_l, [0.5])
+    np.testing.assert_allclose(lc.rig("low").flow_T.cpu().numpy(), olow.flow_T[0].numpy(), rtol=0, atol=2e-6)
+    for i in range(3):
+        np.testing.assert_allclose(low["umaps"][0, i].cpu().numpy(), um_l[i].numpy(), rtol=1e-4, atol=2e-6,
+                                   err_msg="low umap %d" % i)
     # plan_sweep's visual with the same transform (NaN columns kept)
     _, vs = lc.plan_sweep_high(uf, {"start": 6.0, "end": 30.0, "step": 9.0})
     ref = g["field_visual_sweep"]

@@ -205,3 +205,41 @@ def test_plan_with_separate_lc_camera_against_reference():
     _, vs = lc.plan_sweep(T(g["uf"]).clone(), {"start": 6.0, "end": 30.0, "step": 9.0})
     np.testing.assert_array_equal(np.isnan(vs), np.isnan(g["field_visual_sweep"]))
     close(vs, g["field_visual_sweep"], rtol=1e-6, atol=1e-7)
+
+
+def test_correlation_backward_against_reference_twin_and_autograd():
+    """The restated backward of the correlation layer (correlation_cuda_kernel.cu:116-303) against the gradients of
+    the reference's torch twin (tests/golden/corr_bwd.npz), and — kernel 3, stride2 2 — against autograd through a
+    torch restatement of the forward."""
+    from oracle import aux_oracle as A
+    g = load("corr_bwd")
+    g1, g2 = A.correlation_backward(g["grad_out"], g["x1"], g["x2"], 3, 1, 3, 1, 1)
+    close(g1, g["grad_x1"], rtol=1e-5, atol=1e-6)
+    close(g2, g["grad_x2"], rtol=1e-5, atol=1e-6)
+    gen = torch.Generator().manual_seed(3)
+    B, C, H, W, pad, k, md, s2 = 1, 3, 8, 9, 5, 3, 4, 2
+    x1 = torch.randn(B, C, H, W, generator=gen, dtype=torch.float64).requires_grad_()
+    x2 = torch.randn(B, C, H, W, generator=gen, dtype=torch.float64).requires_grad_()
+    oc, oh, ow = A.correlation_shape(H, W, pad, k, md, 1, s2)
+    krad, drad = (k - 1) // 2, md // s2
+    # kernel > 1 taps start krad before the padded frame (the reference reads there unchecked): one more ring of zeros
+    p1 = torch.nn.functional.pad(x1, [pad + krad] * 4)
+    p2 = torch.nn.functional.pad(x2, [pad + krad] * 4)
+    outs = []
+    for tj in range(-drad, drad + 1):
+        for ti in range(-drad, drad + 1):
+            acc = 0
+            for j in range(-krad, krad + 1):
+                for i in range(-krad, krad + 1):
+                    ya, xa = md + j + krad, md + i + krad
+                    acc = acc + (p1[:, :, ya:ya + oh, xa:xa + ow] *
+                                 p2[:, :, ya + tj * s2:ya + tj * s2 + oh, xa + ti * s2:xa + ti * s2 + ow]).sum(1)
+            outs.append(acc / (k * k * C))
+    out = torch.stack(outs, 1)
+    close(out.detach().float(), A.correlation(x1.detach().float(), x2.detach().float(), pad, k, md, 1, s2),
+          rtol=1e-5, atol=1e-6)
+    gout = torch.randn(out.shape, generator=gen, dtype=torch.float64)
+    out.backward(gout)
+    g1, g2 = A.correlation_backward(gout.float(), x1.detach().float(), x2.detach().float(), pad, k, md, 1, s2)
+    close(g1, x1.grad.float().numpy(), rtol=1e-4, atol=1e-6)
+    close(g2, x2.grad.float().numpy(), rtol=1e-4, atol=1e-6)
