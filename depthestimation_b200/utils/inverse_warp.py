@@ -63,6 +63,9 @@ def inverse_warp(img, depth, pose, intrinsics, mode='bilinear', rotation_mode='e
     -> (projected_img [B,C,H,W], valid_points [B,H,W] bool)."""
     check_sizes(depth, 'depth', 'BHW')
     check_sizes(intrinsics, 'intrinsics', 'B33')
+    if torch.is_grad_enabled() and any(t.requires_grad for t in (img, depth, pose)):
+        raise NotImplementedError("inverse_warp: forward only in the B200 path (the reference differentiates it "
+                                  "through torch autograd for its training losses)")
     if pose.shape[1] == 6:
         pose_mat = pose_vec2mat(pose, rotation_mode)
     elif pose.shape[1] == 4 and pose.shape[2] == 4:
