@@ -1,4 +1,4 @@
 mkdir -p gpurun_out
-python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -2
-python bench.py > gpurun_out/bench_final.log 2>&1; echo "rc=$?"; tail -1 gpurun_out/bench_final.log | cut -c1-1500
-python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.log 2>&1; echo "rc=$?"; tail -1 gpurun_out/bench_ref.log | cut -c1-400
+python profiles/step_once.py C2_mono_lc_b8 1 > gpurun_out/step_once.log 2>&1 || { tail -5 gpurun_out/step_once.log; exit 1; }
+ncu --set full --clock-control none --import-source on -k regex:"lsm_stats_kernel|plane_sweep_block_kernel|warp_feature_kernel" -c 3 -o gpurun_out/ncu_r01_sweep_lsm -f python profiles/step_once.py C2_mono_lc_b8 1 > gpurun_out/ncu_sweep_lsm.log 2>&1
+echo "ncu rc=$?"; ls -la gpurun_out/*.ncu-rep
