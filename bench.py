@@ -37,6 +37,8 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--launch", default="graph", choices=["graph", "eager"],
+                    help="value loop: replay one captured CUDA graph per batch slot (default) or launch kernel by kernel")
     ap.add_argument("--streams", type=int, default=6,
                     help="independent batches in flight (steps are issued round-robin on this many CUDA streams)")
     return ap.parse_args()
@@ -160,6 +162,22 @@ def run_b200(args):
             dist.barrier()
             torch.cuda.synchronize(dev)
 
+    graphs = None                                       # per batch slot: (CUDAGraph, its static output dict)
+    launches_per_step = None
+
+    def capture_graphs():
+        """The step is ~80 kernel launches on ~2 ms of GPU work per batch; with 8 ranks on one host the launching
+        threads fall behind the GPUs.  One CUDA graph per batch slot (captured after an eager step has sized every
+        buffer) makes a step one graph launch.  The graph holds exactly the kernels the eager step launches."""
+        got = []
+        n_before = _lib.launch_count()
+        for sl in range(S):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=streams[sl]):
+                out = pipes[sl].step(x)
+            got.append((g, out))
+        return got, (_lib.launch_count() - n_before) // S
+
     def run_steps(n):
         """n steps, step i on stream i % S: successive (independent) batches overlap — the latency-bound planner of
         one batch runs beside the streaming kernels of the next."""
@@ -170,7 +188,11 @@ def run_b200(args):
         coll = sharding.FrameOutputCollector(n, world)
         for i in range(n):
             with torch.cuda.stream(streams[i % S]):
-                coll.add(pipes[i % S].step(x))
+                if graphs is not None:
+                    graphs[i % S][0].replay()
+                    coll.add(graphs[i % S][1])
+                else:
+                    coll.add(pipes[i % S].step(x))
         for st in streams:
             done = torch.cuda.Event()
             done.record(st)
@@ -180,8 +202,20 @@ def run_b200(args):
     # ---- value: inputs resident in HBM --------------------------------------------------------
     run_steps(max(args.warmup, S))
     sync()
+    launch_mode = "eager"
+    if args.launch == "graph":
+        try:
+            graphs, launches_per_step = capture_graphs()
+            launch_mode = "cuda-graph replay, one graph per batch slot"
+            sync()
+            run_steps(max(args.warmup, S))              # warm-up of the replays themselves
+            sync()
+        except Exception as e:                          # stay measurable: kernel-by-kernel launches
+            graphs = None
+            launch_mode = "eager (graph capture failed: %s)" % str(e).splitlines()[0][:120]
+            torch.cuda.synchronize(dev)
     for p_ in pipes:
-        p_.fuse_events = []
+        p_.fuse_events = [] if graphs is None else None  # events inside a captured graph cannot be timed
     n0 = _lib.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clk:
@@ -191,8 +225,24 @@ def run_b200(args):
         e1.record(main)
         sync()
     ms = e0.elapsed_time(e1)
-    launches = _lib.launch_count() - n0
-    fuse_ms = [a.elapsed_time(b) for p_ in pipes for a, b in p_.fuse_events]
+    launches = _lib.launch_count() - n0 if graphs is None else launches_per_step * args.steps
+    if graphs is None:
+        fuse_ms = [a.elapsed_time(b) for p_ in pipes for a, b in p_.fuse_events]
+        ms_events = ms
+    else:
+        # the kernel's in-flight timing needs events around single launches: one more (untimed for `value`) eager pass
+        replay, graphs = graphs, None
+        for p_ in pipes:
+            p_.fuse_events = []
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sync()
+        g0.record(main)
+        run_steps(args.steps)
+        g1.record(main)
+        sync()
+        ms_events = g0.elapsed_time(g1)
+        fuse_ms = [a.elapsed_time(b) for p_ in pipes for a, b in p_.fuse_events]
+        graphs = replay
     for p_ in pipes:
         p_.fuse_events = None
     ms_t = torch.tensor([ms], device=dev)
@@ -217,7 +267,7 @@ def run_b200(args):
             return {"launch_ms": round(t * 1e3, 4), "achieved": round(ach, 1), "frac": round(ach / peak_gbs, 4),
                     "launches_timed": len(times_ms),
                     "share_of_step": round(sum(times_ms) / step_ms_total if step_ms_total else 0.0, 4)}
-        in_region = roof_of(fuse_ms, ms)
+        in_region = roof_of(fuse_ms, ms_events)
         solo = in_region
         if S > 1:
             # With S batches in flight the events around a launch also span the slices other streams' kernels get
@@ -243,6 +293,8 @@ def run_b200(args):
         if S > 1:
             roof["timed_with"] = "1 batch in flight (pass after the timed region)"
             roof["in_flight"] = dict(in_region, batches=S)
+            if launch_mode != "eager" and not launch_mode.startswith("eager"):
+                roof["in_flight"]["timed_with"] = "eager pass of the same streams after the timed region"
         tr = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tr):
             roof["traffic"] = json.load(open(tr)).get("sense_fuse_kernel")
@@ -260,6 +312,7 @@ def run_b200(args):
                 "config": {"workload": args.workload, "frames_per_gpu": B, "H": meta["H"], "W": meta["W"],
                            "D": meta["D"], "C": meta["C"], "T": meta["T"], "lc_iterations": meta["iterations"],
                            "curtains_per_iteration": 1 + 2 * len(meta["step"]), "parallelism": "batch-shard x%d" % world, "streams_in_flight": S,
+                           "launch": launch_mode,
                            "l2_policy": "inputs larger than L2 (0.9 GB streamed per frame)"},
                 "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
                 "ms_per_frame": round(ms_per_step / B, 4)}

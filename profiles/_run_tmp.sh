@@ -1,4 +1,4 @@
 mkdir -p gpurun_out
-python profiles/step_once.py C2_mono_lc_b8 1 > gpurun_out/step_once.log 2>&1 || { tail -5 gpurun_out/step_once.log; exit 1; }
-ncu --set full --clock-control none --import-source on -k regex:"lsm_stats_kernel|plane_sweep_block_kernel|warp_feature_kernel" -c 3 -o gpurun_out/ncu_r01_sweep_lsm -f python profiles/step_once.py C2_mono_lc_b8 1 > gpurun_out/ncu_sweep_lsm.log 2>&1
-echo "ncu rc=$?"; ls -la gpurun_out/*.ncu-rep
+nproc; free -g | head -2
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29518 bench.py --gpus 8 --steps 20 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/bench_8gpu_graph.log 2>&1; echo "N=8 rc=$?"; tail -1 gpurun_out/bench_8gpu_graph.log | cut -c1-260
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29519 bench.py --gpus 8 --steps 40 --warmup 3 --no-cpu-baseline --no-e2e > gpurun_out/bench_8gpu_graph40.log 2>&1; echo "N=8 rc=$?"; tail -1 gpurun_out/bench_8gpu_graph40.log | cut -c1-260
