@@ -59,8 +59,8 @@ struct LcPlanner {
   // lc_planner_solve's producer -> consumer log (grown on demand; one solve at a time per handle)
   unsigned char* d_log = nullptr;
   size_t log_bytes = 0;
-  // device-side solve counter {epoch, CTAs finished}: a launch captured in a CUDA graph takes the tag of its log
-  // entries from it, so that every replay is tagged differently
+  // device-side solve counter {epoch, CTAs finished} of the DPV_PLANNER_DEVTAG=1 variant: a launch captured in a
+  // CUDA graph takes the tag of its log entries from it (the default clears the log with a memset node instead)
   unsigned* d_epoch = nullptr;
   int host_epoch = 0;           // tags of directly launched solves (kernel parameter)
   int last_n = 0;

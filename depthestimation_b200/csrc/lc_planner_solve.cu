@@ -436,8 +436,21 @@ int launch_solve(LcPlanner* p, const float* umaps, int n, int warps, int32_t* ks
     (void)cudaGetLastError();
     cap = cudaStreamCaptureStatusNone;
   }
-  const bool devtag = cap != cudaStreamCaptureStatusNone;
+  const bool capturing = cap != cudaStreamCaptureStatusNone;
   p->host_epoch = p->host_epoch % 32767 + 1;                      // 1..32767
+  unsigned host_tag = (unsigned)p->host_epoch;
+  // Captured in a CUDA graph the tag parameter is frozen, so every replay would meet its own previous entries as
+  // valid ones.  Two ways out: clear this solve's log region inside the graph (a memset node of W*RP*8 bytes per map,
+  // ~6 us at C2) and keep the parameter-tag kernel, or the device-counter variant (no memset; measured 63 us slower
+  // per solve: its two extra registers).  The memset is the default; DPV_PLANNER_DEVTAG=1 selects the counter.
+  // Frozen tags come from 32768..65535, so a directly launched solve (1..32767) never takes a replay's entries for
+  // its own.
+  static const bool want_devtag = getenv("DPV_PLANNER_DEVTAG") && atoi(getenv("DPV_PLANNER_DEVTAG")) != 0;
+  const bool devtag = capturing && want_devtag;
+  if (capturing && !devtag) {
+    DPV_CUDA(cudaMemsetAsync(p->d_log, 0, per_map * n * 8, st));
+    host_tag = 32768u + ((unsigned)p->host_epoch & 32767u);
+  }
   auto kern = devtag ? planner_solve_kernel<LANES, NQL, true> : planner_solve_kernel<LANES, NQL, false>;
   DPV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int threads = ((R * LANES + 31) / 32) * 32;                     // part A: LANES threads per node
@@ -460,7 +473,7 @@ int launch_solve(LcPlanner* p, const float* umaps, int n, int warps, int32_t* ks
   cfg.attrs = attr;
   cfg.numAttrs = 2;
   DPV_CUDA(cudaLaunchKernelEx(&cfg, kern, umaps, W, R, (const float*)p->d_theta, (const float*)p->d_xz,
-                              (const uint8_t*)p->d_win, (unsigned long long*)p->d_log, per_map, (unsigned)p->host_epoch, p->d_epoch, ks, xz,
+                              (const uint8_t*)p->d_win, (unsigned long long*)p->d_log, per_map, host_tag, p->d_epoch, ks, xz,
                               counts));
   return DPV_OK;
 }

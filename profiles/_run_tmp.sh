@@ -1,4 +1,7 @@
 mkdir -p gpurun_out
-python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/b2.log 2>&1 || { tail -5 gpurun_out/b2.log; exit 1; }
-timeout 600 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum,sm__warps_active.avg.pct_of_peak_sustained_active,launch__registers_per_thread --clock-control none -c 600 --csv --log-file gpurun_out/launches_graph.csv python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > gpurun_out/ncu_launches.log 2>&1
-echo "ncu rc=$?"; tail -2 gpurun_out/ncu_launches.log | cut -c1-300; wc -l gpurun_out/launches_graph.csv
+timeout 900 python -m pytest tests -m gpu -q 2>&1 | tail -5
+python bench.py --no-cpu-baseline --no-e2e --steps 24 > gpurun_out/bench_memset.log 2>&1; echo "memset rc=$? $(tail -1 gpurun_out/bench_memset.log | cut -c1-140)"
+DPV_PLANNER_DEVTAG=1 python bench.py --no-cpu-baseline --no-e2e --steps 24 > gpurun_out/bench_devtag.log 2>&1; echo "devtag rc=$? $(tail -1 gpurun_out/bench_devtag.log | cut -c1-140)"
+python bench.py --no-cpu-baseline --no-e2e --steps 24 --launch eager > gpurun_out/bench_eager2.log 2>&1; echo "eager rc=$? $(tail -1 gpurun_out/bench_eager2.log | cut -c1-140)"
+python bench.py --no-cpu-baseline --no-e2e --steps 24 --streams 1 > gpurun_out/bench_memset_s1.log 2>&1; echo "memset S=1 rc=$? $(tail -1 gpurun_out/bench_memset_s1.log | cut -c1-140)"
+python bench.py --no-cpu-baseline --no-e2e --steps 24 --streams 1 --launch eager > gpurun_out/bench_eager_s1.log 2>&1; echo "eager S=1 rc=$? $(tail -1 gpurun_out/bench_eager_s1.log | cut -c1-140)"
