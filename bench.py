@@ -37,8 +37,10 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--launch", default="graph", choices=["graph", "eager"],
-                    help="value loop: replay one captured CUDA graph per batch slot (default) or launch kernel by kernel")
+    ap.add_argument("--launch", default="auto", choices=["auto", "graph", "eager"],
+                    help="value loop: replay one captured CUDA graph per batch slot, or launch kernel by kernel; auto = "
+                         "graphs when more than 4 ranks share the host (their launching threads fall behind the GPUs: "
+                         "DESIGN.md section 7), kernel by kernel otherwise (0-3 %% faster at 1-4 ranks)")
     ap.add_argument("--streams", type=int, default=6,
                     help="independent batches in flight (steps are issued round-robin on this many CUDA streams)")
     return ap.parse_args()
@@ -90,15 +92,21 @@ def time_cpu(workload, steps, warmup, frames_per_step=1):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """SM clock and throttle reasons while the GPU runs the step (B200_PROFILING.md's clocks line: `nvidia-smi -lms 200`
+    started BEFORE the timed region and killed after it, so that its start-up — it attaches to every GPU of the box —
+    stays out of the region).  start() launches it, wait_ready() returns once the first row is in, rows are
+    time-stamped on arrival; summary(t0, t1) uses the rows that arrived in [t0, t1] (the caller keeps the GPU under
+    the same load until at least one has).  DPV_BENCH_CLOCKS=off disables it."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.p = index, [], None
+        self.index, self.rows, self.p, self.t = index, [], None, None
 
-    def __enter__(self):
+    def start(self):
+        if os.environ.get("DPV_BENCH_CLOCKS", "smi") == "off":
+            return self
         try:
             self.p = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
                                        "-lms", "200", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
@@ -110,19 +118,27 @@ class ClockSampler:
 
     def _read(self):
         for line in self.p.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
 
-    def __exit__(self, *a):
+    def wait_ready(self, timeout=5.0):
+        t_end = time.perf_counter() + timeout
+        while self.p and not self.rows and time.perf_counter() < t_end:
+            time.sleep(0.01)
+
+    def count(self, t0, t1=None):
+        return sum(1 for t, _ in self.rows if t >= t0 and (t1 is None or t <= t1))
+
+    def stop(self):
         if self.p:
-            time.sleep(0.25)
             self.p.terminate()
             self.t.join(timeout=2)
 
-    def summary(self):
-        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
-        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+    def summary(self, t0=None, t1=None):
+        rows = [r for t, r in self.rows if (t0 is None or t >= t0) and (t1 is None or t <= t1)]
+        sm = [float(r[1]) for r in rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
         reasons = set()
-        for r in self.rows:
+        for r in rows:
             if len(r) >= 9:
                 for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
                     if v.lower().startswith("active"):
@@ -200,10 +216,11 @@ def run_b200(args):
         coll.finish()                                   # the one exchange of the path: all ranks' depth maps (NCCL)
 
     # ---- value: inputs resident in HBM --------------------------------------------------------
+    sampler = ClockSampler(local).start()               # before the region: its start-up must not land inside it
     run_steps(max(args.warmup, S))
     sync()
     launch_mode = "eager"
-    if args.launch == "graph":
+    if args.launch == "graph" or (args.launch == "auto" and world > 4):
         try:
             graphs, launches_per_step = capture_graphs()
             launch_mode = "cuda-graph replay, one graph per batch slot"
@@ -214,18 +231,44 @@ def run_b200(args):
             graphs = None
             launch_mode = "eager (graph capture failed: %s)" % str(e).splitlines()[0][:120]
             torch.cuda.synchronize(dev)
+    def load_pass():
+        """S steps without the collector (no collective, no barrier): keeps the GPU under the step's load."""
+        for sl in range(S):
+            with torch.cuda.stream(streams[sl]):
+                if graphs is not None:
+                    graphs[sl][0].replay()
+                else:
+                    pipes[sl].step(x)
+        torch.cuda.synchronize(dev)
+
+    sampler.wait_ready()
+    load_pass()                                         # the GPU is under the step's load when the region starts
     for p_ in pipes:
         p_.fuse_events = [] if graphs is None else None  # events inside a captured graph cannot be timed
     n0 = _lib.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clk:
-        sync()
-        e0.record(main)
-        run_steps(args.steps)
-        e1.record(main)
-        sync()
+    sync()
+    t_load0 = time.perf_counter()
+    e0.record(main)
+    run_steps(args.steps)
+    e1.record(main)
+    sync()
+    n1 = _lib.launch_count()
+    stash = [p_.fuse_events for p_ in pipes]
+    for p_ in pipes:
+        p_.fuse_events = None
+    extra = 0
+    while sampler.p and sampler.count(t_load0) == 0 and extra < 40:
+        load_pass()                                     # a short region can fall between two 200 ms samples: keep the
+        extra += 1                                      # same load (untimed, rank-local) until one has been taken
+    t_load1 = time.perf_counter()
+    sampler.stop()
+    for p_, ev in zip(pipes, stash):
+        p_.fuse_events = ev
+    clk_summary = sampler.summary(t_load0, t_load1)
+    clk_summary["window"] = "timed region" if extra == 0 else "timed region + %d untimed passes of the same steps" % extra
     ms = e0.elapsed_time(e1)
-    launches = _lib.launch_count() - n0 if graphs is None else launches_per_step * args.steps
+    launches = n1 - n0 if graphs is None else launches_per_step * args.steps
     if graphs is None:
         fuse_ms = [a.elapsed_time(b) for p_ in pipes for a, b in p_.fuse_events]
         ms_events = ms
@@ -314,7 +357,7 @@ def run_b200(args):
                            "curtains_per_iteration": 1 + 2 * len(meta["step"]), "parallelism": "batch-shard x%d" % world, "streams_in_flight": S,
                            "launch": launch_mode,
                            "l2_policy": "inputs larger than L2 (0.9 GB streamed per frame)"},
-                "clocks": clk.summary(), "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
+                "clocks": clk_summary, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
                 "ms_per_frame": round(ms_per_step / B, 4)}
         print(json.dumps(line))
     if world > 1:
