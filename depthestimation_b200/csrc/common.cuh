@@ -5,6 +5,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 
 #include "dpv_b200.h"
 
@@ -33,6 +34,8 @@ inline int check_launch(const char* what) {
 inline int high_priority() {
   static int greatest = [] {
     int least = 0, g = 0;
+    if (const char* e = getenv("DPV_PRIORITY"))                      // tuning aid: DPV_PRIORITY=0 launches at default priority
+      if (atoi(e) == 0) return 0;
     if (cudaDeviceGetStreamPriorityRange(&least, &g) != cudaSuccess) {
       (void)cudaGetLastError();
       g = 0;

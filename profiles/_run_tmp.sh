@@ -1,4 +1,9 @@
 mkdir -p gpurun_out
-python bench.py > gpurun_out/bench_final.log 2>&1; echo "N=1 rc=$?"; tail -1 gpurun_out/bench_final.log | cut -c1-900
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29538 bench.py --gpus 8 --steps 20 --warmup 3 > gpurun_out/bench_8gpu_final.log 2>&1; echo "N=8 rc=$?"; tail -1 gpurun_out/bench_8gpu_final.log | cut -c1-900
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29539 bench.py --impl reference --gpus 8 --steps 1 --warmup 1 > gpurun_out/bench_8gpu_ref.log 2>&1; echo "N=8 ref rc=$?"; tail -1 gpurun_out/bench_8gpu_ref.log | cut -c1-200
+show() { tail -1 $1 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print(d['value'], d['ms_per_step'])"; }
+A="--no-cpu-baseline --no-e2e --steps 24"
+for i in 1 2; do
+python bench.py $A --launch eager > gpurun_out/p_e$i.log 2>&1; echo "eager prio     $(show gpurun_out/p_e$i.log)"
+python bench.py $A --launch graph > gpurun_out/p_g$i.log 2>&1; echo "graph prio     $(show gpurun_out/p_g$i.log)"
+DPV_PRIORITY=0 python bench.py $A --launch eager > gpurun_out/p_e0$i.log 2>&1; echo "eager no-prio  $(show gpurun_out/p_e0$i.log)"
+DPV_PRIORITY=0 python bench.py $A --launch graph > gpurun_out/p_g0$i.log 2>&1; echo "graph no-prio  $(show gpurun_out/p_g0$i.log)"
+done
