@@ -1,9 +1,3 @@
 mkdir -p gpurun_out
-show() { tail -1 $1 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print(d['value'], d['ms_per_step'])"; }
-A="--no-cpu-baseline --no-e2e --steps 24"
-for i in 1 2; do
-python bench.py $A --launch eager > gpurun_out/p_e$i.log 2>&1; echo "eager prio     $(show gpurun_out/p_e$i.log)"
-python bench.py $A --launch graph > gpurun_out/p_g$i.log 2>&1; echo "graph prio     $(show gpurun_out/p_g$i.log)"
-DPV_PRIORITY=0 python bench.py $A --launch eager > gpurun_out/p_e0$i.log 2>&1; echo "eager no-prio  $(show gpurun_out/p_e0$i.log)"
-DPV_PRIORITY=0 python bench.py $A --launch graph > gpurun_out/p_g0$i.log 2>&1; echo "graph no-prio  $(show gpurun_out/p_g0$i.log)"
-done
+ncu --set full --clock-control none --import-source on -k regex:"lsm_stats_kernel" -s 2 -c 1 -o gpurun_out/ncu_r01_lsm_full -f python profiles/step_once.py C2_mono_lc_b8 1 > gpurun_out/ncu_lsm.log 2>&1
+echo "ncu rc=$?"; ls -la gpurun_out/ncu_r01_lsm_full.ncu-rep
