@@ -61,7 +61,8 @@ def oracle_step(batch, meta, lc_cache={}):
         cost = O.plane_sweep_cost(batch["feat_all"][b:b + 1, -1], batch["feat_all"][b:b + 1, :-1], d,
                                   batch["R"][b, :-1], batch["t"][b, :-1], K, rays, 10.0, "L2")
         bv = O.logsoftmax_stats(cost, d)[0]
-        O.warp_feature_diag(batch["feat_raw"][b:b + 1], d, batch["R"][b], batch["t"][b], K, rays)
+        if meta.get("warp_feature", True):
+            O.warp_feature_diag(batch["feat_raw"][b:b + 1], d, batch["R"][b], batch["t"][b], K, rays)
         O.logsoftmax_stats(bv, d, batch["bv_resi"][b:b + 1])
         logp, mean, var, ent = O.logsoftmax_stats(batch["dec_logits"][b:b + 1], d)
         O.carry_quarter(logp)

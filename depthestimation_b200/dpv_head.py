@@ -65,12 +65,16 @@ class LcLoopState:
 
 
 def lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n, noise=None, trace=None, events=None,
-                 in_prob=False, out_prob=False):
-    """One Bayesian iteration (models.py:1027-1122) for the whole batch: 6 kernel launches, no host sync."""
+                 in_prob=False, out_prob=False, src=None):
+    """One Bayesian iteration (models.py:1027-1122) for the whole batch: 6 kernel launches, no host sync.
+    src = (volume, E[d]) to read instead of the state's own buffers (the first iteration of a loop reads the caller's
+    DPV and writes the state's: the caller's volume and depth map stay as they were, like the reference's
+    output_refined next to output_lc)."""
     from ._lib import check, lib, ptr, stream_ptr
     B, D, H, W, R, nc = state.shape
     dev = rig.dev
-    ops.ufield(state.logp, state.mean, K, lc.d_candi, uf_par, bv_log=not in_prob, want_depth=False, out=state.uf)
+    vol_in, mean_in = (state.logp, state.mean) if src is None else src
+    ops.ufield(vol_in, mean_in, K, lc.d_candi, uf_par, bv_log=not in_prob, want_depth=False, out=state.uf)
     ops.plan_prepare(state.uf, rig.flow, steps, R, state.umaps, state.argmax, state.field_pre)
     rig.planner.solve(state.umaps.view(B * nc, R, W), state.ks, state.xz, state.counts)
     check(lib().lc_curtain_planes(dev._h, ptr(state.xz), ptr(state.counts), B * nc, W, ptr(state.planes), None,
@@ -81,7 +85,7 @@ def lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n,
     if events is not None:                       # bench.py: CUDA-event bracket of the dominant kernel
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-    dev.sense_fuse(state.logp, depth, state.planes, nc, lc.d_candi, spread_iter, spread_n, noise=noise,
+    dev.sense_fuse(vol_in, depth, state.planes, nc, lc.d_candi, spread_iter, spread_n, noise=noise,
                    out=state.logp, mean=state.mean, in_prob=in_prob, out_prob=out_prob,
                    in_clamped=in_prob)           # a probability volume here is the previous iteration's own output
     if events is not None:
@@ -227,8 +231,10 @@ def lc_process(BV_cur_all, model_input, lc, mode="low", iterations=5, viz=False,
     R, nc = len(lc.r_candi_up), 1 + 2 * len(steps)
     if state is None:
         state = LcLoopState(B, D, H, W, R, nc, dev)
-    state.logp.copy_(final)
-    ops.expectation(state.logp, lc.d_candi, True, out=state.mean)
+    final = final.float().contiguous()
+    if iterations == 0:
+        return BV_cur_all.detach().clone(), [[] for _ in range(B)]
+    mean0 = ops.expectation(final, lc.d_candi, True)
     unc_scores = [[] for _ in range(B)]
     for i in range(iterations):
         nz = None
@@ -237,8 +243,9 @@ def lc_process(BV_cur_all, model_input, lc, mode="low", iterations=5, viz=False,
         elif rig.dev.hit_noise > 0:
             nz = rig.dev.noise_like(B * nc)
         # between iterations the volume stays clamped probability (no exp/log per bin); log only in and out
+        # the first iteration reads the caller's volume and writes the state's (no copy, the input stays intact)
         lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n, noise=nz, trace=trace,
-                     in_prob=i > 0, out_prob=i < iterations - 1)
+                     in_prob=i > 0, out_prob=i < iterations - 1, src=(final, mean0) if i == 0 else None)
     out = state.logp
     if D != D_in:                                                             # :1124
         out = ops.resample_depth(out, D_in, bv_log=True)

@@ -33,6 +33,12 @@ WORKLOADS = {
                            d_min=5., d_max=40., dataset="kitti", R=128),
     "C4_stereo_lc_d128": dict(B=4, T=2, H=256, W=768, D=128, C=128, iterations=5, step=[0.5], spread_iter=2,
                               spread_n=5, d_min=5., d_max=40., dataset="kitti", R=128, stereo=True),
+    # BASELINE configs[4] (default_318_lc_sweep shape-scaled): 512 x 1536, D = 128, nmode "lc" (no
+    # warp_feature), d 3-18 m, the config's own LC parameters (configs/default_318_lc_sweep.json:31-38: step [0.75],
+    # spread_iter 1, spread_n 3), "sweep" uncertainty-field branch (pshift 0 + quash, img_utils.py:491-497,532-539),
+    # W = 1536 planner; 4 recursive refinements per frame
+    "C5_lcsweep_hr": dict(B=2, T=2, H=512, W=1536, D=128, C=64, iterations=4, step=[0.75], spread_iter=1, spread_n=3,
+                          d_min=3., d_max=18., dataset="sweep", R=128, warp_feature=False),
     "tiny": dict(B=2, T=2, H=32, W=64, D=16, C=16, iterations=2, step=[0.5], spread_iter=2, spread_n=5,
                  d_min=5., d_max=40., dataset="kitti", R=32, hfov=16.0, vfov=10.0),
     # C4's depth / range resolution (D = C = R = 128: four lanes per pixel, 48 KB of staging in plan_prepare) at test size
@@ -131,8 +137,9 @@ class DpvLcPipeline:
             self.lc = LightCurtain()
             self.lc.init(P)
             nc = 1 + 2 * len(meta["step"])
-            self.state = dpv_head.LcLoopState(meta["B"], meta["D"], H, W, meta["R"], nc, self.device, alloc_volume=False)
+            self.state = dpv_head.LcLoopState(meta["B"], meta["D"], H, W, meta["R"], nc, self.device)
         self.fuse_events = None          # optional list collecting (start, end) CUDA events of sense+fuse launches
+        self.trace = None                # optional list: per-iteration uf / umaps / ks / logp clones (parity tests)
 
     def step(self, x):
         """x: dict of CUDA tensors (synthetic_batch layout) -> dict(depth, var, entropy, carry, carry_lc, logp_lc)."""
@@ -142,7 +149,9 @@ class DpvLcPipeline:
         cost = ops.plane_sweep(x["feat_all"][:, -1], x["feat_all"][:, :-1], x["K"], x["R"][:, :-1], x["t"][:, :-1],
                                x["rays"], center, d, self.sigma, "L2")
         bv = ops.logsoftmax_stats(cost, d, want_var=False, want_entropy=False)["logp"]   # conv0.. are cuDNN, skipped
-        warped = ops.warp_feature(x["feat_raw"], x["K"], x["R"], x["t"], x["rays"], center, d)
+        warped = None
+        if m.get("warp_feature", True):                              # nmode "lc" has no feature warp (models.py:640-661)
+            warped = ops.warp_feature(x["feat_raw"], x["K"], x["R"], x["t"], x["rays"], center, d)
         bv_upd = ops.logsoftmax_stats(bv, d, add=x["bv_resi"], want_var=False, want_entropy=False)["logp"]
         r = ops.logsoftmax_stats(x["dec_logits"], d, want_carry=True)
         out = dict(depth=r["mean"], var=r["var"], entropy=r["entropy"], carry=r["carry"], bv_low=bv_upd, warped=warped,
@@ -163,11 +172,14 @@ class DpvLcPipeline:
         K = mi["intrinsics_up"]
         depth = torch.nn.functional.interpolate(mi["dmaps"].unsqueeze(1), scale_factor=4, mode="nearest").squeeze(1)
         uf_par = img_utils.uf_params(m["dataset"])
-        st.logp, st.mean = logp, mean                                # fuse in place on the freshly written volume
+        # The first iteration reads the refined DPV / depth the log-softmax kernel wrote and writes the loop's own
+        # volume; later iterations run in place on that.  out["logp"] / out["depth"] (the reference's output_refined,
+        # models.py:784-787) therefore stay what they were next to out["logp_lc"] / out["depth_lc"] (output_lc).
         for i in range(m["iterations"]):
             nz = rig.dev.noise_like(st.shape[0] * st.shape[5]) if rig.dev.hit_noise > 0 else None
             dpv_head.lc_iteration(st, lc, rig, depth, K, uf_par, m["step"], m["spread_iter"], m["spread_n"], noise=nz,
-                                  events=self.fuse_events, in_prob=i > 0, out_prob=i < m["iterations"] - 1)
+                                  events=self.fuse_events, trace=self.trace, in_prob=i > 0,
+                                  out_prob=i < m["iterations"] - 1, src=(logp, mean) if i == 0 else None)
         return st.logp
 
     def algorithmic_bytes(self):
@@ -175,7 +187,8 @@ class DpvLcPipeline:
         m = self.m
         B, T, H, W, D, C = m["B"], m["T"], m["H"], m["W"], m["D"], m["C"]
         h, w, V = H // 4, W // 4, T - 1
-        per = dict(sweep=4 * h * w * ((1 + V) * (C + 3) + D), warp_feature=4 * h * w * T * (C + D),
+        per = dict(sweep=4 * h * w * ((1 + V) * (C + 3) + D),
+                   warp_feature=4 * h * w * T * (C + D) if m.get("warp_feature", True) else 0,
                    lsm_low=4 * h * w * D * 5, lsm_full=4 * H * W * (2 * D + 3) + 4 * h * w * D,
                    ufield=4 * H * W * D + 4 * D * W, sense_fuse=4 * H * W * (2 * D + 2))
         return {k: v * B for k, v in per.items()}

@@ -273,6 +273,14 @@ def test_pipeline_tiny_matches_oracle_step(workload):
     pipe = DpvLcPipeline(meta, torch.device("cuda", 0))
     out = pipe.step({k: v.cuda() for k, v in host.items()})
     exp = bench.oracle_step(host, meta)
+    # the refined (pre-LC) outputs stay next to the LC outputs (models.py:784-787: output_refined and output_lc)
+    ref_logp, ref_mean, ref_var, ref_ent = O.logsoftmax_stats(host["dec_logits"], meta["d_candi"])
+    close(out["logp"], ref_logp, atol=1e-5)
+    close(out["depth"], ref_mean, atol=1e-5)
+    close(out["var"], ref_var, atol=1e-4)
+    close(out["entropy"], ref_ent, atol=1e-5)
+    assert out["depth"].data_ptr() != out["depth_lc"].data_ptr() and out["logp"].data_ptr() != out["logp_lc"].data_ptr()
+    assert float((out["depth"] - out["depth_lc"]).abs().max()) > 1e-3         # the curtains did move the depth map
     close(out["logp_lc"], exp, atol=1e-5)
     close(out["depth_lc"], torch.cat([O.dpv_expectation(exp[b:b + 1], meta["d_candi"], True) for b in range(meta["B"])]),
           atol=1e-5)
