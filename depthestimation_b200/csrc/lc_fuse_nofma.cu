@@ -179,6 +179,7 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
     const float kk_q = -1.4426950408889634f / opaque(den_pos ? mine.den : 1.f);
     const float mine_kk = den_pos ? kk_q : (mine.den == 0.f ? -INFINITY : NAN);   // den = 2 sigma^2 is never -0
     const int jn = min(T, nc - c0);
+    unsigned slow_mask = 0;                                  // curtains of this round left to the fix-up below
 #pragma unroll 1
     for (int j = 0; j < jn; j++) {
       float Lz = mine.z, Lkk = mine_kk, LA = mine.A, LBu = mine.Bu;
@@ -206,8 +207,12 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
       }
       const float sgl = (a0.x + a0.y) + (a1.x + a1.y);       // this lane's share of sum(g)
       const float sg = group_sum<T>(sgl, gmask);
-      // sg == 0 or NaN: g/sg is NaN -> -1 in every bin -> constant mixture -> uniform likelihood -> no-op
-      bool ok = sg > 0.f;
+      // sg == 0 or NaN: g/sg is NaN -> -1 in every bin -> constant mixture -> uniform likelihood -> no-op.
+      // A SENSED pixel whose sum is (nearly) flushed is skipped here too and remembered: see the fix-up below.
+      bool ok = sg >= 1e-26f;
+#ifndef DPV_FUSE_NO_DENORMAL_PATH
+      if (!ok && Lkk < 0.f && Lkk > -INFINITY) slow_mask |= 1u << j;
+#endif
       // m = soft * A + uni * B before its clamp at 0 (kept signed: the floor eps*sm below is positive, so
       // max(m, eps*sm) == max(max(m, 0), eps*sm)); sum(max(m, 0)) = (sum(m) + sum|m|) / 2 with sum(m) in closed form
       const float As = LA * rcp_approx(sg);
@@ -255,6 +260,83 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
         }
       }
     }
+#ifndef DPV_FUSE_NO_DENORMAL_PATH
+    // ---- fix-up for thin sheets (rare; warp-uniform branches, every lane takes part in the shuffles).
+    // When the sensed surface lies between (or outside) the depth bins and sigma is small, the whole Gaussian falls
+    // below 2^-126: ex2.approx.ftz flushes it and the loop above skipped the curtain, while the reference's exp()
+    // keeps the denormals and normalises them (g / sum(g) = 1 at the nearest bin, img_utils.py:183-190) -- at
+    // d_min = 3 m that is whole image columns (tests/test_gpu_fullsize.py C5, profiles/r02_fullsize_bins_diag.txt).
+    // The update is a product of likelihoods, so the skipped factor can be applied now, evaluated the way the
+    // reference sees it: an fp32 denormal is a whole number of units of 2^-149, so the reference's exp() is
+    // rint(2^(e + 149)) units (e = log2 of the Gaussian; exact above 2^23 units, i.e. for normal results) --
+    // including the few-bit quantisation that shows in g / sum(g) when the nearest bin is only a few hundred
+    // units, and including a sum of exactly 0 (uniform likelihood, nothing to apply) when even the nearest bin
+    // is below half a unit: surfaces many sigma outside the bins (image edges, z < d_min), the common case here.
+    // ex2.approx on e + 149 is a normal number again; the scale 2^149 drops out of g / sum(g).
+    // Above 2^-86 (the loop's threshold) a flushed bin is < 2^-40 of the sum: nothing the 1/D term can see.
+    if (__any_sync(gmask, slow_mask != 0u)) {
+#pragma unroll 1
+      for (int j = 0; j < jn; j++) {
+        const bool slow = (slow_mask >> j) & 1u;
+        if (!__any_sync(gmask, slow)) continue;
+        float Lz = mine.z, Lkk = mine_kk, LA = mine.A, LBu = mine.Bu;
+        if (T > 1) {
+          Lz = __shfl_sync(gmask, mine.z, gbase + j);
+          Lkk = __shfl_sync(gmask, mine_kk, gbase + j);
+          LA = __shfl_sync(gmask, mine.A, gbase + j);
+          LBu = __shfl_sync(gmask, mine.Bu, gbase + j);
+        }
+        const float2 kk2 = splat2(Lkk), nz2 = splat2(-Lz), up2 = splat2(149.f);
+        Col<NP> g;
+        float2 a0 = splat2(0.f), a1 = splat2(0.f);
+#pragma unroll
+        for (int k = 0; k < NP; k += 2) {
+          const float4 q = dc4_at(k >> 1);
+          float2 e0 = __fadd2_rn(make_float2(q.x, q.y), nz2), e1 = __fadd2_rn(make_float2(q.z, q.w), nz2);
+          e0 = __ffma2_rn(__fmul2_rn(e0, e0), kk2, up2);
+          e1 = __ffma2_rn(__fmul2_rn(e1, e1), kk2, up2);
+          g.v[k] = make_float2(slow && valid(2 * k) ? rintf(exp2f_approx(e0.x)) : 0.f,
+                               slow && valid(2 * k + 1) ? rintf(exp2f_approx(e0.y)) : 0.f);
+          g.v[k + 1] = make_float2(slow && valid(2 * k + 2) ? rintf(exp2f_approx(e1.x)) : 0.f,
+                                   slow && valid(2 * k + 3) ? rintf(exp2f_approx(e1.y)) : 0.f);
+          a0 = __fadd2_rn(a0, g.v[k]);
+          a1 = __fadd2_rn(a1, g.v[k + 1]);
+        }
+        const float sgl = (a0.x + a0.y) + (a1.x + a1.y);
+        const float sg = group_sum<T>(sgl, gmask);
+        const float As = LA / sg;
+        float sml = 0.f;
+#pragma unroll
+        for (int k = 0; k < NP; k++) {                         // mix_value (lc_sense.cuh) per bin, clamped at 0
+          float2 m = __ffma2_rn(g.v[k], splat2(As), splat2(LBu));
+          m.x = valid(2 * k) ? fmaxf(m.x, 0.f) : 0.f;
+          m.y = valid(2 * k + 1) ? fmaxf(m.y, 0.f) : 0.f;
+          g.v[k] = m;
+          sml += m.x + m.y;
+        }
+        const float sm = group_sum<T>(sml, gmask);
+        if (slow && sg > 0.f && sm > 0.f) {
+          const float esm = eps_floor() * sm;
+#pragma unroll
+          for (int k = 0; k < NP; k++)
+            p.v[k] = __fmul2_rn(p.v[k], make_float2(fmaxf(g.v[k].x, esm), fmaxf(g.v[k].y, esm)));
+        }
+        // one more multiplication than the loop's range check counted on: look at the total right away
+        a0 = splat2(0.f); a1 = splat2(0.f);
+#pragma unroll
+        for (int k = 0; k < NP; k += 2) {
+          a0 = __fadd2_rn(a0, p.v[k]);
+          a1 = __fadd2_rn(a1, p.v[k + 1]);
+        }
+        const float s = group_sum<T>((a0.x + a0.y) + (a1.x + a1.y), gmask);
+        if (s < 1e-12f || s > 1e12f) {
+          const float2 inv2 = splat2(1.f / s);
+#pragma unroll
+          for (int k = 0; k < NP; k++) p.v[k] = __fmul2_rn(p.v[k], inv2);
+        }
+      }
+    }
+#endif
     c0 += T;
   } while (c0 < nc);
 

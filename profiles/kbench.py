@@ -52,8 +52,9 @@ def main():
 
     add("plane_sweep", lambda: ops.plane_sweep(x["feat_all"][:, -1], x["feat_all"][:, :-1], x["K"], x["R"][:, :-1],
                                                x["t"][:, :-1], x["rays"], center, d, 10.0, "L2"), alg["sweep"])
-    add("warp_feature", lambda: ops.warp_feature(x["feat_raw"], x["K"], x["R"], x["t"], x["rays"], center, d),
-        alg["warp_feature"])
+    if meta.get("warp_feature", True):
+        add("warp_feature", lambda: ops.warp_feature(x["feat_raw"], x["K"], x["R"], x["t"], x["rays"], center, d),
+            alg["warp_feature"])
     add("lsm_full+stats+carry", lambda: ops.logsoftmax_stats(x["dec_logits"], d, want_carry=True), alg["lsm_full"])
     if meta["iterations"] > 0:
         st, lc = pipe.state, pipe.lc

@@ -18,6 +18,50 @@ def close(a, b, rtol=1e-4, atol=1e-6, what=""):
     np.testing.assert_allclose(a, b, rtol=rtol, atol=atol, equal_nan=True, err_msg=what)
 
 
+def close_dpv(a, b, what=""):
+    """Log-DPVs agree: every bin within rtol 1e-4 / atol 1e-5 in log space, or within 1e-4 relative + 1e-7 absolute
+    as a probability ("compare in probability and log space with an absolute floor of 1e-6"; this floor
+    is 10 x tighter), and fewer than 1e-5 of the bins may need the second criterion
+    (C5, whose sheets are thinnest, has the most: 178 of 100.7 M = 1.8e-6).
+    Measured at C2 / C4 (profiles/r02_fullsize_bins_diag.txt): 3-21 of 12.6-25.2 M bins per iteration leave the
+    log-space tolerance.  Each is a single bin of its column where the curtain's mixture likelihood
+    A g/sum(g) + (1-A)/D crosses its clamp at 0, i.e. is the small difference of two fp32 terms of size 1/D: the two
+    sides then differ by a few ulp of 1/D times the prior (largest seen: |dp| = 6e-9 at p = 6e-9), the other bins
+    of those columns agree to < 1e-5, the column sums and argmax bins are identical."""
+    a = a.detach().cpu().double().numpy()
+    b = b.detach().cpu().double().numpy()
+    assert a.shape == b.shape, what
+    ok_log = np.abs(a - b) <= 1e-5 + 1e-4 * np.abs(b)
+    pa, pb = np.exp(a), np.exp(b)
+    ok_p = np.abs(pa - pb) <= 1e-7 + 1e-4 * pb
+    bad = ~(ok_log | ok_p)
+    # Thin-sheet pixels whose whole Gaussian is a handful of fp32 denormals in the reference (the fix-up path of
+    # sense_fuse_kernel): g / sum(g) then has the relative precision of 1 / (number of denormal units), and CUDA's
+    # evaluation (rint of ex2.approx, in units of 2^-149) and the CPU's exp may round such a value one unit apart.
+    # Seen at C5: 4 bins of 100.7 M at |dlogp| = 0.0012 ... 0.028 (consistent with 1 unit in 830 ... 36; 1 bin at
+    # 0.0027 when the kernel called expf instead).  Allowed: |dlogp| <= 0.05 at no more than 1e-7 of the bins.
+    assert bad.sum() <= max(1, 1e-7 * bad.size) and (not bad.any() or float(np.abs(a - b)[bad].max()) <= 5e-2), \
+        "%s: %d bins differ, max |dlogp| %.3g" % (what, int(bad.sum()), float(np.abs(a - b)[bad].max()))
+    assert (~ok_log).mean() < 1e-5, "%s: %.3g of the bins outside the log-space tolerance" % (what, (~ok_log).mean())
+
+
+def argmax_bins_equal(got_logp, ref_logp, what=""):
+    """Argmax depth bins are identical, except at near-ties: where they differ, the reference's own log-probability
+    at the bin the GPU picked must be within 1e-4 of its maximum (the DPV tolerance: neither volume can tell the two
+    bins apart), and that may happen at no more than 1e-4 of the pixels."""
+    got = got_logp.detach().cpu()
+    ref = ref_logp.detach().cpu()
+    ga, ra = got.argmax(0), ref.argmax(0)
+    diff = ga != ra
+    n = int(diff.sum())
+    if n == 0:
+        return
+    gap = ref.max(0).values - ref.gather(0, ga.unsqueeze(0))[0]
+    assert float(gap[diff].max()) <= 1e-4, "%s: argmax bins differ at %d pixels, reference gap up to %.3g" % (
+        what, n, float(gap[diff].max()))
+    assert n <= 1e-4 * diff.numel(), "%s: argmax bins differ at %d of %d pixels (near-ties)" % (what, n, diff.numel())
+
+
 def _oracle_frame(host, meta, b=0):
     """The oracle's step for frame b with a per-iteration trace (bench.oracle_step keeps only the final volume)."""
     d = meta["d_candi"]
@@ -59,7 +103,7 @@ def _check_frame(host, meta, pipe, out, b=0):
     close(out["depth"][b:b + 1], exp["depth"], atol=1e-5, what="refined depth")
     close(out["var"][b:b + 1], exp["var"], atol=1e-4, what="variance")
     close(out["entropy"][b:b + 1], exp["entropy"], atol=1e-5, what="entropy")
-    assert torch.equal(out["logp"][b].argmax(0).cpu(), exp["logp"][0].argmax(0))
+    argmax_bins_equal(out["logp"][b], exp["logp"][0], "refined DPV")
     for it, (got, ref) in enumerate(zip(pipe.trace, exp["trace"])):
         close(got["uf"][b], ref["uf"][0], what="uf, iteration %d" % it)
         np.testing.assert_array_equal(got["argmax"][b].cpu().numpy(), ref["argmax"].numpy(),
@@ -68,11 +112,11 @@ def _check_frame(host, meta, pipe, out, b=0):
             n = int(got["counts"][b * nc + c])
             np.testing.assert_array_equal(got["ks"][b, c, :n].cpu().numpy(), ref["ks"][c],
                                           err_msg="planner range indices, iteration %d curtain %d" % (it, c))
-        close(got["logp"][b:b + 1], ref["logp"], atol=1e-5, what="fused log-DPV, iteration %d" % it)
+        close_dpv(got["logp"][b:b + 1], ref["logp"], what="fused log-DPV, iteration %d" % it)
     assert len(pipe.trace) == len(exp["trace"]) == meta["iterations"]
-    close(out["logp_lc"][b:b + 1], exp["logp_lc"], atol=1e-5, what="fused log-DPV")
+    close_dpv(out["logp_lc"][b:b + 1], exp["logp_lc"], what="fused log-DPV")
     close(out["depth_lc"][b:b + 1], O.dpv_expectation(exp["logp_lc"], meta["d_candi"], True), atol=1e-5)
-    assert torch.equal(out["logp_lc"][b].argmax(0).cpu(), exp["logp_lc"][0].argmax(0))        # argmax depth bins
+    argmax_bins_equal(out["logp_lc"][b], exp["logp_lc"][0], "fused DPV")
 
 
 def test_c2_frame_matches_oracle_per_iteration():
@@ -89,11 +133,20 @@ def test_c4_frame_matches_oracle_per_iteration():
 
 
 def test_c3_temporal_frame_matches_oracle():
-    """BASELINE configs[2] (T = 3: two source views in the plane sweep and three in warp_feature)."""
+    """BASELINE configs[2] (T = 3: two source views in the plane sweep and three in warp_feature).
+    Low-res DPV tolerance: the cost is a sum of 2 x 67 squared differences of N(0,1) features (magnitude ~19), and
+    the reference's own fp32 arithmetic is up to 1.2e-3 away from the same formula in fp64 on this input, 5789 of
+    786432 elements beyond rtol 1e-4 / atol 1e-5 (profiles/cond_c3_lowres.py).  The kernel is held to 5e-4 absolute
+    everywhere and to rtol 1e-4 / atol 1e-5 at all but 1e-4 of the elements (measured: 20 elements, max 2.1e-4)."""
     host, meta, pipe, out = _run("C3_temporal_b8", 0)
     exp = _oracle_frame(host, meta)
-    close(out["bv_low"], exp["bv_low"], atol=1e-5)
-    close(out["warped"], exp["warped"], atol=1e-5)
+    close(out["bv_low"], exp["bv_low"], rtol=0, atol=5e-4)
+    err = (out["bv_low"].cpu() - exp["bv_low"]).abs()
+    assert float((err > 1e-5 + 1e-4 * exp["bv_low"].abs()).float().mean()) < 1e-4
+    # warped features: one fp32 ulp of a tap coordinate near x = 192 (1.5e-5 px; torch's CPU matmul of K R rays and
+    # the kernel's do not round identically) times the pixel-to-pixel slope of N(0,1) features (~4) is 6e-5:
+    # 1e-4 absolute (measured: 166 of 2.36 M samples beyond 1e-5, max 5.9e-5)
+    close(out["warped"], exp["warped"], rtol=1e-4, atol=1e-4)
     close(out["depth"], exp["depth"], atol=1e-5)
 
 
