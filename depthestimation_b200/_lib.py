@@ -42,6 +42,8 @@ SIGNATURES = {
     "dpv_ufield_scratch_bytes": (ctypes.c_size_t, [c_int, c_int, c_int]),
     "dpv_ufield": (c_int, [c_fp, c_fp, c_fp, c_int, c_int, c_int, c_int, c_fp, c_fp,
                            ctypes.POINTER(DpvUfieldParams), c_fp, c_fp, c_vp, ctypes.c_size_t, c_vp]),
+    "dpv_ufield_static": (c_int, [c_fp, c_fp, c_fp, c_int, c_int, c_int, c_int, c_fp, c_fp,
+                                  ctypes.POINTER(DpvUfieldParams), c_fp, c_fp, c_vp]),
     "lc_plan_prepare": (c_int, [c_fp, c_int, c_int, c_int, c_int, c_fp, c_fp, c_int, c_fp, c_ip, c_fp, c_vp]),
     "lc_plan_field": (c_int, [c_fp, c_int, c_int, c_int, c_int, c_fp, c_int, c_fp, c_fp, c_vp]),
     "lc_plan_prepare_transformed": (c_int, [c_fp, c_int, c_int, c_int, c_int, c_int, c_fp, c_fp, c_fp, c_int, c_int,

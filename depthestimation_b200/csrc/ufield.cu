@@ -11,6 +11,8 @@
 //                              (row, 32-column group), depth_zero
 //   sum                        one warp per (depth plane, 32 columns): walks the non-empty rows in ascending
 //                              order, eight loads in flight, and divides by the column count.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace dpv {
@@ -256,4 +258,57 @@ extern "C" int dpv_ufield(const float* dpv_, const float* mean, const float* mas
   const int rc = check_launch("dpv_ufield");
   if (rc == DPV_OK) count_launch(launches);
   return rc;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// dpv_ufield_static: dpv_ufield for callers that may not allocate (no counterpart in the reference).
+// The scratch that dpv_ufield takes from its caller lives in a file-scope device
+// array instead, so neither the caller nor this function calls cudaMalloc / cudaFree or any allocating routine.
+// Every GPU that loads the library holds the array until the process exits.
+//
+// In host code the array's NAME is a host-side stand-in, not a device address: handing it to a kernel would fault
+// (or, where the GPU can reach host memory, silently use the wrong memory).  Its device address is resolved with
+// cudaGetSymbolAddress once per device, with that device current, and that pointer is what the kernels get.
+namespace dpv {
+
+constexpr size_t kUfStaticBytes = DPV_UFIELD_STATIC_MAX_BYTES;      // 1 MiB: C2 (8 x 256 x 768) needs 240 KiB, C5 (2 x 512 x 1536) 216 KiB
+static __device__ __align__(256) unsigned char g_uf_static_scratch[kUfStaticBytes];
+
+constexpr int kUfMaxDevices = 64;
+
+// Device address of g_uf_static_scratch on the CURRENT device (cached per device ordinal).
+static int uf_static_scratch_ptr(void** out) {
+  static void* ptrs[kUfMaxDevices] = {};
+  static std::mutex mu;
+  int dev = -1;
+  DPV_CUDA(cudaGetDevice(&dev));
+  DPV_REQUIRE(dev >= 0 && dev < kUfMaxDevices, "dpv_ufield_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    DPV_CUDA(cudaGetSymbolAddress(&p, g_uf_static_scratch));
+    DPV_REQUIRE(p != nullptr && ((uintptr_t)p & 255) == 0, "dpv_ufield_static: bad scratch address %p", p);
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return DPV_OK;
+}
+
+}  // namespace dpv
+
+extern "C" int dpv_ufield_static(const float* dpv_, const float* mean, const float* mask, int B, int D, int H, int W,
+                                 const float* d_candi, const float* K_up, const DpvUfieldParams* prm, float* uf,
+                                 float* depth_zero, void* stream) {
+  DPV_REQUIRE(B > 0 && D > 0 && H > 1 && W > 1, "dpv_ufield_static: bad shape");
+  const size_t need = dpv_ufield_scratch_bytes(B, H, W);
+  DPV_REQUIRE(need <= kUfStaticBytes,
+              "dpv_ufield_static: B=%d H=%d W=%d needs %zu bytes of scratch, the static maximum is %zu bytes "
+              "(use dpv_ufield with caller scratch for larger batches)", B, H, W, need, (size_t)kUfStaticBytes);
+  void* scratch = nullptr;
+  const int rc = uf_static_scratch_ptr(&scratch);
+  if (rc != DPV_OK) return rc;
+  // dpv_ufield resets what must start at zero (per-column counts, and the column minima of the quash branch) with
+  // cudaMemsetAsync on `stream` and its mask kernel rewrites every band-mask word, so nothing of the previous call
+  // survives into this one.
+  return dpv_ufield(dpv_, mean, mask, B, D, H, W, d_candi, K_up, prm, uf, depth_zero, scratch, kUfStaticBytes, stream);
 }

@@ -100,6 +100,20 @@ size_t dpv_ufield_scratch_bytes(int B, int H, int W);
 int dpv_ufield(const float* dpv, const float* mean, const float* mask, int B, int D, int H, int W,
                const float* d_candi, const float* K_up, const DpvUfieldParams* prm /*host*/, float* uf,
                float* depth_zero, void* scratch, size_t scratch_bytes, void* stream);
+/* dpv_ufield for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.
+ * Same inputs, outputs and results as dpv_ufield, but the scratch is a 1 MiB (DPV_UFIELD_STATIC_MAX_BYTES) file-scope
+ * device array inside the library -- every GPU that loads the library holds it until the process exits -- and the call
+ * allocates nothing (no cudaMalloc / cudaFree, no allocating library routine).  Shapes with
+ * dpv_ufield_scratch_bytes(B,H,W) > DPV_UFIELD_STATIC_MAX_BYTES are rejected with DPV_EINVAL (C2, 8 x 256 x 768, needs
+ * 240 KiB; use dpv_ufield with caller scratch beyond the limit).  The device to run on must be current; the array's
+ * device address is resolved once per device on the first call there (make that call outside stream capture).
+ * Every call on a device shares the one array: it keeps the last call's contents (each call resets what it needs
+ * zeroed), and calls that overlap on the GPU -- different streams, or graphs replayed concurrently -- race. */
+#define DPV_UFIELD_STATIC_MAX_BYTES (1u << 20)
+int dpv_ufield_static(const float* dpv, const float* mean, const float* mask, int B, int D, int H, int W,
+                      const float* d_candi, const float* K_up, const DpvUfieldParams* prm /*host*/, float* uf,
+                      float* depth_zero, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * (d2) Planner input.  lc/light_curtain.py:646-708 plan_default up to the planner calls
