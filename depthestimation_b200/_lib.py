@@ -66,11 +66,14 @@ SIGNATURES = {
     "lc_transform_points_scratch_bytes": (ctypes.c_size_t, [c_int, c_int, c_int, c_int]),
     "lc_transform_points": (c_int, [c_fp, c_fp, c_int, c_int, c_fp, c_fp, c_int, c_int, c_int, c_fp, c_vp,
                                     ctypes.c_size_t, c_vp]),
+    "lc_depth_to_points": (c_int, [c_fp, c_int, c_int, c_int, c_fp, c_f, c_fp, c_vp]),
     "lc_likelihood_maps": (c_int, [c_fp, c_fp, c_int, c_int, c_int, c_int, c_fp, c_int, c_fp, c_vp]),
     "lc_sweep_sample": (c_int, [c_fp, c_fp, c_fp, c_int, c_int, c_int, c_int, c_int, c_fp, c_ip, c_vp]),
     "dpv_truth_dpv": (c_int, [c_fp, c_fp, c_int, c_int, c_int, c_fp, c_int, c_f, c_fp, c_vp]),
     "lc_likelihood_true": (c_int, [c_fp, c_fp, c_fp, c_fp, c_f, c_f, c_ll, c_fp, c_int, c_fp, c_fp, c_vp]),
     "dpv_inverse_warp": (c_int, [c_fp, c_fp, c_fp, c_fp, c_int, c_int, c_int, c_int, c_int, c_int, c_fp, c_vp, c_vp]),
+    "dpv_inverse_warp_backward": (c_int, [c_fp, c_fp, c_fp, c_fp, c_fp, c_int, c_int, c_int, c_int, c_int, c_int, c_fp,
+                                          c_fp, c_fp, c_vp]),
     "dpv_correlation_shape": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_int, ctypes.POINTER(c_int),
                                       ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
     "dpv_correlation": (c_int, [c_fp, c_fp, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_fp, c_vp]),

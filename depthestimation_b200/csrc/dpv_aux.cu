@@ -101,6 +101,148 @@ __device__ __forceinline__ float reflect_coord(float x, float lo2, float hi2) { 
   return (flips % 2 == 0) ? extra + mn : span - extra + mn;
 }
 
+// ATen clip_coordinates_set_grad / reflect_coordinates_set_grad: the coordinate after padding and d(out)/d(in)
+__device__ __forceinline__ float clip_coord_grad(float x, int size, float* mult) {
+  if (x <= 0.f) { *mult = 0.f; return 0.f; }
+  const float mx = (float)(size - 1);
+  if (x >= mx) { *mult = 0.f; return mx; }
+  *mult = 1.f;
+  return x;
+}
+__device__ __forceinline__ float reflect_coord_grad(float x, float lo2, float hi2, float* mult) {
+  if (lo2 == hi2) { *mult = 0.f; return 0.f; }
+  const float mn = lo2 / 2.f, span = (hi2 - lo2) / 2.f;
+  x = x - mn;
+  float m = 1.f;
+  if (x < 0.f) { m = -1.f; x = -x; }
+  const float extra = fmodf(x, span);
+  const int flips = (int)floorf(x / span);
+  if (flips % 2 == 0) { *mult = m; return extra + mn; }
+  *mult = -m;
+  return span - extra + mn;
+}
+
+// Backward of inverse_warp_kernel (what torch autograd derives for utils/inverse_warp.py:174-210 in the reference:
+// grid_sample backward -> cam2pixel :43-69 -> pixel2cam :26-40).  One thread per output pixel: scatters the image
+// gradient to its taps, chains the grid gradient through the projection to the depth, and reduces the gradient of
+// the 3x4 projection matrix over the warp before one atomicAdd per entry.
+__global__ void inverse_warp_backward_kernel(const float* __restrict__ gout, const float* __restrict__ img,
+                                             const float* __restrict__ depth, const float* __restrict__ Kinv,
+                                             const float* __restrict__ P, int B, int C, int H, int W, int mode,
+                                             int padding, float* __restrict__ gimg, float* __restrict__ gdepth,
+                                             float* __restrict__ gP) {
+  const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long npix = (long long)B * H * W;
+  const bool active = pix < npix;
+  const size_t HW = (size_t)H * W;
+  const int b = active ? (int)(pix / (long long)HW) : B - 1;
+  float gp[12];
+#pragma unroll
+  for (int k = 0; k < 12; k++) gp[k] = 0.f;
+  if (active) {
+    const size_t hw = (size_t)(pix - (long long)b * HW);
+    const int y = (int)(hw / W), x = (int)(hw % W);
+    const float* ki = Kinv + b * 9;
+    const float* p = P + b * 12;
+    const float dz = depth[pix];
+    const float fx = (float)x, fy = (float)y;
+    const float kx = ki[0] * fx + ki[1] * fy + ki[2], ky = ki[3] * fx + ki[4] * fy + ki[5],
+                kz = ki[6] * fx + ki[7] * fy + ki[8];
+    const float cx = kx * dz, cy = ky * dz, cz = kz * dz;
+    const float X = (p[0] * cx + p[1] * cy + p[2] * cz) + p[3];
+    const float Y = (p[4] * cx + p[5] * cy + p[6] * cz) + p[7];
+    const float Zraw = (p[8] * cx + p[9] * cy + p[10] * cz) + p[11];
+    const float Z = fmaxf(Zraw, 1e-3f);
+    const float gx = 2.f * (X / Z) / (float)(W - 1) - 1.f, gy = 2.f * (Y / Z) / (float)(H - 1) - 1.f;
+    float ix = gs_unnormalize(gx, W), iy = gs_unnormalize(gy, H);
+    float mx = 1.f, my = 1.f;                                   // d(ix after padding) / d(ix)
+    if (padding == 1) {
+      ix = clip_coord_grad(ix, W, &mx);
+      iy = clip_coord_grad(iy, H, &my);
+    } else if (padding == 2) {
+      float m1, m2;
+      ix = clip_coord_grad(reflect_coord_grad(ix, -1.f, 2.f * W - 1.f, &m1), W, &m2);
+      mx = m1 * m2;
+      iy = clip_coord_grad(reflect_coord_grad(iy, -1.f, 2.f * H - 1.f, &m1), H, &m2);
+      my = m1 * m2;
+    }
+    mx *= (float)W / 2.f;                                       // un-normalisation, align_corners=False
+    my *= (float)H / 2.f;
+    const float* src = img + (size_t)b * C * HW;
+    float* gsrc = gimg ? gimg + (size_t)b * C * HW : nullptr;
+    const float* go = gout + (size_t)b * C * HW + hw;
+    const bool finite = (ix == ix) && (iy == iy) && fabsf(ix) < 1e9f && fabsf(iy) < 1e9f;
+    float gix = 0.f, giy = 0.f;
+    if (mode == 1) {                                            // nearest: no gradient to the grid
+      const float rx = nearbyintf(ix), ry = nearbyintf(iy);
+      if (finite && gsrc && rx >= 0.f && rx <= (float)(W - 1) && ry >= 0.f && ry <= (float)(H - 1)) {
+        const size_t o = (size_t)((int)ry) * W + (int)rx;
+        for (int c = 0; c < C; c++) atomicAdd(gsrc + (size_t)c * HW + o, go[(size_t)c * HW]);
+      }
+    } else if (finite) {
+      const float x0f = floorf(ix), y0f = floorf(iy);
+      const float tx = ix - x0f, ty = iy - y0f;
+      const int x0 = (int)x0f, y0 = (int)y0f;
+      const bool xin0 = x0 >= 0 && x0 < W, xin1 = x0 + 1 >= 0 && x0 + 1 < W;
+      const bool yin0 = y0 >= 0 && y0 < H, yin1 = y0 + 1 >= 0 && y0 + 1 < H;
+      const float wnw = (1.f - tx) * (1.f - ty), wne = tx * (1.f - ty), wsw = (1.f - tx) * ty, wse = tx * ty;
+      const size_t onw = (size_t)y0 * W + x0;
+      for (int c = 0; c < C; c++) {
+        const float g = go[(size_t)c * HW];
+        const float* s = src + (size_t)c * HW;
+        float* gs = gsrc ? gsrc + (size_t)c * HW : nullptr;
+        if (yin0 && xin0) {
+          const float v = s[onw];
+          gix -= v * (1.f - ty) * g; giy -= v * (1.f - tx) * g;
+          if (gs) atomicAdd(gs + onw, wnw * g);
+        }
+        if (yin0 && xin1) {
+          const float v = s[onw + 1];
+          gix += v * (1.f - ty) * g; giy -= v * tx * g;
+          if (gs) atomicAdd(gs + onw + 1, wne * g);
+        }
+        if (yin1 && xin0) {
+          const float v = s[onw + W];
+          gix -= v * ty * g; giy += v * (1.f - tx) * g;
+          if (gs) atomicAdd(gs + onw + W, wsw * g);
+        }
+        if (yin1 && xin1) {
+          const float v = s[onw + W + 1];
+          gix += v * ty * g; giy += v * tx * g;
+          if (gs) atomicAdd(gs + onw + W + 1, wse * g);
+        }
+      }
+    }
+    const float Ggx = mx * gix, Ggy = my * giy;                 // d loss / d (normalised grid)
+    const float sx = 2.f / (float)(W - 1), sy = 2.f / (float)(H - 1);
+    const float gX = Ggx * sx / Z, gY = Ggy * sy / Z;
+    const float gZ = Zraw >= 1e-3f ? -(Ggx * sx * X + Ggy * sy * Y) / (Z * Z) : 0.f;      // clamp(min=1e-3) backward
+    if (gdepth) {
+      const float gcx = p[0] * gX + p[4] * gY + p[8] * gZ, gcy = p[1] * gX + p[5] * gY + p[9] * gZ,
+                  gcz = p[2] * gX + p[6] * gY + p[10] * gZ;
+      gdepth[pix] = gcx * kx + gcy * ky + gcz * kz;
+    }
+    gp[0] = gX * cx; gp[1] = gX * cy; gp[2] = gX * cz; gp[3] = gX;
+    gp[4] = gY * cx; gp[5] = gY * cy; gp[6] = gY * cz; gp[7] = gY;
+    gp[8] = gZ * cx; gp[9] = gZ * cy; gp[10] = gZ * cz; gp[11] = gZ;
+  }
+  if (!gP) return;
+  const unsigned full = 0xffffffffu;
+  const int b0 = __shfl_sync(full, b, 0);
+  if (__all_sync(full, b == b0 || !active)) {                   // the usual case: the warp lies inside one image
+#pragma unroll
+    for (int k = 0; k < 12; k++) {
+      float v = gp[k];
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(full, v, off);
+      if ((threadIdx.x & 31) == 0 && v != 0.f) atomicAdd(gP + b0 * 12 + k, v);
+    }
+  } else if (active) {
+#pragma unroll
+    for (int k = 0; k < 12; k++) atomicAdd(gP + b * 12 + k, gp[k]);
+  }
+}
+
 // mode: 0 bilinear, 1 nearest; padding: 0 zeros, 1 border, 2 reflection
 __global__ void inverse_warp_kernel(const float* __restrict__ img, const float* __restrict__ depth,
                                     const float* __restrict__ Kinv, const float* __restrict__ P, int B, int C, int H,
@@ -359,6 +501,23 @@ int dpv_inverse_warp(const float* img, const float* depth, const float* Kinv, co
   inverse_warp_kernel<<<aux_blocks(npix), kAuxThreads, 0, (cudaStream_t)stream>>>(img, depth, Kinv, P, B, C, H, W,
                                                                                    mode, padding, out, valid);
   return check_launch("dpv_inverse_warp");
+}
+
+int dpv_inverse_warp_backward(const float* grad_out, const float* img, const float* depth, const float* Kinv,
+                              const float* P, int B, int C, int H, int W, int mode, int padding, float* grad_img,
+                              float* grad_depth, float* grad_P, void* stream) {
+  DPV_REQUIRE(grad_out && img && depth && Kinv && P, "dpv_inverse_warp_backward: null pointer");
+  DPV_REQUIRE(grad_img || grad_depth || grad_P, "dpv_inverse_warp_backward: no gradient requested");
+  DPV_REQUIRE(B > 0 && C > 0 && H > 1 && W > 1, "dpv_inverse_warp_backward: bad shape B=%d C=%d H=%d W=%d", B, C, H, W);
+  DPV_REQUIRE(mode == 0 || mode == 1, "dpv_inverse_warp_backward: mode %d (0 bilinear, 1 nearest)", mode);
+  DPV_REQUIRE(padding >= 0 && padding <= 2, "dpv_inverse_warp_backward: padding %d", padding);
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long npix = (long long)B * H * W;
+  if (grad_img) DPV_CUDA(cudaMemsetAsync(grad_img, 0, (size_t)npix * C * sizeof(float), st));     // scatter target
+  if (grad_P) DPV_CUDA(cudaMemsetAsync(grad_P, 0, (size_t)B * 12 * sizeof(float), st));
+  inverse_warp_backward_kernel<<<aux_blocks(npix), kAuxThreads, 0, st>>>(grad_out, img, depth, Kinv, P, B, C, H, W,
+                                                                         mode, padding, grad_img, grad_depth, grad_P);
+  return check_launch("dpv_inverse_warp_backward");
 }
 
 int dpv_correlation_shape(int H, int W, int pad_size, int kernel_size, int max_displacement, int stride1,

@@ -163,7 +163,31 @@ sweep_sample_kernel(const float* __restrict__ sdepth, const float* __restrict__ 
 
 using namespace dpv;
 
+// utils/img_utils.py:269-293 depth_to_pts, written straight into the [N,4] point layout transformPoints consumes
+// (lc/light_curtain.py:826-830 builds it with a cat and a transpose): ((u - cx) / fx * d, (v - cy) / fy * d, d, w).
+__global__ void __launch_bounds__(kRealThreads)
+depth_to_points_kernel(const float* __restrict__ depth, long long npix, int H, int W, float fx, float cx, float fy,
+                       float cy, float w4, float4* __restrict__ pts) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= npix) return;
+  const long long hw = i % ((long long)H * W);
+  const int v = (int)(hw / W), u = (int)(hw % W);
+  const float d = depth[i];
+  const float xf = __fdiv_rn(__fsub_rn((float)u, cx), fx), yf = __fdiv_rn(__fsub_rn((float)v, cy), fy);
+  pts[i] = make_float4(__fmul_rn(xf, d), __fmul_rn(yf, d), d, w4);
+}
+
 extern "C" {
+
+int lc_depth_to_points(const float* depth, int n, int H, int W, const float* intr, float w4, float* pts, void* stream) {
+  DPV_REQUIRE(depth && intr && pts, "lc_depth_to_points: null pointer");
+  DPV_REQUIRE(n > 0 && H > 0 && W > 0, "lc_depth_to_points: bad shape n=%d H=%d W=%d", n, H, W);
+  DPV_REQUIRE(((uintptr_t)pts & 15) == 0, "lc_depth_to_points: pts must be 16-byte aligned");
+  const long long npix = (long long)n * H * W;
+  depth_to_points_kernel<<<real_blocks(npix), kRealThreads, 0, (cudaStream_t)stream>>>(
+      depth, npix, H, W, intr[0], intr[2], intr[4], intr[5], w4, reinterpret_cast<float4*>(pts));
+  return check_launch("lc_depth_to_points");
+}
 
 size_t lc_transform_points_scratch_bytes(int n, int width, int height, int filtering) {
   const size_t px = (size_t)n * width * height;

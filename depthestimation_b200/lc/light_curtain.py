@@ -301,9 +301,8 @@ class LightCurtain:
         K_lc = np.asarray(P["intr_lc"], np.float32) if mode == "high" else intr_scale_unit(P["intr_lc"], sc)
         size_rgb = (int(P["size_rgb"][0] * sc), int(P["size_rgb"][1] * sc))
         depth = ops.f32(depth_rgb, self.device).reshape(size_rgb[1], size_rgb[0])
-        xyz = img_utils.depth_to_pts(depth.unsqueeze(0), K_rgb)                              # [3,H,W]
-        pts_rgb = torch.cat([xyz.reshape(3, -1), torch.ones(1, depth.numel(), device=self.device)]).t().contiguous()
-        depth_lc = lcsim.transform_points(pts_rgb.unsqueeze(0), torch.ones(1, depth.numel(), device=self.device),
+        pts_rgb = lcsim.depth_to_points(depth.unsqueeze(0), K_rgb)                           # [1,H*W,4], w = 1 (:826-830)
+        depth_lc = lcsim.transform_points(pts_rgb, torch.ones(1, depth.numel(), device=self.device),
                                           K_lc, P["cTr"], r.dev.W, r.dev.H, 2)[:, 0].contiguous()
         img, th = r.dev.sense_image(planes, depth_lc, 1, noise)
         dead = torch.isnan(img[..., 0])                                                      # :847-848

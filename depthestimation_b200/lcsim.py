@@ -48,6 +48,18 @@ def transform_points(pts, thick, intr, M, width, height, filtering=0):
     return maps
 
 
+def depth_to_points(depth, intr, w4=1.0):
+    """depth [n,H,W] (CUDA), intr [3,3] (host) -> pts [n,H*W,4] = ((u-cx)/fx*d, (v-cy)/fy*d, d, w4): img_utils.depth_to_pts
+    (utils/img_utils.py:269-293) in the layout transform_points takes (lc/light_curtain.py:826-830)."""
+    depth = f32(depth)
+    n, H, W = depth.shape
+    K = _host_f32(intr).reshape(3, 3)
+    pts = torch.empty(n, H * W, 4, device=depth.device, dtype=torch.float32)
+    with torch.cuda.device(depth.device):
+        check(lib().lc_depth_to_points(ptr(depth), n, H, W, _hp(K), float(w4), ptr(pts), stream_ptr(depth.device)))
+    return pts
+
+
 def transformPoints(pts, thick, intr, M, width, height, params):
     """pylc_lib.transformPoints (pylc_lib.cpp binding of depth.cpp:143-222): pts [N,4], thick [N] ->
     (depth, intensity, thickness) maps [height,width]; numpy in -> numpy out, CUDA tensors in -> CUDA tensors out."""

@@ -269,6 +269,22 @@ def inverse_warp(img, depth, Kinv, P, mode="bilinear", padding_mode="zeros"):
     return out, valid.bool()
 
 
+def inverse_warp_backward(grad_out, img, depth, Kinv, P, mode="bilinear", padding_mode="zeros", want=(True, True, True)):
+    """Gradients of ops.inverse_warp: grad_out [B,C,H,W] -> (grad_img | None, grad_depth | None, grad_P [B,3,4] | None)."""
+    go = f32(grad_out)
+    dev = go.device
+    im, dp, ki, pm = f32(img, dev), f32(depth, dev), f32(Kinv, dev), f32(P, dev)
+    B, C, H, W = im.shape
+    g_img = torch.empty_like(im) if want[0] else None
+    g_depth = torch.empty_like(dp) if want[1] else None
+    g_P = torch.empty(B, 3, 4, device=dev, dtype=torch.float32) if want[2] else None
+    with torch.cuda.device(_dev(im)):
+        check(lib().dpv_inverse_warp_backward(ptr(go), ptr(im), ptr(dp), ptr(ki), ptr(pm), B, C, H, W, _WARP_MODES[mode],
+                                              _WARP_PADDING[padding_mode], ptr(g_img), ptr(g_depth), ptr(g_P),
+                                              stream_ptr(dev)))
+    return g_img, g_depth, g_P
+
+
 def correlation(x1, x2, pad_size, kernel_size, max_displacement, stride1, stride2):
     """x1, x2 [B,C,H,W] -> [B,(2*(max_displacement//stride2)+1)^2,outH,outW]."""
     a = f32(x1)

@@ -14,11 +14,9 @@ UF_MODES = {                                                         # img_utils
 }
 
 
-def powerf(d_min, d_max, nDepth, power):                             # img_utils.py:238-243
-    f = lambda x: d_min + (d_max - d_min) * x
-    x = np.linspace(start=0, stop=1, num=nDepth)
-    x = np.power(x, power)
-    return np.array([f(v) for v in x])
+def powerf(d_min, d_max, nDepth, power):
+    """Depth candidates d_min + (d_max - d_min) * linspace(0, 1, nDepth) ** power as float64 (img_utils.py:238-243)."""
+    return d_min + (d_max - d_min) * np.linspace(0.0, 1.0, int(nDepth)) ** power
 
 
 def uf_params(cfg=None, cfgx=None):
@@ -63,20 +61,15 @@ def gen_ufield(dpv_predicted, d_candi, intr_up, visualizer=None, img=None, BV_lo
     return uf, dz
 
 
-def depth_to_pts(depthf, intr):                                      # img_utils.py:269-293
-    """depthf [1,H,W] (CUDA) -> point cloud [3,H,W] = ((u - cx) / fx * d, (v - cy) / fy * d, d); the reference's own
-    elementwise torch expressions, evaluated on the GPU."""
+def depth_to_pts(depthf, intr):
+    """depthf [1,H,W] (CUDA) -> point cloud [3,H,W] = ((u - cx) / fx * d, (v - cy) / fy * d, d) (img_utils.py:269-293),
+    one kernel (lc_depth_to_points); the reference refuses a batch, so does this."""
     if depthf.shape[0] != 1:
         raise Exception('Unable to handle this case')
-    depth = depthf[0, :, :]
-    intr = np.asarray(intr.cpu() if torch.is_tensor(intr) else intr, dtype=np.float32)
-    fx, cx, fy, cy = intr[0, 0], intr[0, 2], intr[1, 1], intr[1, 2]
-    yfield, xfield = torch.meshgrid([torch.arange(0, depth.shape[0]).float().to(depthf.device),
-                                     torch.arange(0, depth.shape[1]).float().to(depthf.device)], indexing="ij")
-    yfield = (yfield - float(cy)) / float(fy)
-    xfield = (xfield - float(cx)) / float(fx)
-    return torch.cat([torch.mul(xfield, depth).unsqueeze(0), torch.mul(yfield, depth).unsqueeze(0),
-                      depth.unsqueeze(0)], 0)
+    from .. import lcsim
+    H, W = depthf.shape[1:]
+    K = np.asarray(intr.cpu() if torch.is_tensor(intr) else intr, dtype=np.float32)
+    return lcsim.depth_to_points(depthf, K)[0, :, :3].t().reshape(3, H, W)
 
 
 def gen_dpv_withmask(dmaps, masks, d_candi, var=0.3):                # img_utils.py:567-582

@@ -217,6 +217,10 @@ size_t lc_transform_points_scratch_bytes(int n, int width, int height, int filte
 int lc_transform_points(const float* pts, const float* thick, int n, int N, const float* intr, const float* M,
                         int width, int height, int filtering, float* maps, void* scratch, size_t scratch_bytes,
                         void* stream);
+/* img_utils.depth_to_pts (utils/img_utils.py:269-293) in the point layout lc_transform_points takes
+ * (lc/light_curtain.py:826-830 concatenates a row of ones and transposes): depth [n,H,W], intr host[3x3]
+ *   -> pts [n,H*W,4] = ((u - cx) / fx * d, (v - cy) / fy * d, d, w4). */
+int lc_depth_to_points(const float* depth, int n, int H, int W, const float* intr, float w4, float* pts, void* stream);
 /* The tail of sense_high / sense_low (lc/light_curtain.py:869-888) for a sensor whose returns had to be re-projected
  * (rTc != I, :850-858): maps [B*nc,3,H,W] = lc_transform_points output in the RGB camera, depth [B,H,W] (the
  * ground-truth depth whose > 0 mask gates the pixel)  ->  lik [B*nc,D,H,W], the same mixture as lc_sense_likelihood. */
@@ -247,6 +251,14 @@ int lc_likelihood_true(const float* placement, const float* intensity, const flo
  * 2 reflection. */
 int dpv_inverse_warp(const float* img, const float* depth, const float* Kinv, const float* P, int B, int C, int H,
                      int W, int mode, int padding, float* out, uint8_t* valid, void* stream);
+/* Backward of dpv_inverse_warp: what torch autograd derives in the reference, where inverse_warp is only ever called
+ * under autograd (losses/loss_blocks.py:116,135,168-170): grid_sample backward -> cam2pixel :43-69 -> pixel2cam :26-40.
+ * grad_out [B,C,H,W] -> grad_img [B,C,H,W], grad_depth [B,H,W], grad_P [B,3,4] (each nullable; grad_img and grad_P are
+ * cleared first, then accumulated with atomics).  The gradient w.r.t. the pose vector / 4x4 follows from grad_P through
+ * the small pose algebra the caller keeps in torch. */
+int dpv_inverse_warp_backward(const float* grad_out, const float* img, const float* depth, const float* Kinv,
+                              const float* P, int B, int C, int H, int W, int mode, int padding, float* grad_img,
+                              float* grad_depth, float* grad_P, void* stream);
 /* models/correlation_package (correlation_cuda.cc:21-38 shapes, correlation_cuda_kernel.cu:44-112 forward):
  * out[b, (tj,ti), y, x] = mean over the kernel window and channels of pad(in1)[.., y1+j, x1+i] * pad(in2)[.., y2+j, x2+i],
  * x1 = x*stride1 + max_displacement, x2 = x1 + ti*stride2.  in1, in2 [B,C,H,W] -> out [B,outC,outH,outW]. */

@@ -371,6 +371,43 @@ def case_aux():
          true_d=me.d_candi, true_sensed=sensed, true_peak_img=peak, true_dpv_const=true_const, true_dpv_peak=true_peak)
 
 
+def case_inverse_warp_backward():
+    """Row a18 under autograd, the only way the reference calls it (losses/loss_blocks.py:116,135,168-170): gradients
+    of sum(inverse_warp(...) * gout) w.r.t. img, depth and pose from the unmodified reference -> inverse_warp_bwd.npz."""
+    iw = ref_shim.load_inverse_warp()
+    g = torch.Generator().manual_seed(17)
+    B, C, H, W = 2, 3, 20, 28
+    img = torch.randn(B, C, H, W, generator=g)
+    depth = 4.0 + 6.0 * torch.rand(B, H, W, generator=g)
+    gout = torch.randn(B, C, H, W, generator=g)
+    K, _ = intrinsics(W, H, hfov=60.0, vfov=45.0)
+    Kb = torch.tensor(K).unsqueeze(0).repeat(B, 1, 1)
+    pose6 = torch.tensor([[0.30, -0.10, 0.20, 0.02, -0.03, 0.01], [-0.40, 0.05, -0.30, -0.01, 0.04, 0.03]])
+    # a pose that throws a good part of the image out of view: border / reflection padding and the Z clamp are active
+    pose_far = torch.tensor([[2.5, -0.6, -3.0, 0.10, -0.25, 0.05], [-1.5, 0.8, -5.5, -0.05, 0.30, -0.10]])
+    # a pose that leaves the image by a few widths with Z >= 2.5 everywhere: reflection padding folds coordinates
+    # back several times, yet they stay small enough (< 1e3 px) for their fp32 value to be well defined
+    pose_out = torch.tensor([[1.6, -0.5, -1.5, 0.05, -0.20, 0.04], [-1.2, 0.6, -1.0, -0.04, 0.25, -0.08]])
+    out = dict(img=img, depth=depth, gout=gout, K=Kb, pose6=pose6, pose_far=pose_far, pose_out=pose_out)
+    cases = {"euler_zeros": (pose6, dict()), "quat_border": (pose6, dict(rotation_mode="quat", padding_mode="border")),
+             "out_reflection": (pose_out, dict(padding_mode="reflection")), "far_zeros": (pose_far, dict()),
+             "nearest_border": (pose6, dict(mode="nearest", padding_mode="border"))}
+    for name, (pose, kw) in cases.items():
+        a, d, p = img.clone().requires_grad_(), depth.clone().requires_grad_(), pose.clone().requires_grad_()
+        iw.pixel_coords = None
+        warped, _ = iw.inverse_warp(a, d, p, Kb, **kw)
+        (warped * gout).sum().backward()
+        out[name + "_out"], out[name + "_gimg"] = warped.detach(), a.grad
+        out[name + "_gdepth"], out[name + "_gpose"] = d.grad, p.grad
+    a, d = img.clone().requires_grad_(), depth.clone().requires_grad_()
+    p44 = iw.pose_vec2mat_full(pose6).clone().requires_grad_()
+    iw.pixel_coords = None
+    warped, _ = iw.inverse_warp(a, d, p44, Kb)
+    (warped * gout).sum().backward()
+    out["mat_gimg"], out["mat_gdepth"], out["mat_gpose"] = a.grad, d.grad, p44.grad
+    save("inverse_warp_bwd", **out)
+
+
 def case_lcsim_fixture():
     """The one known-answer vector the reference ships for lcsim: example/dpv.npy['angles']."""
     d = np.load("/root/reference/external/lcsim/python/example/dpv.npy", allow_pickle=True, encoding="bytes")[()]
@@ -392,3 +429,4 @@ if __name__ == "__main__":
     case_sense_transformed()
     case_plan_transformed()
     case_correlation_backward()
+    case_inverse_warp_backward()

@@ -83,6 +83,66 @@ def test_inverse_warp_golden():
         IW.inverse_warp(img, depth.unsqueeze(1), p6, K)
 
 
+def _scaled_close(a, b, what, rel=1e-3):
+    """|a - b| <= rel * (|b| + max|b| / 10): gradients near the Z clamp of cam2pixel are 1/Z^2-large, so the scale of the
+    tensor, not 1, is what an absolute floor has to follow."""
+    a = a.detach().cpu().double().numpy()
+    b = np.asarray(b, np.float64)
+    tol = rel * (np.abs(b) + np.abs(b).max() / 10 + 1e-12)
+    bad = np.abs(a - b) > tol
+    assert not bad.any(), "%s: %d of %d beyond tolerance, worst |diff| %.3g at |ref| %.3g" % (
+        what, int(bad.sum()), bad.size, float(np.abs(a - b)[bad].max()), float(np.abs(b)[bad][np.abs(a - b)[bad].argmax()]))
+
+
+@pytest.mark.parametrize("case,pose_key,kw", [
+    ("euler_zeros", "pose6", {}),
+    ("quat_border", "pose6", dict(rotation_mode="quat", padding_mode="border")),
+    ("far_zeros", "pose_far", {}),
+    ("out_reflection", "pose_out", dict(padding_mode="reflection")),
+    ("nearest_border", "pose6", dict(mode="nearest", padding_mode="border"))])
+def test_inverse_warp_backward_matches_reference_autograd(case, pose_key, kw):
+    """Gradients w.r.t. image, depth and pose vector of the CUDA backward (through torch.autograd.Function and the torch
+    pose algebra) against autograd of the unmodified reference (tests/golden/inverse_warp_bwd.npz)."""
+    from depthestimation_b200.utils import inverse_warp as IW
+    g = load("inverse_warp_bwd")
+    img, depth, pose = (cu(g[k]).requires_grad_() for k in ("img", "depth", pose_key))
+    out, valid = IW.inverse_warp(img, depth, pose, cu(g["K"]), **kw)
+    assert not valid.requires_grad
+    (out * cu(g["gout"])).sum().backward()
+    if case == "nearest_border":                           # a coordinate within 1e-4 px of .5 may pick the other texel
+        assert (np.abs(img.grad.cpu().numpy() - g[case + "_gimg"]) > 1e-5).mean() < 0.01
+        assert float(depth.grad.abs().max()) == 0.0 and float(pose.grad.abs().max()) == 0.0
+        return
+    _scaled_close(out, g[case + "_out"], case + " forward", rel=1e-4)
+    _scaled_close(img.grad, g[case + "_gimg"], case + " grad img")
+    _scaled_close(depth.grad, g[case + "_gdepth"], case + " grad depth")
+    _scaled_close(pose.grad, g[case + "_gpose"], case + " grad pose")
+
+
+def test_inverse_warp_backward_4x4_pose_and_partial_grads():
+    from depthestimation_b200.utils import inverse_warp as IW
+    g = load("inverse_warp_bwd")
+    K = cu(g["K"])
+    img, depth = cu(g["img"]).requires_grad_(), cu(g["depth"]).requires_grad_()
+    p44 = IW.pose_vec2mat_full(cu(g["pose6"])).detach().requires_grad_()
+    out, _ = IW.inverse_warp(img, depth, p44, K)
+    (out * cu(g["gout"])).sum().backward()
+    _scaled_close(img.grad, g["mat_gimg"], "4x4 grad img")
+    _scaled_close(depth.grad, g["mat_gdepth"], "4x4 grad depth")
+    _scaled_close(p44.grad, g["mat_gpose"], "4x4 grad pose")
+    # only the depth asks for a gradient (the photometric loss of a fixed image pair): same values, nothing else touched
+    d2 = cu(g["depth"]).requires_grad_()
+    out2, _ = IW.inverse_warp(cu(g["img"]), d2, cu(g["pose6"]), K)
+    (out2 * cu(g["gout"])).sum().backward()
+    _scaled_close(d2.grad, g["euler_zeros_gdepth"], "depth-only gradient")
+    # under no_grad nothing is recorded; a gradient w.r.t. the intrinsics is refused, not silently dropped
+    with torch.no_grad():
+        assert not IW.inverse_warp(img, depth, cu(g["pose6"]), K)[0].requires_grad
+    Kg = K.clone().requires_grad_()
+    with pytest.raises(NotImplementedError):
+        IW.inverse_warp(cu(g["img"]), cu(g["depth"]), cu(g["pose6"]), Kg)[0].sum().backward()
+
+
 def test_inverse_warp_full_size_against_oracle_and_identity():
     from depthestimation_b200.utils import inverse_warp as IW
     gen = torch.Generator().manual_seed(3)
@@ -93,8 +153,12 @@ def test_inverse_warp_full_size_against_oracle_and_identity():
     pose = torch.tensor([[0.2, -0.05, 0.3, 0.01, -0.02, 0.005], [0.0, 0.0, 0.0, 0.0, 0.0, 0.0]])
     ref, rvalid = A.inverse_warp(img, depth, A.pose_matrix(pose), K)
     out, valid = IW.inverse_warp(img.cuda(), depth.cuda(), pose.cuda(), K.cuda())
+    # Tolerance from the conditioning of this input (profiles/cond_inverse_warp_fullsize.py): coordinates reach 768 px
+    # (one fp32 ulp = 6e-5 px) on an N(0,1) image, and the reference's own fp32 arithmetic is up to 5.9e-4 away from
+    # the same formula in fp64, 3.6 % of the samples beyond 1e-4.  Measured for the kernel against the fp32 oracle:
+    # max 6.7e-4, 2.9 % beyond 1e-4, none beyond 1e-3.
     d = (out.cpu() - ref).abs()
-    assert float(d.max()) < 2e-2 and float((d > 1e-3).float().mean()) < 1e-3, (float(d.max()), float(d.mean()))
+    assert float(d.max()) < 1e-3 and float((d > 1e-4).float().mean()) < 0.05, (float(d.max()), float(d.mean()))
     assert float((valid.cpu() != rvalid).float().mean()) < 1e-3
     # identity pose with align_corners=False sampling of a (w-1)-normalised grid: interior equals a fixed
     # resampling of the image itself, so warping twice the same way is deterministic and finite

@@ -288,3 +288,27 @@ def test_lc_process_with_separate_lc_camera_against_oracle():
     assert bad.mean() < 0.02, bad.mean()               # pixels whose curtain point moved by a DP tie / z-buffer border
     keep = ~bad[0]
     np.testing.assert_allclose(got[0][:, keep], ref[0][:, keep], rtol=1e-3, atol=2e-3)
+
+
+def test_depth_to_points_bit_exact():
+    """lc_depth_to_points / img_utils.depth_to_pts against the reference's own elementwise expressions
+    (utils/img_utils.py:269-293: (x - cx) / fx * depth), evaluated by torch in fp32 ON THE CPU like the goldens -- ATen's
+    CUDA kernel turns a division by a Python scalar into a multiplication by its reciprocal, the CPU one divides --
+    bit for bit."""
+    from depthestimation_b200 import lcsim
+    from depthestimation_b200.utils import img_utils
+    gen = torch.Generator().manual_seed(21)
+    H, W = 37, 53
+    depth = (2.0 + 30.0 * torch.rand(2, H, W, generator=gen)).cuda()
+    K = np.array([[61.3, 0, 25.7], [0, 58.9, 17.2], [0, 0, 1]], np.float32)
+    yy, xx = torch.meshgrid(torch.arange(H).float(), torch.arange(W).float(), indexing="ij")
+    xf, yf = (xx - float(K[0, 2])) / float(K[0, 0]), (yy - float(K[1, 2])) / float(K[1, 1])
+    pts = lcsim.depth_to_points(depth, K)
+    assert pts.shape == (2, H * W, 4)
+    for b in range(2):
+        d = depth[b].cpu()
+        exp = torch.stack([xf * d, yf * d, d, torch.ones_like(d)], -1).reshape(-1, 4)
+        assert torch.equal(pts[b].cpu(), exp)
+        assert torch.equal(img_utils.depth_to_pts(depth[b:b + 1], K).cpu(), exp[:, :3].t().reshape(3, H, W))
+    with pytest.raises(Exception):
+        img_utils.depth_to_pts(depth, K)
