@@ -350,3 +350,30 @@ def test_sense_fuse_ragged_shapes_against_oracle(W, H, D, nsweep):
     close(out, exp, atol=1e-5)
     close(mean, O.dpv_expectation(exp, d_candi, True), atol=1e-4)
     assert float((exp - logp).abs().max()) > 0.1
+
+
+@pytest.mark.parametrize("name", ["fixture_t35", "fixture_t100", "bench_768"])
+def test_planner_bit_exact_against_reference_planning_cpp(name):
+    """The DP kernel against the reference's OWN planner (external/lcsim/lcsim/src/planning.cpp compiled verbatim,
+    tests/golden/planner_ref.npz): same camera angles, edge count, path lengths, every design point bit for bit --
+    fixture field, random map, heavily tied maps, a map with a single non-zero entry (the path ends early)."""
+    from depthestimation_b200 import lcsim
+    g = load("planner_ref")
+    w, h = [int(v) for v in g[name + "_size"]]
+    cp = dict(width=w, height=h, matrix=g[name + "_K"], distortion=[0.] * 5, hit_mode=1, hit_noise=0.)
+    lp = dict(lTc=_lTc(), fov=80., laser_timestep=float(g[name + "_timestep"]))
+    dev = lcsim.LCDevice(CAMERA_PARAMS=cp, LASER_PARAMS=lp)
+    np.testing.assert_array_equal(dev.valid_angles(), g[name + "_angles"])
+    pl = lcsim.PlannerRT(dev, g[name + "_ranges"], w)
+    assert pl.edge_count() == int(g[name + "_edges"])
+    ks, xz, counts = pl.solve(cu(g[name + "_maps"]))
+    ranges = g[name + "_ranges"]
+    for i in range(len(g[name + "_maps"])):
+        n = int(g[name + "_counts"][i])
+        assert int(counts[i]) == n, "map %d: path length %d vs %d" % (i, int(counts[i]), n)
+        np.testing.assert_array_equal(xz[i, :n].cpu().numpy(), g[name + "_xz"][i, :n], err_msg="map %d" % i)
+        assert (ks[i, n:] == -1).all()
+        # the range indices are the ones those design points belong to: r_k = |(x, z)| up to rounding
+        k = ks[i, :n].cpu().numpy()
+        r = np.hypot(g[name + "_xz"][i, :n, 0].astype(np.float64), g[name + "_xz"][i, :n, 1].astype(np.float64))
+        np.testing.assert_allclose(r, ranges[k], rtol=1e-5)

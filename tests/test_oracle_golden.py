@@ -4,6 +4,7 @@ fixture the reference ships for lcsim (example/dpv.npy['angles'])."""
 import os
 
 import numpy as np
+import pytest
 import torch
 
 from oracle import dpv_oracle as O
@@ -243,3 +244,52 @@ def test_correlation_backward_against_reference_twin_and_autograd():
     g1, g2 = A.correlation_backward(gout.float(), x1.detach().float(), x2.detach().float(), pad, k, md, 1, s2)
     close(g1, x1.grad.float().numpy(), rtol=1e-4, atol=1e-6)
     close(g2, x2.grad.float().numpy(), rtol=1e-4, atol=1e-6)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# a12: the DP planner pinned to the reference's own translation unit (planning.cpp compiled verbatim,
+# oracle/ref_planner.py -> tests/golden/planner_ref.npz)
+# ---------------------------------------------------------------------------------------------------------------
+PLANNER_REF_CASES = ("fixture_t35", "fixture_t100", "bench_768")
+
+
+def _planner_ref_device(g, name):
+    from oracle import lcsim as olcsim
+    w, h = [int(v) for v in g[name + "_size"]]
+    T = np.eye(4, dtype=np.float32)
+    T[0, 3] = 0.2
+    cp = dict(width=w, height=h, matrix=g[name + "_K"], distortion=[0.] * 5, hit_mode=1, hit_noise=0.)
+    lp = dict(lTc=T, fov=80., laser_timestep=float(g[name + "_timestep"]))
+    return olcsim.LCDevice(CAMERA_PARAMS=cp, LASER_PARAMS=lp), w
+
+
+@pytest.mark.parametrize("name", PLANNER_REF_CASES)
+def test_oracle_planner_matches_reference_planning_cpp(name):
+    """oracle/lcsim_oracle.cpp's planner against the design points the reference's planning.cpp produced on the same
+    camera angles, ranges and maps: edge count, path length and every (x, z) bit for bit."""
+    from oracle import lcsim as olcsim
+    g = np.load(os.path.join(G, "planner_ref.npz"))
+    dev, w = _planner_ref_device(g, name)
+    np.testing.assert_array_equal(dev.valid_angles(), g[name + "_angles"])       # same planner input
+    pl = olcsim.PlannerRT(dev, g[name + "_ranges"], w)
+    assert pl.edge_count() == int(g[name + "_edges"])
+    for i, m in enumerate(g[name + "_maps"]):
+        n = int(g[name + "_counts"][i])
+        xz = pl.get_design_points(m)
+        assert len(xz) == n, "map %d: path length %d vs %d" % (i, len(xz), n)
+        np.testing.assert_array_equal(xz, g[name + "_xz"][i, :n], err_msg="map %d" % i)
+
+
+def test_planner_ref_golden_is_what_the_reference_produces_now():
+    """Where the reference is on the machine (the build container), recompile planning.cpp and regenerate one case:
+    the committed golden is not stale and the build recipe works."""
+    from oracle import ref_planner as RP
+    if not RP.available():
+        pytest.skip("/root/reference is not on this machine")
+    g = np.load(os.path.join(G, "planner_ref.npz"))
+    name = "fixture_t35"
+    ref = RP.RefPlanner(g[name + "_angles"], g[name + "_ranges"], g["laser_to_cam"], 14000.0, float(g[name + "_timestep"]))
+    assert ref.edge_count() == int(g[name + "_edges"])
+    for i in (0, 2):
+        n = int(g[name + "_counts"][i])
+        np.testing.assert_array_equal(ref.get_design_points(g[name + "_maps"][i]), g[name + "_xz"][i, :n])
