@@ -39,8 +39,10 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--launch", default="auto", choices=["auto", "graph", "eager"],
                     help="value loop: replay one captured CUDA graph per batch slot, or launch kernel by kernel; auto = "
-                         "graphs when more than 4 ranks share the host (their launching threads fall behind the GPUs: "
-                         "DESIGN.md section 7), kernel by kernel otherwise (0-3 %% faster at 1-4 ranks)")
+                         "graphs whenever several ranks share the host (their launching threads compete for its cores: "
+                         "DESIGN.md section 7), kernel by kernel for a single rank")
+    ap.add_argument("--hit-noise", type=float, default=0.01,
+                    help="sigma of the simulator's intensity noise (the reference hard-codes 0.01, lc/light_curtain.py:270-285)")
     ap.add_argument("--streams", type=int, default=6,
                     help="independent batches in flight (steps are issued round-robin on this many CUDA streams)")
     return ap.parse_args()
@@ -151,20 +153,35 @@ class ClockSampler:
 # --------------------------------------------------------------------------------------------------
 # GPU arm
 # --------------------------------------------------------------------------------------------------
+def pick_slots(requested, steps):
+    """Batches in flight: the largest count <= requested that divides the timed steps, so that every slot runs the
+    same number of steps and the region has no tail in which the last batches run alone (>= 4 where possible)."""
+    requested = max(1, min(requested, steps))
+    for s_ in range(requested, 0, -1):
+        if steps % s_ == 0 and (s_ >= min(4, requested) or s_ == 1):
+            return s_
+    return requested
+
+
 def run_b200(args):
     import torch.distributed as dist
     from depthestimation_b200 import _lib, sharding
     from depthestimation_b200.pipeline import STREAMED_KEYS, DpvLcPipeline, synthetic_batch
     rank, world, local = sharding.init_from_env(args.gpus)
+    cores = sharding.pin_rank_to_cores(local, world)    # before any helper thread / the clock sampler starts
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     host, meta = synthetic_batch(args.workload, seed=rank)
     B = meta["B"]
-    S = max(1, min(args.streams, args.steps))
-    pipes = [DpvLcPipeline(meta, dev) for _ in range(S)]
+    S = pick_slots(args.streams, args.steps)
+    hit_noise = args.hit_noise if meta["iterations"] > 0 else 0.0
+    pipes = [DpvLcPipeline(meta, dev, hit_noise=hit_noise, noise_seed=1000 * rank + sl) for sl in range(S)]
     streams = [torch.cuda.Stream(dev) for _ in range(S)]
     pipe = pipes[0]
     x = {k: v.to(dev) for k, v in host.items()}
+    # every batch slot has its own resident copy of the per-step inputs: `value` leaves them where they are, `e2e`
+    # refills them from pinned host memory before each step (the captured graphs read them in both cases)
+    xs = [dict(x, **{k: x[k].clone() for k in STREAMED_KEYS}) for _ in range(S)]
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -183,7 +200,7 @@ def run_b200(args):
     launches_per_step = None
 
     def capture_graphs():
-        """The step is ~80 kernel launches on ~2 ms of GPU work per batch; with 8 ranks on one host the launching
+        """A step is ~80 kernel launches for a few ms of GPU work; with several ranks on one host the launching
         threads fall behind the GPUs.  One CUDA graph per batch slot (captured after an eager step has sized every
         buffer) makes a step one graph launch.  The graph holds exactly the kernels the eager step launches."""
         got = []
@@ -191,13 +208,14 @@ def run_b200(args):
         for sl in range(S):
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, stream=streams[sl]):
-                out = pipes[sl].step(x)
+                out = pipes[sl].step(xs[sl])
             got.append((g, out))
         return got, (_lib.launch_count() - n_before) // S
 
-    def run_steps(n):
-        """n steps, step i on stream i % S: successive (independent) batches overlap — the latency-bound planner of
-        one batch runs beside the streaming kernels of the next."""
+    def run_steps(n, step_events=None):
+        """n steps, step i on stream i % S: successive (independent) batches overlap -- the latency-bound planner of
+        one batch runs beside the streaming kernels of the next.  Each step's depth maps go to every rank through the
+        collector's side-stream all_gather while later steps compute."""
         start = torch.cuda.Event()
         start.record(main)
         for st in streams:
@@ -205,23 +223,30 @@ def run_b200(args):
         coll = sharding.FrameOutputCollector(n, world)
         for i in range(n):
             with torch.cuda.stream(streams[i % S]):
+                if step_events is not None:
+                    a = torch.cuda.Event(enable_timing=True)
+                    a.record()
                 if graphs is not None:
                     graphs[i % S][0].replay()
                     coll.add(graphs[i % S][1])
                 else:
-                    coll.add(pipes[i % S].step(x))
+                    coll.add(pipes[i % S].step(xs[i % S]))
+                if step_events is not None:
+                    b = torch.cuda.Event(enable_timing=True)
+                    b.record()
+                    step_events.append((a, b))
         for st in streams:
             done = torch.cuda.Event()
             done.record(st)
             main.wait_event(done)
-        coll.finish()                                   # the one exchange of the path: all ranks' depth maps (NCCL)
+        coll.finish()                                   # waits for the last per-step gathers (NCCL, side stream)
 
     # ---- value: inputs resident in HBM --------------------------------------------------------
     sampler = ClockSampler(local).start()               # before the region: its start-up must not land inside it
     run_steps(max(args.warmup, S))
     sync()
     launch_mode = "eager"
-    if args.launch == "graph" or (args.launch == "auto" and world > 4):
+    if args.launch == "graph" or (args.launch == "auto" and world > 1):
         try:
             graphs, launches_per_step = capture_graphs()
             launch_mode = "cuda-graph replay, one graph per batch slot"
@@ -232,6 +257,7 @@ def run_b200(args):
             graphs = None
             launch_mode = "eager (graph capture failed: %s)" % str(e).splitlines()[0][:120]
             torch.cuda.synchronize(dev)
+
     def load_pass():
         """S steps without the collector (no collective, no barrier): keeps the GPU under the step's load."""
         for sl in range(S):
@@ -239,56 +265,43 @@ def run_b200(args):
                 if graphs is not None:
                     graphs[sl][0].replay()
                 else:
-                    pipes[sl].step(x)
+                    pipes[sl].step(xs[sl])
         torch.cuda.synchronize(dev)
+
+    def set_kernel_events(on):
+        for p_ in pipes:
+            p_.fuse_events = [] if on else None
+            p_.planner_events = [] if on else None
 
     sampler.wait_ready()
     load_pass()                                         # the GPU is under the step's load when the region starts
-    for p_ in pipes:
-        p_.fuse_events = [] if graphs is None else None  # events inside a captured graph cannot be timed
+    set_kernel_events(graphs is None)                   # events inside a captured graph cannot be timed
+    step_ev = []
     n0 = _lib.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync()
     t_load0 = time.perf_counter()
     e0.record(main)
-    run_steps(args.steps)
+    run_steps(args.steps, step_ev)
     e1.record(main)
     sync()
     n1 = _lib.launch_count()
-    stash = [p_.fuse_events for p_ in pipes]
-    for p_ in pipes:
-        p_.fuse_events = None
+    fuse_in = [ev for p_ in pipes for ev in (p_.fuse_events or [])]
+    set_kernel_events(False)
     extra = 0
-    while sampler.p and sampler.count(t_load0) == 0 and extra < 40:
+    while sampler.p and sampler.count(t_load0) == 0 and time.perf_counter() - t_load0 < 3.0:
         load_pass()                                     # a short region can fall between two 200 ms samples: keep the
         extra += 1                                      # same load (untimed, rank-local) until one has been taken
     t_load1 = time.perf_counter()
     sampler.stop()
-    for p_, ev in zip(pipes, stash):
-        p_.fuse_events = ev
     clk_summary = sampler.summary(t_load0, t_load1)
     clk_summary["window"] = "timed region" if extra == 0 else "timed region + %d untimed passes of the same steps" % extra
     ms = e0.elapsed_time(e1)
     launches = n1 - n0 if graphs is None else launches_per_step * args.steps
-    if graphs is None:
-        fuse_ms = [a.elapsed_time(b) for p_ in pipes for a, b in p_.fuse_events]
-        ms_events = ms
-    else:
-        # the kernel's in-flight timing needs events around single launches: one more (untimed for `value`) eager pass
-        replay, graphs = graphs, None
-        for p_ in pipes:
-            p_.fuse_events = []
-        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        sync()
-        g0.record(main)
-        run_steps(args.steps)
-        g1.record(main)
-        sync()
-        ms_events = g0.elapsed_time(g1)
-        fuse_ms = [a.elapsed_time(b) for p_ in pipes for a, b in p_.fuse_events]
-        graphs = replay
-    for p_ in pipes:
-        p_.fuse_events = None
+    # how long each step took from its first to its last kernel (S of them overlap): a stretched run names its step
+    per_step = sorted(a.elapsed_time(b) for a, b in step_ev)
+    step_spread = {"min": round(per_step[0], 3), "median": round(per_step[len(per_step) // 2], 3),
+                   "max": round(per_step[-1], 3), "note": "ms from a step's first to its last kernel, %d in flight" % S}
     ms_t = torch.tensor([ms], device=dev)
     if world > 1:
         dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
@@ -296,58 +309,67 @@ def run_b200(args):
     ms_per_step = ms / args.steps
     value = world * B * args.steps / (ms / 1e3)
 
+    # ---- one batch in flight (eager, CUDA events around single launches): the latency of a batch and the kernels'
+    # own durations -- the condition the ncu launch list measures too.  Right after the timed region, same data.
+    replay, graphs = graphs, None
+    set_kernel_events(False)
+    with torch.cuda.stream(main):
+        pipe.step(xs[0])                                # warm: eager launches after graph replays
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        pipe.fuse_events, pipe.planner_events = [], []
+        s0.record(main)
+        for _ in range(3):
+            pipe.step(xs[0])
+        s1.record(main)
+    torch.cuda.synchronize(dev)
+    single_batch_ms = s0.elapsed_time(s1) / 3
+    fuse_solo = [a.elapsed_time(b) for a, b in pipe.fuse_events]
+    plan_solo = [a.elapsed_time(b) for a, b in pipe.planner_events]
+    set_kernel_events(False)
+    graphs = replay
+
     # ---- e2e: host buffers in, host results out, copies inside the timed region ------------------
     e2e = None
     if not args.no_e2e:
-        e2e = run_e2e(args, pipes, streams, host, x, dev, world, B, STREAMED_KEYS, sync, sharding)
+        e2e = run_e2e(args, pipes, streams, host, xs, graphs, dev, world, B, STREAMED_KEYS, sync, sharding)
 
-    # ---- roofline of the dominant kernel (sense+fuse: one read + one write of the volume) --------
+    # ---- roofline of the dominant HBM kernel (sense+fuse: one read + one write of the volume) and the kernel that
+    # dominates by TIME (the DP planner: latency-bound, SURVEY 8d reports it in microseconds and SMs, not GB/s)
     alg = pipe.algorithmic_bytes()
     roof = None
-    if fuse_ms:
-        def roof_of(times_ms, step_ms_total):
-            t = statistics.mean(times_ms) / 1e3
-            ach = alg["sense_fuse"] / t / 1e9
-            return {"launch_ms": round(t * 1e3, 4), "achieved": round(ach, 1), "frac": round(ach / peak_gbs, 4),
-                    "launches_timed": len(times_ms),
-                    "share_of_step": round(sum(times_ms) / step_ms_total if step_ms_total else 0.0, 4)}
-        in_region = roof_of(fuse_ms, ms_events)
-        solo = in_region
-        if S > 1:
-            # With S batches in flight the events around a launch also span the slices other streams' kernels get
-            # on the same SMs, so they do not time the kernel.  The kernel itself is timed the same way (CUDA events
-            # on its stream, same data, inside bench.py) in a pass with one batch in flight right after the timed
-            # region; the stretched in-region figure is kept under "in_flight".
-            pipe.fuse_events = []
-            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            with torch.cuda.stream(main):
-                pipe.step(x)
-                s0.record(main)
-                pipe.fuse_events = []
-                for _ in range(3):
-                    pipe.step(x)
-                s1.record(main)
-            sync()
-            solo = roof_of([a.elapsed_time(b) for a, b in pipe.fuse_events], s0.elapsed_time(s1))
-            pipe.fuse_events = None
-        roof = {"kernel": "sense_fuse_kernel", "bound": "hbm", "achieved": solo["achieved"], "peak": peak_gbs,
-                "peak_source": peak_src, "unit": "GB/s", "frac": solo["frac"], "traffic": None,
-                "launch_ms": solo["launch_ms"], "launches_timed": solo["launches_timed"],
-                "algorithmic_bytes_per_launch": alg["sense_fuse"], "share_of_step": solo["share_of_step"]}
-        if S > 1:
-            roof["timed_with"] = "1 batch in flight (pass after the timed region)"
-            roof["in_flight"] = dict(in_region, batches=S)
-            if launch_mode != "eager" and not launch_mode.startswith("eager"):
-                roof["in_flight"]["timed_with"] = "eager pass of the same streams after the timed region"
+    if fuse_solo:
+        t = statistics.mean(fuse_solo) / 1e3
+        ach = alg["sense_fuse"] / t / 1e9
+        nz_bytes = 0 if pipe.noise_pool is None else pipe.noise_pool[0].numel() * 4      # read once per launch
+        roof = {"kernel": "sense_fuse_kernel", "bound": "hbm", "achieved": round(ach, 1), "peak": peak_gbs,
+                "peak_source": peak_src, "unit": "GB/s", "frac": round(ach / peak_gbs, 4), "traffic": None,
+                "launch_ms": round(t * 1e3, 4), "launches_timed": len(fuse_solo),
+                "algorithmic_bytes_per_launch": alg["sense_fuse"], "noise_bytes_per_launch_not_counted": nz_bytes,
+                "timed_with": "CUDA events around each launch, 1 batch in flight (pass after the timed region)",
+                "share_of_single_batch_step": round(sum(fuse_solo) / 3 / single_batch_ms, 4),
+                "role": "dominant HBM kernel (named by hand: the kernel that moves the most bytes per step)"}
+        if fuse_in:
+            tin = [a.elapsed_time(b) for a, b in fuse_in]
+            roof["in_flight"] = {"launch_ms": round(statistics.mean(tin), 4), "batches": S,
+                                 "note": "event-to-event inside the timed region: includes the slices other batches' "
+                                         "kernels get on the same SMs, so it is not the kernel's own duration"}
         tr = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tr):
             roof["traffic"] = json.load(open(tr)).get("sense_fuse_kernel")
+        if plan_solo:
+            nmaps = B * (1 + 2 * len(meta["step"]))
+            roof["dominant_by_time"] = {
+                "kernel": "planner_solve_kernel", "class": "latency-bound (W sequential rays per map)",
+                "launch_us": round(statistics.mean(plan_solo) * 1e3, 1), "launches_per_step": meta["iterations"],
+                "maps_per_launch": nmaps, "sms_occupied": 2 * nmaps, "sms_total": 148,
+                "share_of_single_batch_step": round(sum(plan_solo) / 3 / single_batch_ms, 4)}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        v, dt, cores, _ = time_cpu(args.workload, 1, 0)
-        cpu = {"value": round(v, 5), "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": "1 frame of the same workload through oracle/ (torch-CPU restatement + restated lcsim C++), "
+        v, dt, ncores, _ = time_cpu(args.workload, 1, 1)            # one warm-up like the reference arm (flow field,
+        cpu = {"value": round(v, 5), "unit": UNIT, "cores": ncores, "kind": "port",     # handles, first-touch)
+               "sample": "1 frame of the same workload through oracle/ after 1 warm-up frame (torch-CPU restatement + "
+                         "restated lcsim C++; leaner than the reference's own Python: no D x C warp, no repeat()), "
                          "%.1f s" % dt}
     if rank == 0:
         line = {"metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -355,24 +377,29 @@ def run_b200(args):
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": args.workload, "frames_per_gpu": B, "H": meta["H"], "W": meta["W"],
                            "D": meta["D"], "C": meta["C"], "T": meta["T"], "lc_iterations": meta["iterations"],
-                           "curtains_per_iteration": 1 + 2 * len(meta["step"]), "parallelism": "batch-shard x%d" % world, "streams_in_flight": S,
-                           "launch": launch_mode,
+                           "curtains_per_iteration": 1 + 2 * len(meta["step"]), "hit_noise": hit_noise,
+                           "noise": "pre-generated pool per batch slot" if hit_noise > 0 else "none",
+                           "parallelism": "batch-shard x%d" % world, "streams_in_flight": S, "launch": launch_mode,
+                           "gather": "per-step all_gather on a side stream" if world > 1 else "none (1 rank)",
+                           "rank_cores": None if cores is None else len(cores),
                            "l2_policy": "inputs larger than L2 (0.9 GB streamed per frame)"},
                 "clocks": clk_summary, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
-                "ms_per_frame": round(ms_per_step / B, 4)}
+                "ms_per_frame": round(ms_per_step / B, 4), "single_batch_ms": round(single_batch_ms, 4),
+                "single_batch_note": "latency of ONE batch of %d frame(s) through the whole step, nothing else in "
+                                     "flight (eager launches)" % B,
+                "step_spread_ms": step_spread}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
 
-def run_e2e(args, pipes, streams, host, x, dev, world, B, keys, sync, sharding):
-    """Same step through the public API with HOST buffers: every step copies its inputs from pinned host memory
-    (H2D) and reads depth / variance / LC depth back (D2H), on the step's own stream, so the copies of one batch
-    overlap the kernels of the others."""
+def run_e2e(args, pipes, streams, host, xs, graphs, dev, world, B, keys, sync, sharding):
+    """Same step through the public API with HOST buffers: every step copies its inputs from pinned host memory into
+    its batch slot's device buffers (H2D) and reads depth / variance / LC depth back (D2H), on the step's own stream,
+    so the copies of one batch overlap the kernels of the others.  Launch mode as in the `value` loop."""
     S = len(pipes)
     m = pipes[0].m
     pin = {k: host[k].pin_memory() for k in keys}
-    bufs = [{k: torch.empty_like(x[k]) for k in keys} for _ in range(S)]
     res_host = [{k: torch.empty(B, m["H"], m["W"]).pin_memory() for k in ("depth", "var", "depth_lc")} for _ in range(S)]
     main = torch.cuda.current_stream(dev)
     h2d = sum(pin[k].numel() * 4 for k in keys)
@@ -388,13 +415,15 @@ def run_e2e(args, pipes, streams, host, x, dev, world, B, keys, sync, sharding):
             sl = i % S
             with torch.cuda.stream(streams[sl]):
                 for k in keys:
-                    bufs[sl][k].copy_(pin[k], non_blocking=True)
-                xin = dict(x)
-                xin.update(bufs[sl])
-                out = pipes[sl].step(xin)
+                    xs[sl][k].copy_(pin[k], non_blocking=True)
+                if graphs is not None:
+                    graphs[sl][0].replay()
+                    out = graphs[sl][1]
+                else:
+                    out = pipes[sl].step(xs[sl])
                 coll.add(out)
                 for k in res_host[sl]:
-                    if k in out:
+                    if out.get(k) is not None:
                         res_host[sl][k].copy_(out[k], non_blocking=True)
         for st in streams:
             done = torch.cuda.Event()
@@ -414,8 +443,13 @@ def run_e2e(args, pipes, streams, host, x, dev, world, B, keys, sync, sharding):
         import torch.distributed as dist
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dt = float(t.item())
+    per_rank_gbs = h2d * args.steps / dt / 1e9
     return {"value": round(world * B * args.steps / dt, 2), "unit": UNIT, "h2d_bytes_per_step": h2d,
-            "d2h_bytes_per_step": d2h, "ms_per_step": round(dt / args.steps * 1e3, 4)}
+            "d2h_bytes_per_step": d2h, "ms_per_step": round(dt / args.steps * 1e3, 4),
+            "h2d_gbs_per_rank": round(per_rank_gbs, 1), "h2d_gbs_all_ranks": round(per_rank_gbs * world, 1),
+            "limiter": "host link: every step uploads its inputs (%.0f MB, of which the decoder logits are %.0f MB) from "
+                       "pinned host memory; one rank is PCIe-bound, several ranks share the host's memory / PCIe "
+                       "bandwidth" % (h2d / 1e6, pin["dec_logits"].numel() * 4 / 1e6)}
 
 
 def run_reference(args):

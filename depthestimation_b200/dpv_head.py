@@ -65,7 +65,7 @@ class LcLoopState:
 
 
 def lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n, noise=None, trace=None, events=None,
-                 in_prob=False, out_prob=False, src=None):
+                 in_prob=False, out_prob=False, src=None, planner_events=None):
     """One Bayesian iteration (models.py:1027-1122) for the whole batch: 6 kernel launches, no host sync.
     src = (volume, E[d]) to read instead of the state's own buffers (the first iteration of a loop reads the caller's
     DPV and writes the state's: the caller's volume and depth map stay as they were, like the reference's
@@ -76,7 +76,13 @@ def lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n,
     vol_in, mean_in = (state.logp, state.mean) if src is None else src
     ops.ufield(vol_in, mean_in, K, lc.d_candi, uf_par, bv_log=not in_prob, want_depth=False, out=state.uf)
     ops.plan_prepare(state.uf, rig.flow, steps, R, state.umaps, state.argmax, state.field_pre)
+    if planner_events is not None:
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record()
     rig.planner.solve(state.umaps.view(B * nc, R, W), state.ks, state.xz, state.counts)
+    if planner_events is not None:
+        p1.record()
+        planner_events.append((p0, p1))
     check(lib().lc_curtain_planes(dev._h, ptr(state.xz), ptr(state.counts), B * nc, W, ptr(state.planes), None,
                                   stream_ptr(dev.device)))
     if trace is not None:

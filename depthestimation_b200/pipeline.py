@@ -118,13 +118,18 @@ STATIC_KEYS = ("K", "K_up", "R", "t", "rays")
 class DpvLcPipeline:
     """Holds the per-geometry handles (LC device, planner, polar flow) and runs one batch through the path."""
 
-    def __init__(self, meta, device, hit_noise=0.0, sigma=10.0):
+    def __init__(self, meta, device, hit_noise=0.0, sigma=10.0, noise_seed=0):
+        """hit_noise: sigma of the simulator's intensity noise (the reference hard-codes 0.01 for both rigs,
+        lc/light_curtain.py:270-285, drawn unseeded inside lcsim; parity tests use 0).  With hit_noise > 0 the draws of
+        every LC iteration come from a pool generated once here (iterations x B*nc x H x W, seeded): the step stays
+        free of RNG launches and replays as a CUDA graph, at the cost of seeing the same draws every step."""
         self.m = meta
         self.device = torch.device(device)
         self.sigma = sigma
         H, W = meta["H"], meta["W"]
         self.lc = None
         self.state = None
+        self.noise_pool = None
         if meta["iterations"] > 0:
             eye = np.eye(4, dtype=np.float32)
             lTc = eye.copy()
@@ -138,7 +143,13 @@ class DpvLcPipeline:
             self.lc.init(P)
             nc = 1 + 2 * len(meta["step"])
             self.state = dpv_head.LcLoopState(meta["B"], meta["D"], H, W, meta["R"], nc, self.device)
+            self.noise_pool = None
+            if hit_noise > 0:
+                gen = torch.Generator(device=self.device).manual_seed(noise_seed)
+                self.noise_pool = torch.randn(meta["iterations"], meta["B"] * nc, H, W, device=self.device,
+                                              generator=gen) * hit_noise
         self.fuse_events = None          # optional list collecting (start, end) CUDA events of sense+fuse launches
+        self.planner_events = None       # the same for the DP planner solves
         self.trace = None                # optional list: per-iteration uf / umaps / ks / logp clones (parity tests)
 
     def step(self, x):
@@ -176,9 +187,10 @@ class DpvLcPipeline:
         # volume; later iterations run in place on that.  out["logp"] / out["depth"] (the reference's output_refined,
         # models.py:784-787) therefore stay what they were next to out["logp_lc"] / out["depth_lc"] (output_lc).
         for i in range(m["iterations"]):
-            nz = rig.dev.noise_like(st.shape[0] * st.shape[5]) if rig.dev.hit_noise > 0 else None
+            nz = self.noise_pool[i] if self.noise_pool is not None else None
             dpv_head.lc_iteration(st, lc, rig, depth, K, uf_par, m["step"], m["spread_iter"], m["spread_n"], noise=nz,
-                                  events=self.fuse_events, trace=self.trace, in_prob=i > 0,
+                                  events=self.fuse_events, planner_events=self.planner_events, trace=self.trace,
+                                  in_prob=i > 0,
                                   out_prob=i < m["iterations"] - 1, src=(logp, mean) if i == 0 else None)
         return st.logp
 

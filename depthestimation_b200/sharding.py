@@ -48,34 +48,79 @@ def gather_frame_outputs(out, world, keys=("depth", "depth_lc")):
 
 
 class FrameOutputCollector:
-    """Keeps the per-frame result maps of the steps a rank runs and exchanges them once at the end
-    (north_star: "a single NCCL gather at the end"), so no collective sits between the steps of the path."""
+    """Keeps the per-frame result maps of the steps a rank runs and brings every rank's maps to every rank (the
+    path's only exchange).  No collective sits between the steps: each step's maps are copied into a
+    rank-local buffer on the step's own stream, and -- on CUDA -- an all_gather of just that step's slice is issued
+    on a side stream behind an event, so it runs while the following steps compute instead of as
+    one 2 GB exchange after the last step.  finish() waits for the side stream.  On CPU tensors (gloo tests) the
+    exchange is a single all_gather in finish().  Every rank must add() the same steps in the same order."""
 
-    def __init__(self, n_steps, world, keys=("depth", "depth_lc")):
+    def __init__(self, n_steps, world, keys=("depth", "depth_lc"), overlap=True):
         self.n_steps, self.world, self.keys = n_steps, world, keys
-        self.buf = {}
+        self.buf, self.full = {}, {}
         self.count = 0
+        self.overlap = overlap
+        self.comm = None                # side stream of the per-step gathers
+
+    def _alloc(self, k, t):
+        self.buf[k] = torch.empty((self.n_steps,) + tuple(t.shape), device=t.device, dtype=t.dtype)
+        if self.world > 1 and t.is_cuda and self.overlap:
+            # [step, rank, ...]: one step's gather writes one contiguous block
+            self.full[k] = torch.empty((self.n_steps, self.world) + tuple(t.shape), device=t.device, dtype=t.dtype)
+            if self.comm is None:
+                self.comm = torch.cuda.Stream(t.device)
 
     def add(self, out):
-        """Copies this step's maps into the rank-local buffer (on the current stream)."""
+        """Copies this step's maps into the rank-local buffer (on the current stream) and queues their gather."""
         i = self.count % self.n_steps
+        self.count += 1
+        got = []
         for k in self.keys:
             t = out.get(k)
             if t is None:
                 continue
             if k not in self.buf:
-                self.buf[k] = torch.empty((self.n_steps,) + tuple(t.shape), device=t.device, dtype=t.dtype)
+                self._alloc(k, t)
             self.buf[k][i].copy_(t, non_blocking=True)
-        self.count += 1
+            got.append(k)
+        if self.comm is not None and got:
+            ready = torch.cuda.Event()
+            ready.record()                                             # on the step's stream, after the copies
+            with torch.cuda.stream(self.comm):
+                self.comm.wait_event(ready)
+                for k in got:
+                    dist.all_gather_into_tensor(self.full[k][i], self.buf[k][i])
 
     def finish(self):
-        """-> {key: [world, n_steps, B, H, W]} on every rank (all_gather over NVLink); rank-local view if world = 1."""
+        """-> {key: [world, n_steps, B, H, W]} on every rank; rank-local view if world = 1."""
         res = {}
+        if self.comm is not None:
+            torch.cuda.current_stream(self.comm.device).wait_stream(self.comm)
         for k, t in self.buf.items():
             if self.world <= 1:
                 res[k] = t.unsqueeze(0)
-                continue
-            full = torch.empty((self.world * t.shape[0],) + tuple(t.shape[1:]), device=t.device, dtype=t.dtype)
-            dist.all_gather_into_tensor(full, t)                       # concatenated along dim 0 (gloo needs this form)
-            res[k] = full.view((self.world,) + tuple(t.shape))
+            elif k in self.full:
+                res[k] = self.full[k].transpose(0, 1)                  # [world, n_steps, ...] (a view)
+            else:
+                full = torch.empty((self.world * t.shape[0],) + tuple(t.shape[1:]), device=t.device, dtype=t.dtype)
+                dist.all_gather_into_tensor(full, t)                   # concatenated along dim 0 (gloo needs this form)
+                res[k] = full.view((self.world,) + tuple(t.shape))
         return res
+
+
+def pin_rank_to_cores(local_rank, ranks_on_host):
+    """Gives each rank of a host its own slice of the cores the process may run on (launch threads of eight ranks
+    otherwise migrate over the same cores).  Returns the cores it now runs on (None where unsupported)."""
+    try:
+        cores = sorted(os.sched_getaffinity(0))
+    except AttributeError:
+        return None
+    per = len(cores) // max(1, ranks_on_host)
+    if per < 1:
+        return cores
+    mine = cores[local_rank * per:(local_rank + 1) * per]
+    try:
+        os.sched_setaffinity(0, mine)
+    except OSError:
+        return cores
+    return mine
