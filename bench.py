@@ -303,7 +303,11 @@ def run_b200(args):
     step_spread = {"min": round(per_step[0], 3), "median": round(per_step[len(per_step) // 2], 3),
                    "max": round(per_step[-1], 3), "note": "ms from a step's first to its last kernel, %d in flight" % S}
     ms_t = torch.tensor([ms], device=dev)
+    ms_ranks = [round(ms / args.steps, 4)]
     if world > 1:
+        every = torch.empty(world, device=dev)
+        dist.all_gather_into_tensor(every, ms_t)                 # each rank's own time: a slow GPU or host shows here
+        ms_ranks = [round(float(v) / args.steps, 4) for v in every.tolist()]
         dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
     ms = float(ms_t.item())
     ms_per_step = ms / args.steps
@@ -387,7 +391,7 @@ def run_b200(args):
                 "ms_per_frame": round(ms_per_step / B, 4), "single_batch_ms": round(single_batch_ms, 4),
                 "single_batch_note": "latency of ONE batch of %d frame(s) through the whole step, nothing else in "
                                      "flight (eager launches)" % B,
-                "step_spread_ms": step_spread}
+                "step_spread_ms": step_spread, "ms_per_step_by_rank": ms_ranks}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

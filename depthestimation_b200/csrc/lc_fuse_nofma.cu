@@ -97,14 +97,15 @@ __global__ void __launch_bounds__(kFuseThreads, DPT <= 16 ? kFuseBlocks16 : 4 * 
 sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float* __restrict__ depth,
                   const float* __restrict__ planes, const float* __restrict__ noise, int nc,
                   const float* __restrict__ d_candi, int D, int spread_iter, int flags,
-                  float* __restrict__ vol_out, float* __restrict__ mean_out) {
+                  float* __restrict__ vol_out, float* __restrict__ mean_out, int rows_per_cta) {
   constexpr int NP = DPT / 2;
   constexpr int STR = DPT + 4;      // lane slices of d_candi, padded: 16-byte aligned and 4 banks apart
   __shared__ __align__(16) float dc[STR * T];
-  for (int i = threadIdx.x; i < STR * T; i += kFuseThreads) {
-    const int tt = i / STR, j = i - tt * STR, d = tt * DPT + j;
-    dc[i] = (j < DPT && d < D) ? d_candi[d] : 0.f;
-  }
+  __shared__ float a_lut[256];      // mapping(i / 255) for the 256 intensities the simulator emits (lc_sense.cuh)
+  for (int d = threadIdx.x; d < DPT * T; d += kFuseThreads)           // DPT is a power of two: shifts, no division
+    dc[(d / DPT) * STR + (d % DPT)] = d < D ? d_candi[d] : 0.f;
+  for (int i = threadIdx.x; i < 4 * T; i += kFuseThreads) dc[(i / 4) * STR + DPT + (i % 4)] = 0.f;   // the pads
+  for (int i = threadIdx.x; i < 256; i += kFuseThreads) a_lut[i] = mapping_of((float)i);
   __syncthreads();
   // grid = (column chunks, rows, samples): no per-thread integer division, all pixel indices in 32 bits.
   // Every lane of a warp stays alive (full-mask shuffles, no divergence bookkeeping): columns past the end of
@@ -113,8 +114,6 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
   const int u_raw = (int)(blockIdx.x * (kFuseThreads / T) + threadIdx.x / T);
   const bool live = u_raw < dv.W;
   const int u = live ? u_raw : dv.W - 1;
-  const int v = (int)blockIdx.y;
-  const unsigned hw = (unsigned)v * (unsigned)dv.W + (unsigned)u;
   const int lane = threadIdx.x & 31;
   const int t = lane & (T - 1);
   const int gbase = lane & ~(T - 1);
@@ -129,10 +128,30 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
     return q;
   };
   const int b = blockIdx.z;
-  const size_t pix = (size_t)b * HW + hw;
-  const size_t base = ((size_t)b * D + d0) * HW + hw;
   auto valid = [&](int d) -> bool { return FULL || d0 + d < D; };
 
+  // ---- what depends on the column only (lc_sense.cuh): this lane's curtain (t < nc: one sensing round covers all
+  // curtains) through this lane's column.  Once per CTA instead of once per pixel.
+  const bool col_form = nc <= T;
+  ColGeom cg;
+  cg.kind = 2;
+  if (col_form && t < nc) {
+    const float4* P4 = reinterpret_cast<const float4*>(planes + ((size_t)(b * nc + t) * dv.W + u) * 12);
+    float Pl[12];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      const float4 q = __ldg(P4 + k);
+      Pl[4 * k] = q.x; Pl[4 * k + 1] = q.y; Pl[4 * k + 2] = q.z; Pl[4 * k + 3] = q.w;
+    }
+    cg = column_geometry(Pl, dv.nn_x[u]);
+  }
+
+  const int v_end = min(dv.H, ((int)blockIdx.y + 1) * rows_per_cta);
+#pragma unroll 1
+  for (int v = (int)blockIdx.y * rows_per_cta; v < v_end; v++) {
+  const unsigned hw = (unsigned)v * (unsigned)dv.W + (unsigned)u;
+  const size_t pix = (size_t)b * HW + hw;
+  const size_t base = ((size_t)b * D + d0) * HW + hw;
   // ---- issue the volume loads first; the curtain geometry below overlaps their latency
   Col<NP> p;
   {
@@ -151,15 +170,25 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
     mine.z = 0.f; mine.den = 1.f; mine.A = 0.f; mine.Bu = 0.f;      // idle lane: never broadcast
     if (c0 + t < nc) {
       const int cu = b * nc + c0 + t;
-      const float4* P4 = reinterpret_cast<const float4*>(planes + ((size_t)cu * dv.W + u) * 12);
-      float Pl[12];
+      const float* nzp = noise ? noise + (size_t)cu * HW + hw : nullptr;
+      Ret r;
+      if (cg.kind == 0) {
+        r = sense_pixel_col(dv, cg, u, v, gt, nzp);
+      } else if (cg.kind == 1) {                             // column without a design point: no return
+        r.x = r.y = r.z = NAN;
+        r.inten = 0.f;
+        r.thick = NAN;
+      } else {
+        const float4* P4 = reinterpret_cast<const float4*>(planes + ((size_t)cu * dv.W + u) * 12);
+        float Pl[12];
 #pragma unroll
-      for (int k = 0; k < 3; k++) {
-        const float4 q = __ldg(P4 + k);
-        Pl[4 * k] = q.x; Pl[4 * k + 1] = q.y; Pl[4 * k + 2] = q.z; Pl[4 * k + 3] = q.w;
+        for (int k = 0; k < 3; k++) {
+          const float4 q = __ldg(P4 + k);
+          Pl[4 * k] = q.x; Pl[4 * k + 1] = q.y; Pl[4 * k + 2] = q.z; Pl[4 * k + 3] = q.w;
+        }
+        r = sense_pixel(dv, Pl, u, v, gt, nzp);
       }
-      const Ret r = sense_pixel(dv, Pl, u, v, gt, noise ? noise + (size_t)cu * HW + hw : nullptr);
-      mine = lik_params(r, gt, D);
+      mine = lik_params(r, gt, D, a_lut);
     }
     if (c0 == 0) {                                           // models.py:1097 (after the loads have landed)
       if (flags & 4) {
@@ -211,7 +240,7 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
       // A SENSED pixel whose sum is (nearly) flushed is skipped here too and remembered: see the fix-up below.
       bool ok = sg >= 1e-26f;
 #ifndef DPV_FUSE_NO_DENORMAL_PATH
-      if (!ok && Lkk < 0.f && Lkk > -INFINITY) slow_mask |= 1u << j;
+      slow_mask |= (unsigned)(!ok && Lkk > -INFINITY) << j;   // kk is -inf / NaN for an un-sensed pixel, else < 0
 #endif
       // m = soft * A + uni * B before its clamp at 0 (kept signed: the floor eps*sm below is positive, so
       // max(m, eps*sm) == max(max(m, 0), eps*sm)); sum(max(m, 0)) = (sum(m) + sum|m|) / 2 with sum(m) in closed form
@@ -382,6 +411,7 @@ sense_fuse_kernel(LcDeviceView dv, const float* __restrict__ vol_in, const float
   }
   const float mean = group_sum<T>((m0.x + m0.y) + (m1.x + m1.y), gmask);
   if (mean_out && t == 0 && live) mean_out[pix] = mean;
+  }  // rows of this CTA
 }
 
 }  // namespace dpv
@@ -405,11 +435,22 @@ extern "C" int lc_sense_fuse(const LcDevice* dev, const float* logp_in, const fl
   DPV_REQUIRE(B <= 65535 && dev->H <= 65535 && hw_img * 32 < (1ll << 31), "lc_sense_fuse: B=%d or image too large", B);
   cudaStream_t st = (cudaStream_t)stream;
   const int half = spread_iter == 0 ? 0 : spread_n / 2;
+  // A CTA keeps its 32 columns and walks `rows` image rows: the prologue (depth bins and mapping table into shared
+  // memory) and the column-only sheet geometry are paid once per CTA.  At most 4 rows (C2: 0.301 / 0.281 / 0.272 /
+  // 0.279 ms for 1 / 2 / 4 / 8 rows), fewer while the grid would have under ten waves of CTAs on 148 SMs x 8 resident
+  // CTAs: with five waves the last, partly filled one already costs what the longer loop saves (tuning aid:
+  // DPV_FUSE_ROWS).
+  static const int rows_env = getenv("DPV_FUSE_ROWS") ? atoi(getenv("DPV_FUSE_ROWS")) : 0;
+  int rows = rows_env > 0 ? rows_env : 4;
+  if (rows_env <= 0) {
+    const long long ctas_per_row = (long long)((dev->W * 4 + kFuseThreads - 1) / kFuseThreads) * B;
+    while (rows > 1 && ctas_per_row * ((dev->H + rows - 1) / rows) < 10ll * 148 * 8) rows >>= 1;
+  }
 #define LAUNCH4(DPT, T, HALF, FULL)                                                                                \
   sense_fuse_kernel<DPT, T, HALF, FULL>                                                                            \
-      <<<dim3((unsigned)((dev->W * T + kFuseThreads - 1) / kFuseThreads), (unsigned)dev->H, (unsigned)B),         \
-         kFuseThreads, 0, st>>>(                                                                                   \
-          dev->view, logp_in, depth, planes, noise, nc, d_candi, D, spread_iter, flags, logp_out, mean_out)
+      <<<dim3((unsigned)((dev->W * T + kFuseThreads - 1) / kFuseThreads), (unsigned)((dev->H + rows - 1) / rows), \
+              (unsigned)B), kFuseThreads, 0, st>>>(                                                                \
+          dev->view, logp_in, depth, planes, noise, nc, d_candi, D, spread_iter, flags, logp_out, mean_out, rows)
 #define LAUNCH3(DPT, T, HALF)                        \
   do {                                               \
     if (D == DPT * T) { LAUNCH4(DPT, T, HALF, true); }   \

@@ -62,8 +62,83 @@ __device__ __forceinline__ Ret sense_pixel(const LcDeviceView& dv, const float* 
       if (err < unc / 2.) inten = color;
     } else {
       float err = drange - srange;
-      float scale = (float)(err / (unc / 2.));
-      if (fabsf(err) > unc / 2.) scale = (float)(((0.f < err) - (err < 0.f)) * 1.);
+      // (float)(err / (unc / 2.)) of dprocessor.cpp:975: unc / 2 is exact, and a double-precision quotient of two
+      // floats rounded to float IS the correctly rounded float quotient (53 >= 2 * 24 + 2 bits: double rounding is
+      // innocuous for division), so the fp32 IEEE division gives the same bits without the fp64 pipe
+      const float half_unc = unc * 0.5f;
+      float scale = __fdiv_rn(err, half_unc);
+      if (fabsf(err) > half_unc) scale = (float)(((0.f < err) - (err < 0.f)) * 1.);
+      int idx = (int)(((scale + 1.) / 2.) * (dv.hit_N - 1));
+      idx = min(max(idx, 0), dv.hit_N - 1);
+      inten = dv.hit_lut[idx];
+    }
+    if (noise) {
+      inten += *noise;
+      inten = fmaxf(0.f, fminf(inten, 1.f));
+    }
+    c3 = (float)(int)(255 * inten);
+  }
+  r.x = c[0]; r.y = c[1]; r.z = c[2]; r.inten = c3;
+  return r;
+}
+
+// ---- the same image formation with its column-only part factored out --------------------------------------
+// When none of a column's three sheet planes has a y component (P[1] == P[5] == P[9] == 0: every laser that only
+// rotates about the camera's y axis, i.e. every rig lcsim simulates on this path) the ray parameters
+// t = -P3 / (P0 rx + P1 ry + P2) of util.cpp:47-52 do not depend on the image row: P1 * ry is +-0 and adding it
+// changes nothing, so the quotients below are bit for bit the ones sense_pixel forms at every pixel of the column.
+struct ColGeom {
+  float tc, tb, tt;     // ray parameter on the centre / lower / upper sheet plane
+  float c0;             // surface x = rx * tc
+  float dxf, dzf;       // (bot - top).x and .z
+  int kind;             // 0: column-only form valid, 1: no design point (no return anywhere), 2: general planes
+};
+
+__device__ __forceinline__ ColGeom column_geometry(const float* P, float rx) {
+  ColGeom g;
+  g.tc = g.tb = g.tt = g.c0 = g.dxf = g.dzf = 0.f;
+  const bool nan0 = (P[0] != P[0]) || (P[1] != P[1]) || (P[2] != P[2]) || (P[3] != P[3]);
+  bool zero12 = true;
+#pragma unroll
+  for (int k = 4; k < 12; k++) zero12 = zero12 && (P[k] == 0.f);
+  if (nan0 && zero12) { g.kind = 1; return g; }
+  if (!(P[1] == 0.f && P[5] == 0.f && P[9] == 0.f)) { g.kind = 2; return g; }
+  g.kind = 0;
+  g.tc = -P[3] / (P[0] * rx + P[2]);
+  g.tb = -P[7] / (P[4] * rx + P[6]);
+  g.tt = -P[11] / (P[8] * rx + P[10]);
+  g.c0 = rx * g.tc;
+  g.dxf = rx * g.tb - rx * g.tt;
+  g.dzf = g.tb - g.tt;
+  return g;
+}
+
+// sense_pixel for a column whose ColGeom.kind == 0 (hit_mode 1 and 0 alike)
+__device__ __forceinline__ Ret sense_pixel_col(const LcDeviceView& dv, const ColGeom& g, int u, int v, float zval,
+                                               const float* noise) {
+  Ret r;
+  const float ry = dv.nn_y[v];
+  float c[3] = {g.c0, ry * g.tc, g.tc};
+  float c3 = 0.f;
+  if (c[2] < 0 || fabs((double)c[1]) > 3.0) { c[0] = c[1] = c[2] = c3 = NAN; }      // :818-823
+  const float dyf = ry * g.tb - ry * g.tt;
+  const double dx = (double)g.dxf, dy = (double)dyf, dz = (double)g.dzf;
+  const float unc = (float)sqrt(dx * dx + dy * dy + dz * dz);                        // :884-887
+  r.thick = unc;
+  if (!(c[0] != c[0]) && !(unc != unc) && !(zval != zval)) {                         // computeDepthHits
+    float srange = sqrtf(c[0] * c[0] + c[1] * c[1] + c[2] * c[2]);
+    float drange = zval / dv.ztoramap[(size_t)v * dv.W + u];
+    float inten = 0.f;
+    if (dv.hit_mode == 0) {
+      float err = fabsf(drange - srange);
+      float color = 0;
+      if (err >= 0) color = (float)(1. - 1. * (err / (unc / 2.)));
+      if (err < unc / 2.) inten = color;
+    } else {
+      float err = drange - srange;
+      const float half_unc = unc * 0.5f;
+      float scale = __fdiv_rn(err, half_unc);
+      if (fabsf(err) > half_unc) scale = (float)(((0.f < err) - (err < 0.f)) * 1.);
       int idx = (int)(((scale + 1.) / 2.) * (dv.hit_N - 1));
       idx = min(max(idx, 0), dv.hit_N - 1);
       inten = dv.hit_lut[idx];
@@ -104,7 +179,20 @@ __device__ __forceinline__ float div255(float it) {
   return fmaf(fmaf(-255.f, q, it), rc, q);
 }
 
-__device__ __forceinline__ Lik lik_params(const Ret& r, float gt, int D) {
+// mapping(intensity / 255), light_curtain.py:228-244 (m = 20, f = 0.5) with :875's division
+__device__ __forceinline__ float mapping_of(float it) {
+  const float x = div255(it);
+  if (x > 0.5f) {
+    const float cc = (float)(20.0 / ((20.0 * 0.5 + 0.5) * (20.0 * 0.5 + 0.5)));
+    const float c1 = (float)(1.0 - 20.0 / ((20.0 * 0.5 + 0.5) * (20.0 * 0.5 + 0.5)));
+    return cc * x + c1;
+  }
+  return (1.0f / (20.f * (0.025f + x))) * -1.0f + 1.0f;
+}
+
+// a_lut: optional table of mapping_of(0..255) (the simulator's intensities are (int)(255 * i), dprocessor.cpp:990),
+// filled with mapping_of itself, so reading it is the same value without the two divisions per pixel and curtain
+__device__ __forceinline__ Lik lik_params(const Ret& r, float gt, int D, const float* a_lut = nullptr) {
   float z = r.z, th = r.thick, it = r.inten;
   if (r.x != r.x) { z = 0.f; it = 0.f; }            // light_curtain.py:847 (whole pixel -> 0)
   if (th != th) th = 0.f;                           // :848 (only where the thickness itself is NaN)
@@ -112,16 +200,10 @@ __device__ __forceinline__ Lik lik_params(const Ret& r, float gt, int D) {
   z = z * mask;
   th = th * mask;
   it = it * mask;
-  const float x = div255(it);
-  // mapping(), light_curtain.py:228-244 (m = 20, f = 0.5)
   float A;
-  if (x > 0.5f) {
-    const float cc = (float)(20.0 / ((20.0 * 0.5 + 0.5) * (20.0 * 0.5 + 0.5)));
-    const float c1 = (float)(1.0 - 20.0 / ((20.0 * 0.5 + 0.5) * (20.0 * 0.5 + 0.5)));
-    A = cc * x + c1;
-  } else {
-    A = (1.0f / (20.f * (0.025f + x))) * -1.0f + 1.0f;
-  }
+  const int ii = (int)it;
+  if (a_lut && it >= 0.f && it <= 255.f && (float)ii == it) A = a_lut[ii];
+  else A = mapping_of(it);
   Lik L;
   L.z = z;
   const float t10 = div_zero_fast(th, 10.0f);
