@@ -118,6 +118,25 @@ def check(rc):
         raise DpvError(lib().dpv_last_error().decode("utf-8", "replace") or ("dpv error %d" % rc))
 
 
+class _NoCtx:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
+_NOCTX = _NoCtx()
+
+
+def on_device(device):
+    """Context that makes `device` the current CUDA device for a launch (kernels run on the current device: a process
+    that drives several GPUs must not launch on tensors of another one); free when it already is."""
+    if device is None or device.index is None or device.index == torch.cuda.current_device():
+        return _NOCTX
+    return torch.cuda.device(device)
+
+
 def stream_ptr(device=None):
     return torch.cuda.current_stream(device).cuda_stream
 

@@ -2,6 +2,8 @@
 // Host part mirrors DatumProcessor::setSensors (external/lcsim/lcsim/src/dprocessor.cpp:41-235);
 // the per-geometry tables are computed once on the host and kept in HBM.
 #pragma once
+#include <map>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -56,12 +58,18 @@ struct LcPlanner {
   float* d_theta = nullptr;     // [W,R]
   float* d_xz = nullptr;        // [W,R,2]
   uint8_t* d_win = nullptr;     // [W,R,2] lo,hi (lo > hi = no edge); last ray has none
-  // lc_planner_solve's producer -> consumer log (grown on demand; one solve at a time per handle)
-  unsigned char* d_log = nullptr;
-  size_t log_bytes = 0;
-  // device-side solve counter {epoch, CTAs finished} of the DPV_PLANNER_DEVTAG=1 variant: a launch captured in a
-  // CUDA graph takes the tag of its log entries from it (the default clears the log with a memset node instead)
-  unsigned* d_epoch = nullptr;
-  int host_epoch = 0;           // tags of directly launched solves (kernel parameter)
-  int last_n = 0;
+  // lc_planner_solve's producer -> consumer log.  Solves issued on one stream are ordered and share a log; solves on
+  // different streams may overlap on the GPU, so each stream gets its own (grown on demand, never while that stream
+  // is being captured; freed with the handle).  The map is guarded by `mu` (the launch itself is outside the lock).
+  struct Log {
+    unsigned char* d_log = nullptr;
+    size_t log_bytes = 0;
+    // device-side solve counter {epoch, CTAs finished} of the DPV_PLANNER_DEVTAG=1 variant: a launch captured in a
+    // CUDA graph takes the tag of its log entries from it (the default clears the log with a memset node instead)
+    unsigned* d_epoch = nullptr;
+    int host_epoch = 0;         // tags of directly launched solves (kernel parameter)
+    int last_n = 0;
+  };
+  std::map<void*, Log> logs;    // keyed by cudaStream_t
+  std::mutex mu;
 };

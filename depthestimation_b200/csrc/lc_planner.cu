@@ -78,7 +78,7 @@ int lc_planner_create(const LcDevice* dev, const float* ranges, int R, LcPlanner
   }
   p->edges = edges;
   size_t smem = (size_t)6 * R * 4 + (size_t)((W + 1) & ~1) * 2 + (size_t)W * R;
-  if (smem > 227 * 1024 - 64) {
+  if (smem > 227 * 1024 - 128)   /* the solve kernel also has a few static shared words */ {
     delete p;
     dpv::set_error("lc_planner_create: W*R = %d*%d back-pointers exceed shared memory", W, R);
     return DPV_EUNSUPPORTED;
@@ -87,8 +87,6 @@ int lc_planner_create(const LcDevice* dev, const float* ranges, int R, LcPlanner
   if ((e = cudaMalloc(&p->d_theta, th.size() * 4)) != cudaSuccess ||
       (e = cudaMalloc(&p->d_xz, xz.size() * 4)) != cudaSuccess ||
       (e = cudaMalloc(&p->d_win, win.size())) != cudaSuccess ||
-      (e = cudaMalloc(&p->d_epoch, 2 * sizeof(unsigned))) != cudaSuccess ||
-      (e = cudaMemset(p->d_epoch, 0, 2 * sizeof(unsigned))) != cudaSuccess ||
       (e = cudaMemcpy(p->d_theta, th.data(), th.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess ||
       (e = cudaMemcpy(p->d_xz, xz.data(), xz.size() * 4, cudaMemcpyHostToDevice)) != cudaSuccess ||
       (e = cudaMemcpy(p->d_win, win.data(), win.size(), cudaMemcpyHostToDevice)) != cudaSuccess) {
@@ -105,8 +103,10 @@ void lc_planner_destroy(LcPlanner* p) {
   cudaFree(p->d_theta);
   cudaFree(p->d_xz);
   cudaFree(p->d_win);
-  cudaFree(p->d_log);
-  cudaFree(p->d_epoch);
+  for (auto& kv : p->logs) {
+    cudaFree(kv.second.d_log);
+    cudaFree(kv.second.d_epoch);
+  }
   delete p;
 }
 

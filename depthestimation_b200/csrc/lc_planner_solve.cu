@@ -48,6 +48,11 @@ __device__ __forceinline__ unsigned long long log_entry(float unc, int code, uns
   return (unsigned long long)__float_as_uint(unc) | ((unsigned long long)(unsigned)(code & 0xffff) << 32) |
          ((unsigned long long)tag << 48);
 }
+// Both sides of the log are strong (relaxed, gpu scope) operations, so the single-copy atomicity of an aligned
+// 8-byte access is what the PTX memory model guarantees, not an artefact of how a weak store happens to be issued.
+__device__ __forceinline__ void st_relaxed(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v));   // no clobber: the entry depends on no other memory
+}
 __device__ __forceinline__ unsigned long long ld_relaxed(const unsigned long long* p) {
   unsigned long long v;
   asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -173,9 +178,9 @@ __device__ __forceinline__ void planner_part_a(unsigned char* smraw, const float
       }
       // one lane per node appends the log entry: the owner when a single candidate exists, lane 0 otherwise
       if (!better) {
-        if (s == 0) lg[(size_t)i * RP + k] = log_entry(bu, kCodeBare, tag);
+        if (s == 0) st_relaxed(lg + (size_t)i * RP + k, log_entry(bu, kCodeBare, tag));
       } else if (owner || (s == 0 && tot >= 2)) {
-        lg[(size_t)i * RP + k] = log_entry(bu, code, tag);
+        st_relaxed(lg + (size_t)i * RP + k, log_entry(bu, code, tag));
       }
     }
     __syncthreads();                                              // ray i complete in shared memory
@@ -206,6 +211,8 @@ __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float
   uint8_t* sub = reinterpret_cast<uint8_t*>(path + ((W + 7) & ~7));   // [W][R]
   __shared__ int s_nt[3];                                         // tie counts, ring like state
   __shared__ int s_cnt;
+  __shared__ volatile int s_gaveup;                               // some wait ran out of polls: the result is void
+
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int k = threadIdx.x;                                      // node whose log entries this thread follows
   const bool node = k < R;
@@ -214,6 +221,7 @@ __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float
 
   for (int i = threadIdx.x; i < 3 * SLOT; i += blockDim.x) state[i] = ((i % SLOT) < RP) ? -INFINITY : 0.f;
   if (threadIdx.x < 3) s_nt[threadIdx.x] = 0;
+  if (threadIdx.x == 0) s_gaveup = 0;
   __syncthreads();
 
   auto load_ray = [&](int i) {                                    // may come back with an old tag: checked at use
@@ -230,11 +238,28 @@ __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float
   // Stage ray i for the step that will finish it: unc and theta into its ring slot, the node inputs, the list of
   // tie nodes.  Returns the node's code (successor | bare | tie) and theta for the thread to keep.
   auto stage_ray = [&](int i, LogRay r, int slot, int& code_out, float& th_out) {
-    if (node)                                                     // A has not got here yet: wait for this node's entry
+    if (node) {                                                   // A has not got here yet: wait for this node's entry
+      // Part B waits here on most rays (A, the producer, sets the pace), so this loop is as tight as it gets: sleep,
+      // re-read, and a poll counter in a register.  Bounded per wait: A is co-scheduled (same cluster) and produces a
+      // ray in about a microsecond; 2^15 polls (~15 ms) without the entry mean that A faulted or was never
+      // launched.  Instead of spinning the GPU forever the thread raises a flag that voids the map's result (thread 0
+      // turns the count into -1 after the last ray), takes a "bare node" entry in place of the missing one and goes
+      // on; a dead producer therefore costs one such wait per ray (W x ~15 ms), then an error -- not a hung device.
+      // Nothing about it sits in the per-ray path, and it is written the one way that keeps this kernel at 62
+      // registers: an abort check per ray cost 6 %, the same wait out of line 8 %, a separate block after the loop
+      // 10 %, filling in the remaining entries from here 11 % (each of them 64 registers); as written the bound is
+      // free (0.743 ms with it and the strong log stores, 0.758 without, 0.762 before).
+      unsigned polls = 0;
       while ((unsigned)(r.entry >> 48) != tag) {
+        if (++polls > (1u << 15)) {
+          s_gaveup = 1;
+          r.entry = log_entry(0.f, kCodeBare, tag);
+          break;
+        }
         __nanosleep(32);
         r.entry = ld_relaxed(lg + (size_t)i * RP + k);
       }
+    }
     const int code = (int)(short)(unsigned short)(r.entry >> 32);
     const int lo = (int)(r.w & 0xffu), hi = (int)(r.w >> 8);
     if (node) {
@@ -345,6 +370,7 @@ __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float
         i++;
       }
     }
+    if (s_gaveup) cnt = -1;              // a wait ran out of polls: the path is void (ks -1, points 0 below)
     s_cnt = cnt;
     if (counts) counts[map] = cnt;
   }
@@ -383,8 +409,11 @@ planner_solve_kernel(const float* __restrict__ umaps, int W, int R, const float*
   // from the host's range, and the last CTA of the grid to finish advances the counter after every CTA has read it).
   // Either way it is never 0 = "written by no solve" and differs from the previous solve's tag, whose entries are
   // the only stale ones a reader can meet (every solve rewrites all entries of its maps).
-  const unsigned tag = DEVTAG ? 32768u + (*reinterpret_cast<volatile unsigned*>(epoch) & 32767u) : host_tag;
-  if ((blockIdx.x & 1) == 0) planner_part_a<LANES, NQL>(smraw, umap, W, R, win, lg, tag);
+  const unsigned tag = DEVTAG ? 32768u + (*reinterpret_cast<volatile unsigned*>(epoch) & 32767u) : (host_tag & 0xffffu);
+  if ((blockIdx.x & 1) == 0) {
+    if (host_tag >> 31) return;                                   // test hook (DPV_PLANNER_TEST_NO_PRODUCER): A never writes
+    planner_part_a<LANES, NQL>(smraw, umap, W, R, win, lg, tag);
+  }
   else planner_part_b<RP / 128>(smraw, umap, W, R, theta, node_xz, win, lg, tag, map, ks, xz, counts);
   if (DEVTAG) {
     __syncthreads();
@@ -410,35 +439,50 @@ int launch_solve(LcPlanner* p, const float* umaps, int n, int warps, int32_t* ks
   const int W = p->W, R = p->R;
   constexpr int RP = 4 * LANES * NQL;
   DPV_REQUIRE(R <= RP, "lc_planner_solve: R=%d does not fit the %d-entry kernel", R, RP);
-  // the log A writes and B follows: grown on demand, kept in the handle
-  const size_t per_map = (size_t)W * RP;                          // entries per umap
-  if (p->log_bytes < per_map * n * 8) {
-    if (p->d_log) DPV_CUDA(cudaFree(p->d_log));
-    p->d_log = nullptr;
-    p->log_bytes = 0;
-    DPV_CUDA(cudaMalloc(&p->d_log, per_map * n * 8));
-    p->log_bytes = per_map * n * 8;
-    p->last_n = 0;
-  }
-  if (n != p->last_n) {
-    // a different number of maps than the previous solve: the regions of maps that sat out keep older tags, which a
-    // wrapped-around 16-bit tag could meet again -- back to tag 0 = "written by no solve" everywhere
-    DPV_CUDA(cudaMemsetAsync(p->d_log, 0, p->log_bytes, st));
-    p->last_n = n;
-  }
-  const size_t smem_b = (size_t)9 * RP * 4 + (size_t)2 * RP * 16 + (size_t)2 * RP * 4 + (size_t)((W + 7) & ~7) * 2 +
-                        (size_t)W * R;
-  const size_t smem_a = (size_t)2 * (RP + 2 * (RP / 4)) * 4;
-  const size_t smem = smem_a > smem_b ? smem_a : smem_b;
-  DPV_REQUIRE(smem <= 227 * 1024, "lc_planner_solve: W*R = %d*%d back-pointers exceed shared memory", W, R);
   cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
   if (cudaStreamIsCapturing(st, &cap) != cudaSuccess) {
     (void)cudaGetLastError();
     cap = cudaStreamCaptureStatusNone;
   }
   const bool capturing = cap != cudaStreamCaptureStatusNone;
-  p->host_epoch = p->host_epoch % 32767 + 1;                      // 1..32767
-  unsigned host_tag = (unsigned)p->host_epoch;
+  // the log A writes and B follows: one per stream (solves on different streams may overlap on the GPU), grown on
+  // demand, kept in the handle.  The entry in the map is only touched under the lock; its address is stable.
+  const size_t per_map = (size_t)W * RP;                          // entries per umap
+  LcPlanner::Log* lgp;
+  {
+    std::lock_guard<std::mutex> lock(p->mu);
+    lgp = &p->logs[(void*)st];
+    if (lgp->log_bytes < per_map * n * 8 || !lgp->d_epoch) {
+      // cudaMalloc / cudaFree are not allowed while the stream is being captured: size the log with one solve of
+      // this many maps before the capture (pipeline.py does: an eager step precedes every capture)
+      DPV_REQUIRE(!capturing, "lc_planner_solve: the log of this stream must grow (%d maps) but the stream is being "
+                  "captured -- run one solve of this size on it before the capture", n);
+      if (lgp->d_log) DPV_CUDA(cudaFree(lgp->d_log));
+      lgp->d_log = nullptr;
+      lgp->log_bytes = 0;
+      DPV_CUDA(cudaMalloc(&lgp->d_log, per_map * n * 8));
+      lgp->log_bytes = per_map * n * 8;
+      lgp->last_n = 0;
+      if (!lgp->d_epoch) {
+        DPV_CUDA(cudaMalloc(&lgp->d_epoch, 2 * sizeof(unsigned)));
+        DPV_CUDA(cudaMemsetAsync(lgp->d_epoch, 0, 2 * sizeof(unsigned), st));
+      }
+    }
+  }
+  LcPlanner::Log& L = *lgp;
+  if (n != L.last_n) {
+    // a different number of maps than the previous solve: the regions of maps that sat out keep older tags, which a
+    // wrapped-around 16-bit tag could meet again -- back to tag 0 = "written by no solve" everywhere
+    DPV_CUDA(cudaMemsetAsync(L.d_log, 0, L.log_bytes, st));
+    L.last_n = n;
+  }
+  const size_t smem_b = (size_t)9 * RP * 4 + (size_t)2 * RP * 16 + (size_t)2 * RP * 4 + (size_t)((W + 7) & ~7) * 2 +
+                        (size_t)W * R;
+  const size_t smem_a = (size_t)2 * (RP + 2 * (RP / 4)) * 4;
+  const size_t smem = smem_a > smem_b ? smem_a : smem_b;
+  DPV_REQUIRE(smem + 64 <= 227 * 1024,   /* + the kernel's static shared memory */ "lc_planner_solve: W*R = %d*%d back-pointers exceed shared memory", W, R);
+  L.host_epoch = L.host_epoch % 32767 + 1;                        // 1..32767
+  unsigned host_tag = (unsigned)L.host_epoch;
   // Captured in a CUDA graph the tag parameter is frozen, so every replay would meet its own previous entries as
   // valid ones.  Two ways out: clear this solve's log region inside the graph (a memset node of W*RP*8 bytes per map,
   // ~6 us at C2) and keep the parameter-tag kernel, or the device-counter variant (no memset; measured 63 us slower
@@ -448,9 +492,11 @@ int launch_solve(LcPlanner* p, const float* umaps, int n, int warps, int32_t* ks
   static const bool want_devtag = getenv("DPV_PLANNER_DEVTAG") && atoi(getenv("DPV_PLANNER_DEVTAG")) != 0;
   const bool devtag = capturing && want_devtag;
   if (capturing && !devtag) {
-    DPV_CUDA(cudaMemsetAsync(p->d_log, 0, per_map * n * 8, st));
-    host_tag = 32768u + ((unsigned)p->host_epoch & 32767u);
+    DPV_CUDA(cudaMemsetAsync(L.d_log, 0, per_map * n * 8, st));
+    host_tag = 32768u + ((unsigned)L.host_epoch & 32767u);
   }
+  if (const char* e = getenv("DPV_PLANNER_TEST_NO_PRODUCER"))    // exercises part B's bounded wait (tests only)
+    if (atoi(e) != 0 && !devtag) host_tag |= 0x80000000u;
   auto kern = devtag ? planner_solve_kernel<LANES, NQL, true> : planner_solve_kernel<LANES, NQL, false>;
   DPV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int threads = ((R * LANES + 31) / 32) * 32;                     // part A: LANES threads per node
@@ -473,7 +519,7 @@ int launch_solve(LcPlanner* p, const float* umaps, int n, int warps, int32_t* ks
   cfg.attrs = attr;
   cfg.numAttrs = 2;
   DPV_CUDA(cudaLaunchKernelEx(&cfg, kern, umaps, W, R, (const float*)p->d_theta, (const float*)p->d_xz,
-                              (const uint8_t*)p->d_win, (unsigned long long*)p->d_log, per_map, host_tag, p->d_epoch, ks, xz,
+                              (const uint8_t*)p->d_win, (unsigned long long*)L.d_log, per_map, host_tag, L.d_epoch, ks, xz,
                               counts));
   return DPV_OK;
 }

@@ -70,7 +70,7 @@ def lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n,
     src = (volume, E[d]) to read instead of the state's own buffers (the first iteration of a loop reads the caller's
     DPV and writes the state's: the caller's volume and depth map stay as they were, like the reference's
     output_refined next to output_lc)."""
-    from ._lib import check, lib, ptr, stream_ptr
+    from ._lib import check, lib, on_device, ptr, stream_ptr
     B, D, H, W, R, nc = state.shape
     dev = rig.dev
     vol_in, mean_in = (state.logp, state.mean) if src is None else src
@@ -83,8 +83,9 @@ def lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n,
     if planner_events is not None:
         p1.record()
         planner_events.append((p0, p1))
-    check(lib().lc_curtain_planes(dev._h, ptr(state.xz), ptr(state.counts), B * nc, W, ptr(state.planes), None,
-                                  stream_ptr(dev.device)))
+    with on_device(dev.device):
+        check(lib().lc_curtain_planes(dev._h, ptr(state.xz), ptr(state.counts), B * nc, W, ptr(state.planes), None,
+                                      stream_ptr(dev.device)))
     if trace is not None:
         trace.append(dict(uf=state.uf.clone(), ks=state.ks.clone().view(B, nc, W), counts=state.counts.clone(),
                           umaps=state.umaps.clone(), argmax=state.argmax.clone()))

@@ -9,7 +9,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import check, f32, lib, ptr, stream_ptr
+from ._lib import check, f32, lib, on_device, ptr, stream_ptr
 
 
 def _host_f32(a):
@@ -145,8 +145,9 @@ class LCDevice:
         design = torch.empty(n, self.W, 4, device=self.device, dtype=torch.float32) if want_design else None
         if counts is not None:
             counts = counts.to(device=self.device, dtype=torch.int32).contiguous()
-        check(lib().lc_curtain_planes(self._h, ptr(xz), ptr(counts), n, npts, ptr(planes), ptr(design),
-                                      stream_ptr(self.device)))
+        with on_device(self.device):
+            check(lib().lc_curtain_planes(self._h, ptr(xz), ptr(counts), n, npts, ptr(planes), ptr(design),
+                                          stream_ptr(self.device)))
         return (planes, design) if want_design else planes
 
     def noise_like(self, n):
@@ -161,8 +162,9 @@ class LCDevice:
         B = depth.shape[0]
         img = torch.empty(B * nc, self.H, self.W, 4, device=self.device, dtype=torch.float32)
         th = torch.empty(B * nc, self.H, self.W, device=self.device, dtype=torch.float32)
-        check(lib().lc_sense_image(self._h, ptr(planes), ptr(depth), ptr(noise), B, nc, ptr(img), ptr(th),
-                                   stream_ptr(self.device)))
+        with on_device(self.device):
+            check(lib().lc_sense_image(self._h, ptr(planes), ptr(depth), ptr(noise), B, nc, ptr(img), ptr(th),
+                                       stream_ptr(self.device)))
         return img, th
 
     def sense_likelihood(self, planes, depth, nc, d_candi, noise=None):
@@ -171,8 +173,9 @@ class LCDevice:
         B = depth.shape[0]
         dc = d_candi_tensor(d_candi, self.device)
         lik = torch.empty(B * nc, dc.numel(), self.H, self.W, device=self.device, dtype=torch.float32)
-        check(lib().lc_sense_likelihood(self._h, ptr(planes), ptr(depth), ptr(noise), B, nc, ptr(dc), dc.numel(),
-                                        ptr(lik), stream_ptr(self.device)))
+        with on_device(self.device):
+            check(lib().lc_sense_likelihood(self._h, ptr(planes), ptr(depth), ptr(noise), B, nc, ptr(dc), dc.numel(),
+                                            ptr(lik), stream_ptr(self.device)))
         return lik
 
     def sense_fuse(self, logp, depth, planes, nc, d_candi, spread_iter, spread_n, noise=None, out=None, mean=None,
@@ -185,10 +188,11 @@ class LCDevice:
         dc = d_candi_tensor(d_candi, self.device)
         out = torch.empty_like(logp) if out is None else out
         mean = torch.empty(B, self.H, self.W, device=self.device, dtype=torch.float32) if mean is None else mean
-        check(lib().lc_sense_fuse(self._h, ptr(logp), ptr(depth), ptr(planes), ptr(noise), B, nc, ptr(dc), D,
-                                  int(spread_iter), int(spread_n), (1 if in_prob else 0) | (2 if out_prob else 0) | (4 if in_clamped else 0) |
-                                  (8 if out_raw else 0),
-                                  ptr(out), ptr(mean), stream_ptr(self.device)))
+        with on_device(self.device):
+            check(lib().lc_sense_fuse(self._h, ptr(logp), ptr(depth), ptr(planes), ptr(noise), B, nc, ptr(dc), D,
+                                      int(spread_iter), int(spread_n), (1 if in_prob else 0) | (2 if out_prob else 0) | (4 if in_clamped else 0) |
+                                      (8 if out_raw else 0),
+                                      ptr(out), ptr(mean), stream_ptr(self.device)))
         return out, mean
 
     # ---- sim.LCDevice.get_return (sim.py:168-211) -----------------------------------------------
@@ -242,13 +246,16 @@ class PlannerRT:
         ks = torch.empty(n, self.W, device=self.device, dtype=torch.int32) if ks is None else ks
         xz = torch.empty(n, self.W, 2, device=self.device, dtype=torch.float32) if xz is None else xz
         counts = torch.empty(n, device=self.device, dtype=torch.int32) if counts is None else counts
-        check(lib().lc_planner_solve(self._h, ptr(umaps), n, ptr(ks), ptr(xz), ptr(counts), stream_ptr(self.device)))
+        with on_device(self.device):
+            check(lib().lc_planner_solve(self._h, ptr(umaps), n, ptr(ks), ptr(xz), ptr(counts), stream_ptr(self.device)))
         return ks, xz, counts
 
     def get_design_points(self, umap, return_indices=False):
         as_numpy = isinstance(umap, np.ndarray)
         ks, xz, counts = self.solve(f32(umap, self.device).unsqueeze(0))
         n = int(counts[0].item())
+        if n < 0:
+            raise _lib.DpvError("PlannerRT: the solve was aborted on the device (its producer never delivered: count -1)")
         xz, ks = xz[0, :n], ks[0, :n]
         if as_numpy:
             xz, ks = xz.cpu().numpy(), ks.cpu().numpy()

@@ -11,7 +11,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import check, f32, lib, ptr, stream_ptr
+from ._lib import check, f32, lib, on_device, ptr, stream_ptr
 
 _dc_cache = {}
 
@@ -51,9 +51,10 @@ def plane_sweep(ref, src, K, R, t, rays, center, d_candi, sigma, metric="L2", ou
     if out is None:
         out = torch.empty(B, D, h, w, device=dev, dtype=torch.float32)
     stride = 0 if rays.shape[0] == 1 else 3 * h * w
-    check(lib().dpv_plane_sweep(ptr(ref), ptr(src), B, V, C, h, w, ptr(K), ptr(R), ptr(t), ptr(rays), stride,
-                                ptr(center), ptr(dc), D, float(sigma), 0 if metric == "L2" else 1, ptr(out),
-                                stream_ptr(dev)))
+    with on_device(dev):
+        check(lib().dpv_plane_sweep(ptr(ref), ptr(src), B, V, C, h, w, ptr(K), ptr(R), ptr(t), ptr(rays), stride,
+                                    ptr(center), ptr(dc), D, float(sigma), 0 if metric == "L2" else 1, ptr(out),
+                                    stream_ptr(dev)))
     return out
 
 
@@ -67,8 +68,9 @@ def warp_feature(src, K, R, t, rays, center, d_candi, out=None):
     if out is None:
         out = torch.empty(B, T, D, h, w, device=dev, dtype=torch.float32)
     stride = 0 if rays.shape[0] == 1 else 3 * h * w
-    check(lib().dpv_warp_feature(ptr(src), B, T, C, h, w, ptr(K), ptr(R), ptr(t), ptr(rays), stride, ptr(center),
-                                 ptr(dc), D, ptr(out), stream_ptr(dev)))
+    with on_device(dev):
+        check(lib().dpv_warp_feature(ptr(src), B, T, C, h, w, ptr(K), ptr(R), ptr(t), ptr(rays), stride, ptr(center),
+                                     ptr(dc), D, ptr(out), stream_ptr(dev)))
     return out
 
 
@@ -84,8 +86,9 @@ def logsoftmax_stats(x, d_candi, add=None, want_var=True, want_entropy=True, wan
     var = torch.empty_like(mean) if want_var else None
     ent = torch.empty_like(mean) if want_entropy else None
     carry = torch.empty(B, D, H // 4, W // 4, device=dev, dtype=torch.float32) if want_carry else None
-    check(lib().dpv_logsoftmax_stats(ptr(x), ptr(add), B, D, H, W, ptr(dc), ptr(logp), ptr(mean), ptr(var),
-                                     ptr(ent), ptr(carry), stream_ptr(dev)))
+    with on_device(dev):
+        check(lib().dpv_logsoftmax_stats(ptr(x), ptr(add), B, D, H, W, ptr(dc), ptr(logp), ptr(mean), ptr(var),
+                                         ptr(ent), ptr(carry), stream_ptr(dev)))
     return dict(logp=logp, mean=mean, var=var, entropy=ent, carry=carry)
 
 
@@ -95,7 +98,8 @@ def expectation(dpv, d_candi, bv_log=False, out=None):
     B, D, H, W = dpv.shape
     dc = d_candi_tensor(d_candi, dev)
     mean = out if out is not None else torch.empty(B, H, W, device=dev, dtype=torch.float32)
-    check(lib().dpv_expectation(ptr(dpv), B, D, H, W, ptr(dc), int(bool(bv_log)), ptr(mean), stream_ptr(dev)))
+    with on_device(dev):
+        check(lib().dpv_expectation(ptr(dpv), B, D, H, W, ptr(dc), int(bool(bv_log)), ptr(mean), stream_ptr(dev)))
     return mean
 
 
@@ -104,7 +108,8 @@ def spread(p, N=5):
     p = f32(p, dev)
     B, D, H, W = p.shape
     out = torch.empty_like(p)
-    check(lib().dpv_spread(ptr(p), B, D, H, W, int(N), ptr(out), stream_ptr(dev)))
+    with on_device(dev):
+        check(lib().dpv_spread(ptr(p), B, D, H, W, int(N), ptr(out), stream_ptr(dev)))
     return out
 
 
@@ -113,7 +118,8 @@ def resample_depth(dpv, N, bv_log=False):
     dpv = f32(dpv, dev)
     B, D, H, W = dpv.shape
     out = torch.empty(B, int(N), H, W, device=dev, dtype=torch.float32)
-    check(lib().dpv_resample_depth(ptr(dpv), B, D, H, W, int(N), int(bool(bv_log)), ptr(out), stream_ptr(dev)))
+    with on_device(dev):
+        check(lib().dpv_resample_depth(ptr(dpv), B, D, H, W, int(N), int(bool(bv_log)), ptr(out), stream_ptr(dev)))
     return out
 
 
@@ -127,8 +133,9 @@ def bayes_fuse(logp, liks, d_candi, spread_iter, spread_n, out=None):
     dc = d_candi_tensor(d_candi, dev)
     out = out if out is not None else torch.empty_like(logp)
     mean = torch.empty(B, H, W, device=dev, dtype=torch.float32)
-    check(lib().dpv_bayes_fuse(ptr(logp), ptr(liks), n, B, D, H, W, ptr(dc), int(spread_iter), int(spread_n),
-                               ptr(out), ptr(mean), stream_ptr(dev)))
+    with on_device(dev):
+        check(lib().dpv_bayes_fuse(ptr(logp), ptr(liks), n, B, D, H, W, ptr(dc), int(spread_iter), int(spread_n),
+                                   ptr(out), ptr(mean), stream_ptr(dev)))
     return out, mean
 
 
@@ -146,8 +153,9 @@ def ufield(dpv, mean, K_up, d_candi, params, bv_log=True, mask=None, want_depth=
     dz = torch.empty(B, H, W, device=dev, dtype=torch.float32) if want_depth else None
     nbytes = int(lib().dpv_ufield_scratch_bytes(B, H, W))
     scratch = torch.empty(nbytes, device=dev, dtype=torch.uint8)      # caching allocator: no cudaMalloc per call
-    check(lib().dpv_ufield(ptr(dpv), ptr(mean), ptr(mask), B, D, H, W, ptr(dc), ptr(K_up), ctypes.byref(prm),
-                           ptr(uf), ptr(dz), scratch.data_ptr(), nbytes, stream_ptr(dev)))
+    with on_device(dev):
+        check(lib().dpv_ufield(ptr(dpv), ptr(mean), ptr(mask), B, D, H, W, ptr(dc), ptr(K_up), ctypes.byref(prm),
+                               ptr(uf), ptr(dz), scratch.data_ptr(), nbytes, stream_ptr(dev)))
     return uf, dz
 
 
@@ -164,8 +172,9 @@ def plan_prepare(uf, flow, steps, R, umaps=None, argmax=None, field_pre=None):
         argmax = torch.empty(B, W, device=dev, dtype=torch.int32)
     if field_pre is None:
         field_pre = torch.empty(B, R, W, device=dev, dtype=torch.float32)
-    check(lib().lc_plan_prepare(ptr(uf), B, D, W, int(R), ptr(flow), ctypes.cast(st, ctypes.c_void_p), n,
-                                ptr(umaps), ptr(argmax), ptr(field_pre), stream_ptr(dev)))
+    with on_device(dev):
+        check(lib().lc_plan_prepare(ptr(uf), B, D, W, int(R), ptr(flow), ctypes.cast(st, ctypes.c_void_p), n,
+                                    ptr(umaps), ptr(argmax), ptr(field_pre), stream_ptr(dev)))
     return umaps, argmax, field_pre
 
 
@@ -191,7 +200,8 @@ def plan_field(uf, flow, R, flags=7):
     B, D, W = uf.shape
     frange = torch.empty(B, int(R), W, device=dev, dtype=torch.float32)
     pre = torch.empty(B, int(R), W, device=dev, dtype=torch.float32)
-    check(lib().lc_plan_field(ptr(uf), B, D, W, int(R), ptr(flow), int(flags), ptr(frange), ptr(pre), stream_ptr(dev)))
+    with on_device(dev):
+        check(lib().lc_plan_field(ptr(uf), B, D, W, int(R), ptr(flow), int(flags), ptr(frange), ptr(pre), stream_ptr(dev)))
     return frange, pre
 
 
@@ -210,9 +220,10 @@ def plan_prepare_transformed(uf, flow_T, flow, steps, R, W_out, flags=7):
     argmax = torch.empty(B, W, device=dev, dtype=torch.int32)
     pre = torch.empty(B, R, W, device=dev, dtype=torch.float32)
     scratch = torch.empty(2, B, R, W, device=dev, dtype=torch.float32)
-    check(lib().lc_plan_prepare_transformed(ptr(uf), B, D, Win, R, W, None if flow_T is None else ptr(flow_T),
-                                            ptr(flow), ctypes.cast(st, ctypes.c_void_p), n, int(flags), ptr(umaps),
-                                            ptr(argmax), ptr(pre), ptr(scratch), stream_ptr(dev)))
+    with on_device(dev):
+        check(lib().lc_plan_prepare_transformed(ptr(uf), B, D, Win, R, W, None if flow_T is None else ptr(flow_T),
+                                                ptr(flow), ctypes.cast(st, ctypes.c_void_p), n, int(flags), ptr(umaps),
+                                                ptr(argmax), ptr(pre), ptr(scratch), stream_ptr(dev)))
     return umaps, argmax, pre
 
 
@@ -294,7 +305,7 @@ def correlation(x1, x2, pad_size, kernel_size, max_displacement, stride1, stride
     B, C, H, W = a.shape
     oc, oh, ow = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
     check(lib().dpv_correlation_shape(H, W, pad_size, kernel_size, max_displacement, stride1, stride2,
-                                      ctypes.byref(oc), ctypes.byref(oh), ctypes.byref(ow)))
+                                      ctypes.byref(oc), ctypes.byref(oh), ctypes.byref(ow)))       # host only
     out = torch.empty(B, oc.value, oh.value, ow.value, device=a.device)
     with torch.cuda.device(_dev(a)):
         check(lib().dpv_correlation(ptr(a), ptr(b), B, C, H, W, pad_size, kernel_size, max_displacement, stride1,

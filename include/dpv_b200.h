@@ -167,7 +167,11 @@ typedef struct LcPlanner LcPlanner;
 int lc_planner_create(const LcDevice* dev, const float* ranges, int R, LcPlanner** out);
 void lc_planner_destroy(LcPlanner* pl);
 long long lc_planner_edge_count(const LcPlanner* pl);
-/* umaps [n,R,W] -> ks [n,W] (range index per ray, -1 past the end), xz [n,W,2], counts [n] */
+/* umaps [n,R,W] -> ks [n,W] (range index per ray, -1 past the end), xz [n,W,2], counts [n] (design points of the
+ * path; -1 = the solve of that map was aborted on the device because its producer CTA never delivered, i.e. a fault or
+ * a failed launch: the wait is bounded instead of hanging the GPU).  Solves on one stream are ordered and share a log
+ * inside the handle; solves on different streams use separate logs and may overlap.  A log grows on the first solve of
+ * a given size on its stream: not while that stream is being captured (DPV_EINVAL; run one solve of that size first). */
 int lc_planner_solve(LcPlanner* pl, const float* umaps, int n, int32_t* ks, float* xz, int32_t* counts,
                      void* stream);
 

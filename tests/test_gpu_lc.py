@@ -300,6 +300,15 @@ def test_pipeline_step_replays_as_cuda_graph():
     eager1 = {k: v.clone() for k, v in pipe.step(x).items() if k in ("logp_lc", "depth_lc", "depth")}
     st = torch.cuda.Stream(dev)
     st.wait_stream(torch.cuda.current_stream(dev))
+    # the planner keeps one producer/consumer log per stream and will not allocate during capture: a capture stream
+    # that has never run a solve of this size is refused ...
+    with pytest.raises(Exception, match="captured"):
+        with torch.cuda.graph(torch.cuda.CUDAGraph(), stream=st):
+            pipe.step(x)
+    torch.cuda.synchronize()
+    with torch.cuda.stream(st):                            # ... so warm up on it, as torch asks of every capture anyway
+        pipe.step(x)
+    torch.cuda.synchronize()
     g = torch.cuda.CUDAGraph()
     with torch.cuda.graph(g, stream=st):
         out = pipe.step(x)
@@ -377,3 +386,62 @@ def test_planner_bit_exact_against_reference_planning_cpp(name):
         k = ks[i, :n].cpu().numpy()
         r = np.hypot(g[name + "_xz"][i, :n, 0].astype(np.float64), g[name + "_xz"][i, :n, 1].astype(np.float64))
         np.testing.assert_allclose(r, ranges[k], rtol=1e-5)
+
+
+def test_planner_one_handle_two_streams_concurrently():
+    """Solves issued on different streams through ONE PlannerRT handle may overlap on the GPU: each stream has its own
+    producer/consumer log inside the handle, so both return what a solve on its own returns."""
+    from depthestimation_b200 import lcsim
+    g = load("planner_ref")
+    name = "bench_768"
+    w, h = [int(v) for v in g[name + "_size"]]
+    cp = dict(width=w, height=h, matrix=g[name + "_K"], distortion=[0.] * 5, hit_mode=1, hit_noise=0.)
+    lp = dict(lTc=_lTc(), fov=80., laser_timestep=float(g[name + "_timestep"]))
+    pl = lcsim.PlannerRT(lcsim.LCDevice(CAMERA_PARAMS=cp, LASER_PARAMS=lp), g[name + "_ranges"], w)
+    gen = np.random.default_rng(5)
+    maps = [cu(np.round(gen.random((6, len(g[name + "_ranges"]), w)) * 8).astype(np.float32) / 8) for _ in range(2)]
+    alone = [tuple(t.clone() for t in pl.solve(m)) for m in maps]
+    torch.cuda.synchronize()
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    for rep in range(4):                                   # interleaved launches: the 12 + 12 CTA pairs share the GPU
+        got = []
+        for s_, m in zip(streams, maps):
+            with torch.cuda.stream(s_):
+                got.append(pl.solve(m))
+        torch.cuda.synchronize()
+        for (ks, xz, cnt), (eks, exz, ecnt) in zip(got, alone):
+            assert torch.equal(cnt, ecnt) and torch.equal(ks, eks) and torch.equal(xz, exz)
+
+
+def test_planner_bounded_wait_reports_instead_of_hanging():
+    """Part B's wait for the producer's log entries is bounded: launched without the producer (test hook
+    DPV_PLANNER_TEST_NO_PRODUCER) every map comes back with count -1 / indices -1 after a bounded time instead of
+    spinning on the GPU forever, the synchronous wrapper raises, and the handle solves normally afterwards."""
+    import time
+    from depthestimation_b200 import _lib, lcsim
+    g = load("lcsim_dpv_fixture")
+    W, H, R = 96, 64, 37
+    K = g["intrinsics"].copy()
+    K[0, 2], K[1, 2] = W / 2, H / 2
+    dev, odev = _devices(K, W, H, 1.0e-4)
+    r_candi = np.linspace(5.0, 40.0, R).astype(np.float32)
+    pl = lcsim.PlannerRT(dev, r_candi, W)
+    maps = cu(np.random.default_rng(1).random((3, R, W), dtype=np.float32))
+    good = tuple(t.clone() for t in pl.solve(maps))
+    torch.cuda.synchronize()
+    os.environ["DPV_PLANNER_TEST_NO_PRODUCER"] = "1"
+    try:
+        t0 = time.perf_counter()
+        ks, xz, counts = pl.solve(maps)
+        torch.cuda.synchronize()
+        waited = time.perf_counter() - t0
+        assert (counts == -1).all() and (ks == -1).all() and float(xz.abs().max()) == 0.0
+        assert waited < 20.0, waited
+        with pytest.raises(_lib.DpvError, match="aborted"):
+            pl.get_design_points(maps[0])
+    finally:
+        del os.environ["DPV_PLANNER_TEST_NO_PRODUCER"]
+    again = pl.solve(maps)
+    torch.cuda.synchronize()
+    for a, b in zip(again, good):
+        assert torch.equal(a, b)
