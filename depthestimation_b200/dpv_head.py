@@ -65,7 +65,7 @@ class LcLoopState:
 
 
 def lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n, noise=None, trace=None, events=None,
-                 in_prob=False, out_prob=False, src=None, planner_events=None):
+                 in_prob=False, out_prob=False, src=None, planner_events=None, uf_hook=None):
     """One Bayesian iteration (models.py:1027-1122) for the whole batch: 6 kernel launches, no host sync.
     src = (volume, E[d]) to read instead of the state's own buffers (the first iteration of a loop reads the caller's
     DPV and writes the state's: the caller's volume and depth map stay as they were, like the reference's
@@ -75,6 +75,8 @@ def lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n,
     dev = rig.dev
     vol_in, mean_in = (state.logp, state.mean) if src is None else src
     ops.ufield(vol_in, mean_in, K, lc.d_candi, uf_par, bv_log=not in_prob, want_depth=False, out=state.uf)
+    if uf_hook is not None:
+        uf_hook(state.uf)                        # score=True: the predicted field of this iteration, before planning
     ops.plan_prepare(state.uf, rig.flow, steps, R, state.umaps, state.argmax, state.field_pre)
     if planner_events is not None:
         p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -102,7 +104,31 @@ def lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n,
         trace[-1]["logp"] = torch.log(state.logp) if out_prob else state.logp.clone()
 
 
-def _lc_process_sweep(BV_cur_all, model_input, lc, mode, iterations, params, noise, trace):
+def _truth_field(model_input, depth, K, lc, uf_par, mode, dev):
+    """models.py:1008-1010: the uncertainty field of the ground-truth DPV (gen_dpv_withmask, variance 0.3)."""
+    if "masks" not in model_input:
+        raise Exception("lc_process(score=True) needs model_input['masks']")
+    masks = model_input["masks"].to(dev).float()
+    B = depth.shape[0]
+    if mode == "high":                                                        # :987, nearest x4 like the depth
+        masks = torch.nn.functional.interpolate(masks.reshape(B, 1, *masks.shape[-2:]), scale_factor=4, mode="nearest")
+    masks = masks.reshape(B, *depth.shape[-2:]).contiguous()
+    true_dpv = ops.truth_dpv(depth, masks, lc.d_candi, 0.3)
+    uf_truth, _ = ops.ufield(true_dpv, ops.expectation(true_dpv, lc.d_candi, False), K, lc.d_candi, uf_par, bv_log=False,
+                             want_depth=False)
+    return uf_truth
+
+
+def _score_hook(uf_truth, d_candi, unc_scores):
+    """models.py:1044-1046: compute_unc_rmse(truth, predicted) per sample, appended as a Python float (.item())."""
+    def hook(uf_pred):
+        vals = torch.stack([ops.unc_rmse(uf_truth[b], uf_pred[b], d_candi) for b in range(uf_pred.shape[0])])
+        for b, v in enumerate(vals.tolist()):                                 # one host sync per iteration
+            unc_scores[b].append(v)
+    return hook
+
+
+def _lc_process_sweep(BV_cur_all, model_input, lc, mode, iterations, params, noise, trace, score=False, cfg=None):
     """lc_process with planner == "sweep" (models.py:1054-1055; plan_sweep light_curtain.py:441-503): every iteration
     senses the same flat curtains at depths arange(start, end, step).  The curtains do not depend on the field, so
     their plane coefficients are built once and neither the uncertainty field nor the DP planner runs; the fused
@@ -132,7 +158,17 @@ def _lc_process_sweep(BV_cur_all, model_input, lc, mode, iterations, params, noi
     chunks = [planes[c:c + 8].unsqueeze(0).expand(B, -1, -1, -1).contiguous() for c in range(0, len(zs), 8)]
     mean = torch.empty(B, vol.shape[2], vol.shape[3], device=dev, dtype=torch.float32)
     first = True
+    unc_scores = [[] for _ in range(B)]
+    hook = None
+    if score:                  # the flat curtains do not need the field; the reference still builds and scores it (:1029)
+        K = model_input["intrinsics_up" if mode == "high" else "intrinsics"].to(dev).float().reshape(B, 3, 3)
+        uf_par = img_utils.uf_params(cfg if cfg is not None else "kitti")
+        hook = _score_hook(_truth_field(model_input, depth, K, lc, uf_par, mode, dev), lc.d_candi, unc_scores)
     for i in range(iterations):
+        if hook is not None:
+            cur = vol if first else torch.log(vol)
+            hook(ops.ufield(cur, ops.expectation(cur, lc.d_candi, True), K, lc.d_candi, uf_par, bv_log=True,
+                            want_depth=False)[0])
         for j, pl in enumerate(chunks):
             ncc = pl.shape[1]
             last_chunk = j == len(chunks) - 1
@@ -150,10 +186,10 @@ def _lc_process_sweep(BV_cur_all, model_input, lc, mode, iterations, params, noi
             trace.append(dict(logp=torch.log(vol) if i < iterations - 1 else vol.clone()))
     if vol.shape[1] != D_in:
         vol = ops.resample_depth(vol, D_in, bv_log=True)
-    return vol, [[] for _ in range(B)]
+    return vol, unc_scores
 
 
-def _lc_process_separate_camera(BV_cur_all, model_input, lc, mode, iterations, planner, params, cfg, trace):
+def _lc_process_separate_camera(BV_cur_all, model_input, lc, mode, iterations, planner, params, cfg, trace, score=False):
     """lc_process for an LC camera posed or sized differently from the RGB camera (rTc != I / size_lc != size_rgb):
     the fused sense+update kernel does not apply (a curtain return lands on other pixels than it was sensed on), so
     the loop is the reference's own composition (models.py:1027-1122) of GPU steps: uncertainty field -> planning field
@@ -177,9 +213,13 @@ def _lc_process_separate_camera(BV_cur_all, model_input, lc, mode, iterations, p
     D_in = final.shape[1]
     if D_in != lc.expand_A:
         final = ops.resample_depth(final, lc.expand_A, bv_log=True)
+    unc_scores = [[] for _ in range(B)]
+    hook = _score_hook(_truth_field(model_input, depth, K, lc, uf_par, mode, dev), lc.d_candi, unc_scores) if score else None
     for it in range(iterations):
         mean = ops.expectation(final, lc.d_candi, True)
         uf, _ = ops.ufield(final, mean, K, lc.d_candi, uf_par, bv_log=True, want_depth=False)
+        if hook is not None:
+            hook(uf)
         per_sample = []
         for b in range(B):
             if planner == "default":
@@ -196,7 +236,7 @@ def _lc_process_separate_camera(BV_cur_all, model_input, lc, mode, iterations, p
         final, _ = ops.bayes_fuse(final, torch.stack(per_sample), lc.d_candi, spread_iter, spread_n)
     if final.shape[1] != D_in:
         final = ops.resample_depth(final, D_in, bv_log=True)
-    return final, [[] for _ in range(B)]
+    return final, unc_scores
 
 
 def lc_process(BV_cur_all, model_input, lc, mode="low", iterations=5, viz=False, score=False, planner="default",
@@ -207,15 +247,19 @@ def lc_process(BV_cur_all, model_input, lc, mode="low", iterations=5, viz=False,
     params has .step / ["step"], spread_iter, spread_n.  noise: optional [iterations, B*nc, H, W] intensity noise
     (the reference draws unseeded N(0, 0.01)); None uses the device's hit_noise setting.
     Returns (fused log-DPV [B,D,H,W], unc_scores list) like the reference."""
+    if viz:
+        raise NotImplementedError("lc_process(viz=True) drives the reference's PCL / OpenCV viewer (models.py:1072-1094): "
+                                  "graphics, unavailable on this box")
     if planner not in ("default", "sweep"):
         raise NotImplementedError("planner %r: 'default' and 'sweep' are on the B200 path (plan_m1 is not: numpy RNG + "
                                   "alglib spline fit, DESIGN.md section 8)" % planner)
     if getattr(lc, "transform_needed", False):
-        return _lc_process_separate_camera(BV_cur_all, model_input, lc, mode, iterations, planner, params, cfg, trace)
+        return _lc_process_separate_camera(BV_cur_all, model_input, lc, mode, iterations, planner, params, cfg, trace,
+                                           score)
     get = (lambda k: params[k]) if isinstance(params, dict) else (lambda k: getattr(params, k))
     spread_iter, spread_n = int(get("spread_iter")), int(get("spread_n"))
     if planner == "sweep":
-        return _lc_process_sweep(BV_cur_all, model_input, lc, mode, iterations, params, noise, trace)
+        return _lc_process_sweep(BV_cur_all, model_input, lc, mode, iterations, params, noise, trace, score, cfg)
     steps = list(get("step"))
     dev = BV_cur_all.device
     B = BV_cur_all.shape[0]
@@ -243,6 +287,7 @@ def lc_process(BV_cur_all, model_input, lc, mode="low", iterations=5, viz=False,
         return BV_cur_all.detach().clone(), [[] for _ in range(B)]
     mean0 = ops.expectation(final, lc.d_candi, True)
     unc_scores = [[] for _ in range(B)]
+    hook = _score_hook(_truth_field(model_input, depth, K, lc, uf_par, mode, dev), lc.d_candi, unc_scores) if score else None
     for i in range(iterations):
         nz = None
         if noise is not None:
@@ -252,7 +297,7 @@ def lc_process(BV_cur_all, model_input, lc, mode="low", iterations=5, viz=False,
         # between iterations the volume stays clamped probability (no exp/log per bin); log only in and out
         # the first iteration reads the caller's volume and writes the state's (no copy, the input stays intact)
         lc_iteration(state, lc, rig, depth, K, uf_par, steps, spread_iter, spread_n, noise=nz, trace=trace,
-                     in_prob=i > 0, out_prob=i < iterations - 1, src=(final, mean0) if i == 0 else None)
+                     in_prob=i > 0, out_prob=i < iterations - 1, src=(final, mean0) if i == 0 else None, uf_hook=hook)
     out = state.logp
     if D != D_in:                                                             # :1124
         out = ops.resample_depth(out, D_in, bv_log=True)

@@ -445,3 +445,47 @@ def test_planner_bounded_wait_reports_instead_of_hanging():
     torch.cuda.synchronize()
     for a, b in zip(again, good):
         assert torch.equal(a, b)
+
+
+def test_lc_process_score_matches_oracle():
+    """lc_process(score=True) (models/models.py:1008-1010, :1044-1046): per sample and iteration,
+    compute_unc_rmse(field of the ground-truth DPV, predicted field before planning), against the oracle's
+    gen_dpv_withmask / gen_ufield / compute_unc_rmse on the oracle's own per-iteration fields."""
+    from oracle import aux_oracle as A
+    from depthestimation_b200 import dpv_head
+    g = load("light_curtain")
+    lc = _golden_lc(g)
+    H, W = g["logp"].shape[2:]
+    rng = np.random.default_rng(4)
+    masks = (rng.random((1, 1, H // 4, W // 4)) > 0.2).astype(np.float32)                 # some pixels without truth
+    mi = {"dmaps": cu(g["dmaps"]).unsqueeze(0), "intrinsics_up": cu(g["Kup"]).unsqueeze(0), "masks": cu(masks)}
+    prm = {"step": [0.5], "spread_iter": 2, "spread_n": 5}
+    fused, scores = dpv_head.lc_process(cu(g["logp"]), mi, lc, mode="high", iterations=3, score=True, params=prm,
+                                        cfg="kitti")
+    assert len(scores) == 1 and len(scores[0]) == 3 and all(isinstance(v, float) for v in scores[0])
+    # the oracle's side of it
+    olc = LO.LightCurtainOracle(g["Kup"], W, H, g["d_candi"], g["d_candi_up"])
+    depth = np.repeat(np.repeat(g["dmaps"], 4, 0), 4, 1).astype(np.float32)
+    m_up = torch.tensor(np.repeat(np.repeat(masks, 4, 2), 4, 3))
+    true_dpv = O.masked_truth_dpv(torch.tensor(depth).unsqueeze(0), m_up, g["d_candi"], 0.3)
+    par = O.uf_params("kitti")
+    uf_truth, _ = O.ufield(true_dpv, g["d_candi"], torch.tensor(g["Kup"]), par, BV_log=False)
+    otrace = []
+    exp = LO.lc_loop(torch.tensor(g["logp"]), depth, olc, g["Kup"], par, 3, [0.5], 2, 5, trace=otrace)
+    want = [float(A.unc_rmse(uf_truth, t["uf"], g["d_candi"])) for t in otrace]
+    np.testing.assert_allclose(scores[0], want, rtol=1e-4, atol=1e-5)
+    assert want[0] > 0.05                                                                   # a real score, not zeros
+    close(fused, exp, atol=1e-5)                                                            # scoring changes nothing
+    # sweep planner: same scores machinery, the field is built only to be scored
+    sw = {"start": 8.0, "end": 30.0, "step": 5.5, "spread_iter": 2, "spread_n": 5}
+    _, s2 = dpv_head.lc_process(cu(g["logp"]), mi, lc, mode="high", iterations=2, score=True, planner="sweep", params=sw,
+                                cfg="kitti")
+    ot2 = []
+    LO.lc_loop(torch.tensor(g["logp"]), depth, olc, g["Kup"], par, 2, None, 2, 5, trace=ot2, sweep=sw)
+    np.testing.assert_allclose(s2[0], [float(A.unc_rmse(uf_truth, t["uf"], g["d_candi"])) for t in ot2], rtol=1e-4,
+                               atol=1e-5)
+    with pytest.raises(NotImplementedError, match="graphics"):
+        dpv_head.lc_process(cu(g["logp"]), mi, lc, mode="high", iterations=1, viz=True, params=prm, cfg="kitti")
+    with pytest.raises(Exception, match="masks"):
+        dpv_head.lc_process(cu(g["logp"]), {k: v for k, v in mi.items() if k != "masks"}, lc, mode="high", iterations=1,
+                            score=True, params=prm, cfg="kitti")
