@@ -267,8 +267,42 @@ class LightCurtain:
         return [], self.field_visual
 
     def plan_m1_high(self, field, cfg):
-        raise NotImplementedError("plan_m1 (:505-644) draws its curtains with numpy's global RNG and lcsim's alglib "
-                                  "B-spline fit: not reproducible bit for bit, left out (DESIGN.md section 8)")
+        return list(self.plan_m1(field, self.planner_large, self.fw_large, "high", cfg, yield_mode=False))[0]
+
+    def plan_m1_low(self, field, cfg):
+        return list(self.plan_m1(field, self.planner_small, self.fw_small, "low", cfg, yield_mode=False))[0]
+
+    # ---- the generic forms the reference's *_high / *_low wrappers call (light_curtain.py:375-394): `planner` and `fw`
+    # are the objects the caller took from this instance (planner_large / fw_large ...: the rig holds them here), `kw`
+    # is the "high" / "low" string, and the result comes through a generator: with yield_mode every curtain as soon as
+    # it is planned, otherwise one (curtains, field_visual) pair.
+    planner_large = property(lambda self: self.rig("high").planner)
+    planner_small = property(lambda self: self.rig("low").planner)
+    fw_large = property(lambda self: self.rig("high"))
+    fw_small = property(lambda self: self.rig("low"))
+
+    def _generic(self, result, yield_mode):
+        pts, vis = result
+        if yield_mode:
+            for p in pts:
+                yield p
+        else:
+            yield (pts, vis)
+
+    def plan_default(self, field, planner, fw, kw, cfg, yield_mode):
+        return self._generic(self._plan_default(field, cfg, kw), yield_mode)
+
+    def plan_sweep(self, field, planner, fw, kw, cfg, yield_mode):
+        return self._generic(self._plan_sweep(field, cfg, kw), yield_mode)
+
+    def plan_empty(self, field, planner, fw, kw, cfg, yield_mode):
+        self.field_visual = self._field_visual(field, kw, 2)
+        return self._generic(([], self.field_visual), yield_mode)
+
+    def plan_m1(self, field, planner, fw, kw, cfg, yield_mode):
+        raise NotImplementedError("plan_m1 (light_curtain.py:506-644: per-column samples from numpy's global RNG, lcsim's "
+                                  "fitBSpline through them, cv2.GaussianBlur of the rasterised spline, DP on the product) "
+                                  "is not on the B200 path yet (DESIGN.md section 8)")
 
     # ---- real-sensor measurement (light_curtain.py:1076-1089) --------------------------------------
     def transform_measurement(self, output_lc, thickness_lc, rTc=None, intr_rgb=None, size_rgb=None):
@@ -319,6 +353,14 @@ class LightCurtain:
 
     def sense_low(self, depth_rgb, design_pts_lc, visualizer=None, noise=None):
         return self._sense(depth_rgb, design_pts_lc, "low", noise)
+
+    def gen_lc_dpv_approx(self, sensed_arr, std_div):
+        """light_curtain.py:1091-1104: the mixture likelihood (mapping + mixed_model) of a sensed_arr [3,H,W] =
+        (depth, intensity 0..255, thickness) with sigma = thickness / std_div.  One kernel (lc_likelihood_maps, which
+        divides the thickness by 10: the map handed over is scaled by 10 / std_div)."""
+        s = ops.f32(sensed_arr, self.device)
+        maps = torch.stack([s[0], s[1], s[2] * (10.0 / float(std_div))]).unsqueeze(0).contiguous()
+        return ops.likelihood_maps(maps, s[0].unsqueeze(0).contiguous(), 1, self.d_candi)[0]
 
     def gen_lc_dpv_true(self, sensed_arr, std_div, peak_img=None):
         """light_curtain.py:1106-1125 — likelihood of a real sensor return under the intensity model

@@ -246,3 +246,19 @@ def test_compute_unc_rmse_and_field():
     ft, fp, _ = img_utils.compute_unc_field(logp, torch.exp(logp), d, K.unsqueeze(0), cu(u["mask"]), cfg)
     close(ft, u["uf_masked"], atol=1e-5, what="truth field")
     close(fp, u["uf_kitti"], atol=1e-5, what="predicted field")
+
+
+def test_gen_lc_dpv_approx_against_oracle():
+    """LightCurtain.gen_lc_dpv_approx (lc/light_curtain.py:1091-1104): mapping + mixed_model on a sensed_arr with
+    sigma = thickness / std_div, against the oracle's mixture likelihood."""
+    from depthestimation_b200.lc.light_curtain import LightCurtain
+    g = load("aux")
+    lc = LightCurtain.__new__(LightCurtain)
+    lc.d_candi, lc.device = g["true_d"], torch.device("cuda", 0)
+    sensed = torch.tensor(g["true_sensed"])
+    for std_div in (10.0, 4.0):
+        out = lc.gen_lc_dpv_approx(sensed, std_div)
+        mask = (sensed[0] > 0).float()
+        A = O.intensity_to_weight(sensed[1] * mask / 255.0)
+        exp = O.mixed_likelihood(g["true_d"], sensed[0], (sensed[2] * mask / std_div) ** 2, A, 1.0 - A)
+        close(out, exp, rtol=1e-4, atol=1e-6, what="std_div %s" % std_div)
