@@ -25,6 +25,10 @@ void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 constexpr int kThreads = 128;
 
+// dpv_softmax_tma.cu: DPV_OK / DPV_E* when it took the call, -1 when the shape is not its case
+int logsoftmax_stats_tma(const float* x, int B, int D, int H, int W, const float* d_candi, float* logp, float* mean,
+                         float* var, float* entropy, float* carry, cudaStream_t st);
+
 // ---------------------------------------------------------------------------------------------
 // log_softmax over D (+ optional addend) with fused expectation / variance / entropy / x0.25 carry.
 // models/models.py:351,671,777 ; utils/img_utils.py:197-215 ; trainer/default_trainer.py:284,446-450
@@ -334,6 +338,12 @@ int dpv_logsoftmax_stats(const float* x, const float* add, int B, int D, int H, 
   cudaStream_t st = (cudaStream_t)stream;
   const long long npix = (long long)B * H * W, hw_img = (long long)H * W;
   DPV_REQUIRE(B <= 65535 && hw_img * 32 < (1ll << 31), "dpv_logsoftmax_stats: B=%d or image too large", B);
+  // full-resolution volumes (D = 64 / 128, no addend, rows of at least 32 pixels): the TMA-tiled kernel
+  // (dpv_softmax_tma.cu); anything else, or DPV_LSM_TMA=0, takes the register-column kernels below
+  if (add == nullptr) {
+    const int rc = logsoftmax_stats_tma(x, B, D, H, W, d_candi, logp, mean, var, entropy, carry, st);
+    if (rc >= 0) return rc;
+  }
   const unsigned g = blocks_for(npix, kThreads);
 #define LAUNCH(DPT, T)                                                                                       \
   do {                                                                                                          \
