@@ -70,6 +70,20 @@ class FrameOutputCollector:
             if self.comm is None:
                 self.comm = torch.cuda.Stream(t.device)
 
+    def reserve(self, out):
+        """Allocates every buffer for outputs shaped like `out` now (so that no cudaMalloc -- which synchronises the
+        whole device -- happens inside a timed region) and returns self."""
+        for k in self.keys:
+            t = out.get(k)
+            if t is not None and k not in self.buf:
+                self._alloc(k, t)
+        return self
+
+    def reset(self):
+        """Forget the recorded steps, keep the buffers."""
+        self.count = 0
+        return self
+
     def add(self, out):
         """Copies this step's maps into the rank-local buffer (on the current stream) and queues their gather."""
         i = self.count % self.n_steps
