@@ -43,6 +43,10 @@ def parse():
                          "N = 1 against 3.41-3.53 ms kernel by kernel, and several ranks on one host need it)")
     ap.add_argument("--hit-noise", type=float, default=0.01,
                     help="sigma of the simulator's intensity noise (the reference hard-codes 0.01, lc/light_curtain.py:270-285)")
+    ap.add_argument("--gather", default="round", choices=["round", "step", "end", "none"],
+                    help="exchange of the per-frame depth maps between ranks: one all_gather per round of S steps on a "
+                         "side stream (default), one per step, one after the last step, or none (diagnostic only: the "
+                         "path requires the exchange)")
     ap.add_argument("--streams", type=int, default=6,
                     help="independent batches in flight (steps are issued round-robin on this many CUDA streams)")
     return ap.parse_args()
@@ -218,7 +222,8 @@ def run_b200(args):
         """One collector per step count, its buffers allocated on first use (always outside the timed region: the
         same step count is run untimed first) and reused after that."""
         if n not in collectors:
-            collectors[n] = sharding.FrameOutputCollector(n, world).reserve(sample_out)
+            collectors[n] = sharding.FrameOutputCollector(n, world if args.gather != "none" else 1,
+                                                          chunk={"round": S, "step": 1}.get(args.gather, 0)).reserve(sample_out)
         return collectors[n].reset()
 
     def run_steps(n, step_events=None):
@@ -400,7 +405,10 @@ def run_b200(args):
                            "curtains_per_iteration": 1 + 2 * len(meta["step"]), "hit_noise": hit_noise,
                            "noise": "pre-generated pool per batch slot" if hit_noise > 0 else "none",
                            "parallelism": "batch-shard x%d" % world, "streams_in_flight": S, "launch": launch_mode,
-                           "gather": "per-step all_gather on a side stream" if world > 1 else "none (1 rank)",
+                           "gather": ({"round": "one all_gather per round of %d steps on a side stream" % S,
+                                       "step": "per-step all_gather on a side stream", "end": "one all_gather after "
+                                       "the last step", "none": "DISABLED (diagnostic run)"}[args.gather]
+                                      if world > 1 else "none (1 rank)"),
                            "rank_cores": None if cores is None else len(cores),
                            "l2_policy": "inputs larger than L2 (0.9 GB streamed per frame)"},
                 "clocks": clk_summary, "e2e": e2e, "gpu_launches": launches, "roofline": roof, "cpu_baseline": cpu,
@@ -432,7 +440,7 @@ def run_e2e(args, pipes, streams, host, xs, graphs, dev, world, B, keys, sync, s
         for st in streams:
             st.wait_event(start)
         if n not in e2e_coll:
-            e2e_coll[n] = sharding.FrameOutputCollector(n, world).reserve(graphs[0][1] if graphs is not None else pipes[0].step(xs[0]))
+            e2e_coll[n] = sharding.FrameOutputCollector(n, world, chunk=S).reserve(graphs[0][1] if graphs is not None else pipes[0].step(xs[0]))
         coll = e2e_coll[n].reset()
         for i in range(n):
             sl = i % S
