@@ -30,6 +30,8 @@ SIGNATURES = {
     "dpv_launch_count": (c_ll, []),
     "dpv_plane_sweep": (c_int, [c_fp, c_fp, c_int, c_int, c_int, c_int, c_int, c_fp, c_fp, c_fp, c_fp, c_ll, c_fp,
                                 c_fp, c_int, c_f, c_int, c_fp, c_vp]),
+    "dpv_plane_sweep_strided": (c_int, [c_fp, c_ll, c_fp, c_ll, c_int, c_int, c_int, c_int, c_int, c_fp, c_fp, c_ll, c_fp,
+                                        c_ll, c_fp, c_ll, c_fp, c_fp, c_int, c_f, c_int, c_fp, c_vp]),
     "dpv_warp_feature": (c_int, [c_fp, c_int, c_int, c_int, c_int, c_int, c_fp, c_fp, c_fp, c_fp, c_ll, c_fp, c_fp,
                                  c_int, c_fp, c_vp]),
     "dpv_logsoftmax_stats": (c_int, [c_fp, c_fp, c_int, c_int, c_int, c_int, c_fp, c_fp, c_fp, c_fp, c_fp, c_fp,
@@ -66,6 +68,7 @@ SIGNATURES = {
     "lc_transform_points_scratch_bytes": (ctypes.c_size_t, [c_int, c_int, c_int, c_int]),
     "lc_transform_points": (c_int, [c_fp, c_fp, c_int, c_int, c_fp, c_fp, c_int, c_int, c_int, c_fp, c_vp,
                                     ctypes.c_size_t, c_vp]),
+    "dpv_upsample_nearest": (c_int, [c_fp, c_int, c_int, c_int, c_int, c_fp, c_vp]),
     "lc_depth_to_points": (c_int, [c_fp, c_int, c_int, c_int, c_fp, c_f, c_fp, c_vp]),
     "lc_likelihood_maps": (c_int, [c_fp, c_fp, c_int, c_int, c_int, c_int, c_fp, c_int, c_fp, c_vp]),
     "lc_sweep_sample": (c_int, [c_fp, c_fp, c_fp, c_int, c_int, c_int, c_int, c_int, c_fp, c_ip, c_vp]),

@@ -159,10 +159,6 @@ sweep_sample_kernel(const float* __restrict__ sdepth, const float* __restrict__ 
   }
 }
 
-}  // namespace dpv
-
-using namespace dpv;
-
 // utils/img_utils.py:269-293 depth_to_pts, written straight into the [N,4] point layout transformPoints consumes
 // (lc/light_curtain.py:826-830 builds it with a cat and a transpose): ((u - cx) / fx * d, (v - cy) / fy * d, d, w).
 __global__ void __launch_bounds__(kRealThreads)
@@ -177,7 +173,33 @@ depth_to_points_kernel(const float* __restrict__ depth, long long npix, int H, i
   pts[i] = make_float4(__fmul_rn(xf, d), __fmul_rn(yf, d), d, w4);
 }
 
+// F.interpolate(depth, scale_factor=s, mode='nearest') of the ground-truth depth (models/models.py:986,
+// lc/light_curtain.py callers): dst (y, x) <- src (y / s, x / s) for an integer factor.
+__global__ void __launch_bounds__(kRealThreads)
+upsample_nearest_kernel(const float* __restrict__ in, long long nout, int h, int w, int s, float* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nout) return;
+  const int W = w * s, H = h * s;
+  const int x = (int)(i % W);
+  const long long r = i / W;
+  const int y = (int)(r % H);
+  const long long n = r / H;
+  out[i] = in[(n * h + y / s) * w + x / s];
+}
+
+}  // namespace dpv
+
+using namespace dpv;
+
 extern "C" {
+
+int dpv_upsample_nearest(const float* in, int n, int h, int w, int scale, float* out, void* stream) {
+  DPV_REQUIRE(in && out, "dpv_upsample_nearest: null pointer");
+  DPV_REQUIRE(n > 0 && h > 0 && w > 0 && scale >= 1, "dpv_upsample_nearest: bad shape n=%d h=%d w=%d scale=%d", n, h, w, scale);
+  const long long nout = (long long)n * h * w * scale * scale;
+  upsample_nearest_kernel<<<real_blocks(nout), kRealThreads, 0, (cudaStream_t)stream>>>(in, nout, h, w, scale, out);
+  return check_launch("dpv_upsample_nearest");
+}
 
 int lc_depth_to_points(const float* depth, int n, int H, int W, const float* intr, float w4, float* pts, void* stream) {
   DPV_REQUIRE(depth && intr && pts, "lc_depth_to_points: null pointer");

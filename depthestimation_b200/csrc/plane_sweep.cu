@@ -13,6 +13,12 @@
 
 namespace dpv {
 
+// element strides between the batch items of ref / src / R / t: the inputs may be views into larger tensors
+// (models/models.py:607-617 takes the reference and source views out of one [B,T,C,h,w] feature tensor)
+struct SweepStrides {
+  long long ref_b, src_b, R_b, t_b;
+};
+
 struct Taps {
   int o00, o01, o10, o11;
   float w00, w01, w10, w11;
@@ -143,7 +149,7 @@ __global__ void __launch_bounds__(128)
 plane_sweep_kernel(const float* __restrict__ ref, const float* __restrict__ src, int V, int C, int h, int w,
                    const float* __restrict__ K, const float* __restrict__ R, const float* __restrict__ t,
                    const float* __restrict__ rays, long long rays_bstride, const float* __restrict__ center,
-                   const float* __restrict__ d_candi, int D, float sigma, float* __restrict__ cost) {
+                   const float* __restrict__ d_candi, int D, float sigma, float* __restrict__ cost, SweepStrides sd) {
   const int hw = h * w;
   const int pix = blockIdx.x * blockDim.x + threadIdx.x;
   const int d0 = blockIdx.y * DC;
@@ -155,16 +161,16 @@ plane_sweep_kernel(const float* __restrict__ ref, const float* __restrict__ src,
   float acc[DC];
 #pragma unroll
   for (int j = 0; j < DC; j++) acc[j] = 0.f;
-  const float* refp = ref + (size_t)b * C * hw + pix;
+  const float* refp = ref + (size_t)b * sd.ref_b + pix;
   for (int v = 0; v < V; v++) {
     float M[9], kt[3], krp[3];
-    pose_terms(K + b * 9, R + ((size_t)b * V + v) * 9, t + ((size_t)b * V + v) * 3, M, kt);
+    pose_terms(K + b * 9, R + (size_t)b * sd.R_b + v * 9, t + (size_t)b * sd.t_b + v * 3, M, kt);
 #pragma unroll
     for (int i = 0; i < 3; i++) krp[i] = fmaf(M[i * 3 + 2], r2, fmaf(M[i * 3 + 1], r1, M[i * 3 + 0] * r0));
     Taps T[DC];
 #pragma unroll
     for (int j = 0; j < DC; j++) T[j] = make_taps(kt, krp, d_candi[min(d0 + j, D - 1)], cu, cv, h, w);
-    const float* sp = src + ((size_t)b * V + v) * C * hw;
+    const float* sp = src + (size_t)b * sd.src_b + (size_t)v * C * hw;
     float dist[DC];
 #pragma unroll
     for (int j = 0; j < DC; j++) dist[j] = 0.f;
@@ -201,7 +207,7 @@ __global__ void __launch_bounds__(128, DPV_SWEEP_MINB)
 plane_sweep_block_kernel(const float* __restrict__ ref, const float* __restrict__ src, int V, int C, int h, int w,
                    const float* __restrict__ K, const float* __restrict__ R, const float* __restrict__ t,
                    const float* __restrict__ rays, long long rays_bstride, const float* __restrict__ center,
-                   const float* __restrict__ d_candi, int D, float sigma, float* __restrict__ cost) {
+                   const float* __restrict__ d_candi, int D, float sigma, float* __restrict__ cost, SweepStrides sd) {
   const int hw = h * w;
   const int pix = blockIdx.x * blockDim.x + threadIdx.x;
   const int d0 = blockIdx.y * DC;
@@ -213,16 +219,16 @@ plane_sweep_block_kernel(const float* __restrict__ ref, const float* __restrict_
   float acc[DC];
 #pragma unroll
   for (int j = 0; j < DC; j++) acc[j] = 0.f;
-  const float* refp = ref + (size_t)b * C * hw + pix;
+  const float* refp = ref + (size_t)b * sd.ref_b + pix;
   for (int v = 0; v < V; v++) {
     float M[9], kt[3], krp[3];
-    pose_terms(K + b * 9, R + ((size_t)b * V + v) * 9, t + ((size_t)b * V + v) * 3, M, kt);
+    pose_terms(K + b * 9, R + (size_t)b * sd.R_b + v * 9, t + (size_t)b * sd.t_b + v * 3, M, kt);
 #pragma unroll
     for (int i = 0; i < 3; i++) krp[i] = fmaf(M[i * 3 + 2], r2, fmaf(M[i * 3 + 1], r1, M[i * 3 + 0] * r0));
     TapsB T[DC];
 #pragma unroll
     for (int j = 0; j < DC; j++) T[j] = make_taps_block(kt, krp, d_candi[min(d0 + j, D - 1)], cu, cv, h, w);
-    const float* sp = src + ((size_t)b * V + v) * C * hw;
+    const float* sp = src + (size_t)b * sd.src_b + (size_t)v * C * hw;
     float dist[DC];
 #pragma unroll
     for (int j = 0; j < DC; j++) dist[j] = 0.f;
@@ -272,13 +278,17 @@ using namespace dpv;
 
 extern "C" {
 
-int dpv_plane_sweep(const float* ref, const float* src, int B, int V, int C, int h, int w, const float* K,
-                    const float* R, const float* t, const float* rays, long long rays_batch_stride,
-                    const float* center, const float* d_candi, int D, float sigma, int metric, float* cost,
-                    void* stream) {
+int dpv_plane_sweep_strided(const float* ref, long long ref_batch_stride, const float* src, long long src_batch_stride,
+                            int B, int V, int C, int h, int w, const float* K, const float* R, long long R_batch_stride,
+                            const float* t, long long t_batch_stride, const float* rays, long long rays_batch_stride,
+                            const float* center, const float* d_candi, int D, float sigma, int metric, float* cost,
+                            void* stream) {
   DPV_REQUIRE(ref && src && K && R && t && rays && center && d_candi && cost, "dpv_plane_sweep: null pointer");
   DPV_REQUIRE(B > 0 && V > 0 && C > 0 && h > 0 && w > 0 && D > 0, "dpv_plane_sweep: bad shape");
   DPV_REQUIRE(B <= 65535, "dpv_plane_sweep: B=%d > 65535", B);
+  DPV_REQUIRE(ref_batch_stride >= (long long)C * h * w && src_batch_stride >= (long long)V * C * h * w &&
+              R_batch_stride >= 9ll * V && t_batch_stride >= 3ll * V, "dpv_plane_sweep: batch strides overlap the items");
+  const SweepStrides sd = {ref_batch_stride, src_batch_stride, R_batch_stride, t_batch_stride};
   // homography.py:84-86: raise Exception('undefined metric for feature distance ...')
   DPV_REQUIRE(metric == 0 || metric == 1, "undefined metric for feature distance ...");
   cudaStream_t st = (cudaStream_t)stream;
@@ -291,17 +301,25 @@ int dpv_plane_sweep(const float* ref, const float* src, int B, int V, int C, int
   if (block_taps && w >= 2 && h >= 2) {
     if (metric == 0)
       plane_sweep_block_kernel<DC, 0><<<grid, 128, 0, st>>>(ref, src, V, C, h, w, K, R, t, rays, rays_batch_stride,
-                                                           center, d_candi, D, sigma, cost);
+                                                           center, d_candi, D, sigma, cost, sd);
     else
       plane_sweep_block_kernel<DC, 1><<<grid, 128, 0, st>>>(ref, src, V, C, h, w, K, R, t, rays, rays_batch_stride,
-                                                           center, d_candi, D, sigma, cost);
+                                                           center, d_candi, D, sigma, cost, sd);
   } else if (metric == 0)
     plane_sweep_kernel<DC, 0><<<grid, 128, 0, st>>>(ref, src, V, C, h, w, K, R, t, rays, rays_batch_stride, center,
-                                                   d_candi, D, sigma, cost);
+                                                   d_candi, D, sigma, cost, sd);
   else
     plane_sweep_kernel<DC, 1><<<grid, 128, 0, st>>>(ref, src, V, C, h, w, K, R, t, rays, rays_batch_stride, center,
-                                                   d_candi, D, sigma, cost);
+                                                   d_candi, D, sigma, cost, sd);
   return check_launch("dpv_plane_sweep");
+}
+
+int dpv_plane_sweep(const float* ref, const float* src, int B, int V, int C, int h, int w, const float* K,
+                    const float* R, const float* t, const float* rays, long long rays_batch_stride,
+                    const float* center, const float* d_candi, int D, float sigma, int metric, float* cost,
+                    void* stream) {
+  return dpv_plane_sweep_strided(ref, (long long)C * h * w, src, (long long)V * C * h * w, B, V, C, h, w, K, R, 9ll * V, t,
+                                 3ll * V, rays, rays_batch_stride, center, d_candi, D, sigma, metric, cost, stream);
 }
 
 int dpv_warp_feature(const float* src, int B, int T, int C, int h, int w, const float* K, const float* R,

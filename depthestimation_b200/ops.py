@@ -37,13 +37,27 @@ def _dev(t):
     return t.device
 
 
+def _batch_view(x, dev):
+    """fp32 CUDA tensor whose items are dense but whose batch stride may be larger (a slice of a bigger tensor along
+    dim 1, like feat_all[:, -1] or R[:, :-1]): -> (tensor, batch stride in elements) without copying; anything else is
+    made contiguous."""
+    if torch.is_tensor(x) and x.is_cuda and x.dtype == torch.float32 and x.device == dev and x.dim() >= 2:
+        inner = x[0]
+        if inner.is_contiguous() and (x.shape[0] == 1 or x.stride(0) >= inner.numel()):
+            return x.detach(), int(x.stride(0)) if x.shape[0] > 1 else int(inner.numel())
+    x = f32(x, dev)
+    return x, int(x[0].numel())
+
+
 def plane_sweep(ref, src, K, R, t, rays, center, d_candi, sigma, metric="L2", out=None):
     """ref [B,C,h,w], src [B,V,C,h,w], K [B,3,3], R [B,V,3,3], t [B,V,3], rays [B|1,3,h*w], center [B,2]
-    -> cost [B,D,h,w]  (est_swp_volume_v4, warping/homography.py:98-135)."""
+    -> cost [B,D,h,w]  (est_swp_volume_v4, warping/homography.py:98-135).  ref / src / R / t may be views with a
+    larger batch stride (e.g. feat_all[:, -1], feat_all[:, :-1], R[:, :-1]): they are read in place."""
     if metric not in ("L2", "L1"):
         raise Exception("undefined metric for feature distance ...")     # homography.py:84-86
     dev = _dev(ref)
-    ref, src, K, R, t, rays, center = (f32(x, dev) for x in (ref, src, K, R, t, rays, center))
+    (ref, ref_bs), (src, src_bs), (R, R_bs), (t, t_bs) = (_batch_view(x, dev) for x in (ref, src, R, t))
+    K, rays, center = (f32(x, dev) for x in (K, rays, center))
     B, C, h, w = ref.shape
     V = src.shape[1]
     dc = d_candi_tensor(d_candi, dev)
@@ -52,9 +66,10 @@ def plane_sweep(ref, src, K, R, t, rays, center, d_candi, sigma, metric="L2", ou
         out = torch.empty(B, D, h, w, device=dev, dtype=torch.float32)
     stride = 0 if rays.shape[0] == 1 else 3 * h * w
     with on_device(dev):
-        check(lib().dpv_plane_sweep(ptr(ref), ptr(src), B, V, C, h, w, ptr(K), ptr(R), ptr(t), ptr(rays), stride,
-                                    ptr(center), ptr(dc), D, float(sigma), 0 if metric == "L2" else 1, ptr(out),
-                                    stream_ptr(dev)))
+        check(lib().dpv_plane_sweep_strided(ref.data_ptr(), ref_bs, src.data_ptr(), src_bs, B, V, C, h, w, ptr(K),
+                                            R.data_ptr(), R_bs, t.data_ptr(), t_bs, ptr(rays), stride, ptr(center),
+                                            ptr(dc), D, float(sigma), 0 if metric == "L2" else 1, ptr(out),
+                                            stream_ptr(dev)))
     return out
 
 
@@ -90,6 +105,18 @@ def logsoftmax_stats(x, d_candi, add=None, want_var=True, want_entropy=True, wan
         check(lib().dpv_logsoftmax_stats(ptr(x), ptr(add), B, D, H, W, ptr(dc), ptr(logp), ptr(mean), ptr(var),
                                          ptr(ent), ptr(carry), stream_ptr(dev)))
     return dict(logp=logp, mean=mean, var=var, entropy=ent, carry=carry)
+
+
+def upsample_nearest(x, scale=4, out=None):
+    """x [n,h,w] -> [n,h*scale,w*scale], nearest (F.interpolate(scale_factor=scale, mode='nearest'), models.py:986)."""
+    dev = _dev(x)
+    x = f32(x, dev)
+    n, h, w = x.shape
+    if out is None:
+        out = torch.empty(n, h * scale, w * scale, device=dev, dtype=torch.float32)
+    with on_device(dev):
+        check(lib().dpv_upsample_nearest(ptr(x), n, h, w, int(scale), ptr(out), stream_ptr(dev)))
+    return out
 
 
 def expectation(dpv, d_candi, bv_log=False, out=None):

@@ -148,6 +148,7 @@ class DpvLcPipeline:
                 gen = torch.Generator(device=self.device).manual_seed(noise_seed)
                 self.noise_pool = torch.randn(meta["iterations"], meta["B"] * nc, H, W, device=self.device,
                                               generator=gen) * hit_noise
+        self._center, self._center_key = None, None
         self.fuse_events = None          # optional list collecting (start, end) CUDA events of sense+fuse launches
         self.planner_events = None       # the same for the DP planner solves
         self.trace = None                # optional list: per-iteration uf / umaps / ks / logp clones (parity tests)
@@ -156,7 +157,13 @@ class DpvLcPipeline:
         """x: dict of CUDA tensors (synthetic_batch layout) -> dict(depth, var, entropy, carry, carry_lc, logp_lc)."""
         m, d = self.m, self.m["d_candi"]
         T = x["feat_all"].shape[1]
-        center = x["K"][:, :2, 2].contiguous()
+        # the principal point per frame: a function of the intrinsics only, computed once per K tensor (not per step)
+        # (inside a CUDA-graph capture it is always recomputed, so that a replay follows an in-place change of K)
+        key = (x["K"].data_ptr(), x["K"]._version)
+        if self._center_key != key or torch.cuda.is_current_stream_capturing():
+            self._center, self._center_key = x["K"][:, :2, 2].contiguous(), key
+        center = self._center
+        # reference = last view, sources = the others (models.py:607-617): views of feat_all / R / t, read in place
         cost = ops.plane_sweep(x["feat_all"][:, -1], x["feat_all"][:, :-1], x["K"], x["R"][:, :-1], x["t"][:, :-1],
                                x["rays"], center, d, self.sigma, "L2")
         bv = ops.logsoftmax_stats(cost, d, want_var=False, want_entropy=False)["logp"]   # conv0.. are cuDNN, skipped
@@ -181,7 +188,7 @@ class DpvLcPipeline:
         m, lc, st = self.m, self.lc, self.state
         rig = lc.rig("high")
         K = mi["intrinsics_up"]
-        depth = torch.nn.functional.interpolate(mi["dmaps"].unsqueeze(1), scale_factor=4, mode="nearest").squeeze(1)
+        depth = ops.upsample_nearest(mi["dmaps"], 4)                 # models.py:986
         uf_par = img_utils.uf_params(m["dataset"])
         # The first iteration reads the refined DPV / depth the log-softmax kernel wrote and writes the loop's own
         # volume; later iterations run in place on that.  out["logp"] / out["depth"] (the reference's output_refined,

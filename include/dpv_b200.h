@@ -44,6 +44,15 @@ int dpv_plane_sweep(const float* ref, const float* src, int B, int V, int C, int
                     long long rays_batch_stride, const float* center, const float* d_candi, int D,
                     float sigma, int metric, float* cost, void* stream);
 
+/* The same with explicit element strides between batch items, for inputs that are views into larger tensors: the
+ * reference takes both views out of one [B,T,C,h,w] feature tensor (models/models.py:607-617: ref = [:, -1],
+ * src = [:, :-1]) and the poses out of [B,T,3,3] / [B,T,3].  Within an item the layout is dense. */
+int dpv_plane_sweep_strided(const float* ref, long long ref_batch_stride, const float* src, long long src_batch_stride,
+                            int B, int V, int C, int h, int w, const float* K, const float* R, long long R_batch_stride,
+                            const float* t, long long t_batch_stride, const float* rays, long long rays_batch_stride,
+                            const float* center, const float* d_candi, int D, float sigma, int metric, float* cost,
+                            void* stream);
+
 /* warping/homography.py:137-168 warp_feature: out[b,v,i] = warp of channel i of view v onto plane i.
  *   src [B,T,C,h,w] with C >= D  ->  out [B,T,D,h,w]   (reference requires C == D) */
 int dpv_warp_feature(const float* src, int B, int T, int C, int h, int w, const float* K,
@@ -221,6 +230,9 @@ size_t lc_transform_points_scratch_bytes(int n, int width, int height, int filte
 int lc_transform_points(const float* pts, const float* thick, int n, int N, const float* intr, const float* M,
                         int width, int height, int filtering, float* maps, void* scratch, size_t scratch_bytes,
                         void* stream);
+/* F.interpolate(x, scale_factor=scale, mode='nearest') for an integer factor (the ground-truth depth of mode "high",
+ * models/models.py:986): in [n,h,w] -> out [n,h*scale,w*scale], out(y,x) = in(y/scale, x/scale). */
+int dpv_upsample_nearest(const float* in, int n, int h, int w, int scale, float* out, void* stream);
 /* img_utils.depth_to_pts (utils/img_utils.py:269-293) in the point layout lc_transform_points takes
  * (lc/light_curtain.py:826-830 concatenates a row of ones and transposes): depth [n,H,W], intr host[3x3]
  *   -> pts [n,H*W,4] = ((u - cx) / fx * d, (v - cy) / fy * d, d, w4). */

@@ -193,3 +193,24 @@ def test_bayes_fuse():
         close(mean[b:b + 1], O.dpv_expectation(exp, d, True), atol=1e-5)
     out3, _ = ops.bayes_fuse(logp.cuda(), liks.cuda(), d, 1, 3)
     close(out3[:1], O.bayes_fuse(logp[:1], [liks[0, i] for i in range(n)], 1, 3), atol=1e-5)
+
+
+def test_plane_sweep_reads_views_in_place_and_upsample_nearest():
+    """dpv_plane_sweep_strided: the reference / source views of one [B,T,C,h,w] tensor and the pose slices are read in
+    place (no copies) and give exactly what the dense entry point gives on contiguous copies; dpv_upsample_nearest
+    equals F.interpolate(scale_factor=4, mode='nearest')."""
+    from depthestimation_b200 import _lib, ops
+    from depthestimation_b200.pipeline import synthetic_batch
+    host, meta = synthetic_batch("tiny", seed=9)
+    x = {k: v.cuda() for k, v in host.items()}
+    center = x["K"][:, :2, 2].contiguous()
+    d = meta["d_candi"]
+    n0 = _lib.launch_count()
+    got = ops.plane_sweep(x["feat_all"][:, -1], x["feat_all"][:, :-1], x["K"], x["R"][:, :-1], x["t"][:, :-1], x["rays"],
+                          center, d, 10.0, "L2")
+    assert _lib.launch_count() - n0 == 1
+    dense = ops.plane_sweep(x["feat_all"][:, -1].contiguous(), x["feat_all"][:, :-1].contiguous(), x["K"],
+                            x["R"][:, :-1].contiguous(), x["t"][:, :-1].contiguous(), x["rays"], center, d, 10.0, "L2")
+    assert torch.equal(got, dense)
+    up = ops.upsample_nearest(x["dmaps"], 4)
+    assert torch.equal(up, torch.nn.functional.interpolate(x["dmaps"].unsqueeze(1), scale_factor=4, mode="nearest").squeeze(1))
