@@ -56,6 +56,7 @@ SIGNATURES = {
     "lc_device_angles": (c_int, [c_vp, c_fp]),
     "lc_device_hit_lut": (c_int, [c_vp, c_fp]),
     "lc_camera_angles": (c_int, [c_fp, c_int, c_int, c_fp]),
+    "lc_fit_bspline": (c_int, [c_fp, c_int, c_fp, c_ll, ctypes.POINTER(c_ll)]),
     "lc_planner_create": (c_int, [c_vp, c_fp, c_int, ctypes.POINTER(c_vp)]),
     "lc_planner_destroy": (None, [c_vp]),
     "lc_planner_edge_count": (c_ll, [c_vp]),

@@ -51,7 +51,7 @@ FUNCTION_PATCHES = [
 ]
 
 # the compiled lcsim modules of lc/light_curtain.py:11-13 -> names taken from depthestimation_b200.lcsim
-LCSIM_MODULES = {"sim": ("LCDevice",), "planner": ("PlannerRT",), "pylc_lib": ("generateCameraAngles", "transformPoints")}
+LCSIM_MODULES = {"sim": ("LCDevice",), "planner": ("PlannerRT",), "pylc_lib": ("generateCameraAngles", "transformPoints", "fitBSpline", "SplineParamsVec")}
 
 _installed = []          # (object, attribute, previous value | _MISSING)
 _registered = []         # names this module put into sys.modules

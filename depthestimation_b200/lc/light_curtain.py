@@ -300,9 +300,79 @@ class LightCurtain:
         return self._generic(([], self.field_visual), yield_mode)
 
     def plan_m1(self, field, planner, fw, kw, cfg, yield_mode):
-        raise NotImplementedError("plan_m1 (light_curtain.py:506-644: per-column samples from numpy's global RNG, lcsim's "
-                                  "fitBSpline through them, cv2.GaussianBlur of the rasterised spline, DP on the product) "
-                                  "is not on the B200 path yet (DESIGN.md section 8)")
+        """light_curtain.py:506-644: the main DP curtain on the un-normalised planning field, then cfg["step"] more:
+        per sampled column (every cfg["interval"]-th) a range bin is drawn from the column's distribution with numpy's
+        GLOBAL RNG (np.random.choice, as in the reference: seed it to reproduce a run), lcsim's fitBSpline goes through
+        the draws, the rasterised curve is blurred (3 x 5x5 Gaussian, sigma 1), normalised per column, multiplied into
+        the field and planned again.  Field preparation, blur / fuse and every DP run on the GPU; the draws and the
+        spline are host arithmetic like the reference's.  `field` is not modified."""
+        mode = kw
+        r = self.rig(mode)
+        R, W = len(self.r_candi_up), r.width
+        field = field.clone()
+        field[:, 0] = field[:, 1]                                                # :514-515, on a copy
+        field[:, -1] = field[:, -2]
+        if self.transform_needed:
+            um, _, pre = ops.plan_prepare_transformed(field.unsqueeze(0), r.flow_T, r.flow, [], R, W, 1)
+            frange, fpre = um[0, 0], pre[0]
+        else:
+            frange, fpre = ops.plan_field(field.unsqueeze(0), r.flow, R, 1)      # NaN columns fixed, nothing normalised
+            frange, fpre = frange[0], fpre[0]
+        frange[:, 0] = frange[:, 1]                                              # :550-551
+        frange[:, -1] = frange[:, -2]
+        lo, hi = fpre.min(0, keepdim=True).values, fpre.max(0, keepdim=True).values
+        vis = np.repeat(((fpre - lo) / (hi - lo)).cpu().numpy()[:, :, np.newaxis], 3, axis=2)   # :554
+        d_up = np.asarray(self.d_candi_up)
+
+        def solve(m):
+            ks, xz, counts = r.planner.solve(m.unsqueeze(0).contiguous())
+            return xz[0, :int(counts[0])]
+
+        def mark(pts):
+            p = pts.cpu().numpy()
+            vis[np.digitize(p[:, 1], d_up) - 1, np.arange(p.shape[0]), :] = [1, 0, 1]
+
+        pts_main = solve(frange)
+        if yield_mode:
+            yield pts_main
+        mark(pts_main)
+        if yield_mode:
+            yield pts_main                                                       # the reference yields it twice (:560,:565)
+        pts_all = [pts_main]
+        g1 = np.exp(-0.5 * np.arange(-2, 3, dtype=np.float64) ** 2)              # cv2.getGaussianKernel(5, 1)
+        g1 = torch.tensor((g1 / g1.sum()).astype(np.float32), device=self.device)
+        host_field = frange.cpu().numpy()
+        for _ in range(int(cfg["step"])):
+            temp = host_field.copy()
+            sampled = []
+            for c in range(0, W, int(cfg["interval"])):                          # :585-591
+                ray = temp[:, c]
+                ray[np.isnan(ray)] = 1e-5
+                ray = ray / np.sum(ray)
+                sampled.append([c, np.random.choice(ray.shape[0], 1, p=ray)[0], 5.])
+            spline = lcsim.fitBSpline(np.array(sampled).astype(np.float32)).astype(np.int64)
+            spline = spline[(spline[:, 0] >= 0) & (spline[:, 0] < W) & (spline[:, 1] >= 0) & (spline[:, 1] < R)]
+            vis[spline[:, 1], spline[:, 0]] = (1, 0, 0)
+            empty = torch.tensor(temp, device=self.device) * 0                   # NaN stays NaN, like temp * 0 (:606)
+            sp = torch.tensor(spline, device=self.device)
+            empty[sp[:, 1], sp[:, 0]] = 1.
+            e4 = empty.reshape(1, 1, R, W)
+            for _i in range(3):                                                  # cv2.GaussianBlur((5,5), 1), BORDER_REFLECT_101
+                e4 = torch.nn.functional.conv2d(torch.nn.functional.pad(e4, (2, 2, 0, 0), mode="reflect"), g1.reshape(1, 1, 1, 5))
+                e4 = torch.nn.functional.conv2d(torch.nn.functional.pad(e4, (0, 0, 2, 2), mode="reflect"), g1.reshape(1, 1, 5, 1))
+            empty = e4[0, 0]
+            empty = empty / empty.sum(0, keepdim=True)                           # :621-624
+            mult = frange * empty
+            towork = mult / mult.sum(0, keepdim=True)
+            towork = torch.nan_to_num(towork, nan=0.0, posinf=float("inf"), neginf=float("-inf"))
+            pts = solve(towork)
+            pts_all.append(pts)
+            if yield_mode:
+                yield pts
+            mark(pts)
+        self.field_visual = vis
+        if not yield_mode:
+            yield (pts_all, vis)
 
     # ---- real-sensor measurement (light_curtain.py:1076-1089) --------------------------------------
     def transform_measurement(self, output_lc, thickness_lc, rTc=None, intr_rgb=None, size_rgb=None):

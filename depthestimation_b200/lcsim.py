@@ -31,6 +31,24 @@ def generateCameraAngles(K, dist, w, h):
     return [float(v) for v in out]        # pybind11 hands std::vector<float> back as Python floats
 
 
+def fitBSpline(input_pts, splineParams=None, computeCurve=True):
+    """pylc_lib.fitBSpline (algo.cpp:449-589): control points [n,3] = (x, y, weight) -> curve samples [m,2] float32
+    (every 0.01 units along each segment).  Host arithmetic, like the reference's; splineParams is accepted and ignored
+    (plan_m1 does not read it back)."""
+    if not computeCurve:
+        raise NotImplementedError("fitBSpline(computeCurve=False) only fills splineParams, which this path does not use")
+    p = _host_f32(input_pts).reshape(-1, 3)
+    n = ctypes.c_longlong(0)
+    check(lib().lc_fit_bspline(_hp(p), int(p.shape[0]), None, 0, ctypes.byref(n)))
+    out = np.zeros((int(n.value), 2), np.float32)
+    check(lib().lc_fit_bspline(_hp(p), int(p.shape[0]), _hp(out), int(n.value), ctypes.byref(n)))
+    return out
+
+
+class SplineParamsVec:
+    """pylc_lib.SplineParamsVec: the container plan_m1 hands to fitBSpline (unused on this path)."""
+
+
 def transform_points(pts, thick, intr, M, width, height, filtering=0):
     """Batched Depth::transformPoints (depth.cpp:143-222) on the GPU: pts [n,N,4], thick [n,N] (CUDA tensors or arrays),
     intr [3,3], M [4,4] (host) -> maps [n,3,height,width] = (depth, intensity, thickness)."""

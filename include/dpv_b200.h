@@ -170,6 +170,11 @@ int lc_device_hit_lut(const LcDevice* dev, float* out_host);
 /* external/lcsim/lcsim/src/algo.cpp:696-741 Algo::generateCameraAngles (zero distortion). host in/out */
 int lc_camera_angles(const float* K, int W, int H, float* out_host);
 
+/* pylc.fitBSpline = Algo::fitBSpline (external/lcsim/lcsim/src/algo.cpp:449-589; lc/light_curtain.py:580-582, plan_m1):
+ * the cubic curve through n_pts control points pts host[n_pts,3] = (x, y, weight), sampled every 0.01 units
+ * -> out host[*n_out,2].  Host only.  out = NULL asks for the number of points (*n_out). */
+int lc_fit_bspline(const float* pts, int n_pts, float* out, long long cap, long long* n_out);
+
 /* (d3) DP planner.  external/lcsim/lcsim/src/planning.cpp:14-126 (+ Trajectory :162-217),
  * python/planner.py:162-189 PlannerRT.  ranges host [R]. */
 typedef struct LcPlanner LcPlanner;

@@ -180,6 +180,72 @@ class LightCurtainOracle:
             vis[pix[:, 0], pix[:, 1], :] = [1, 0, 1]
         return pts_all, vis
 
+    # ---- plan_m1, light_curtain.py:506-644 -----------------------------------------------------
+    def plan_m1(self, field, cfg, return_indices=False):
+        """field [D,W] (mutated in place) -> (list of design-point arrays, field_visual [R,W,3]).  Draws from numpy's
+        GLOBAL RNG exactly like the reference (np.random.choice per sampled column): seed it before the call."""
+        import cv2
+        from . import spline_oracle
+        field[:, 0] = field[:, 1]                                    # :514-515
+        field[:, -1] = field[:, -2]
+        for i in range(field.shape[1]):                              # :518-522
+            if torch.isnan(field[:, i]).any():
+                field[:, i] = O.EPS
+                field[-1, i] = 1.0
+        f = F.interpolate(field.unsqueeze(0).unsqueeze(0), size=[len(self.d_candi_up), self.W],
+                          mode="bilinear", align_corners=False)      # :526
+        k = torch.zeros(5, 5)
+        k[:, 2] = 1 / 5.0
+        f = F.conv2d(f, k.reshape(1, 1, 5, 5), padding=2).squeeze(0).squeeze(0)      # :529-531
+        f = self._rgb_to_lc(f)                                       # :534-535 (no normalisation here: :538-539 are comments)
+        fr = flow_warp(f, self.flow())                               # :544
+        fr[:, 0] = fr[:, 1]                                          # :550-551
+        fr[:, -1] = fr[:, -2]
+        lo, _ = f.unsqueeze(0).min(1)
+        hi, _ = f.unsqueeze(0).max(1)
+        vis = np.repeat(((f.unsqueeze(0) - lo) / (hi - lo)).squeeze(0).numpy()[:, :, np.newaxis], 3, axis=2)   # :554
+        d_up = np.asarray(self.d_candi_up)
+
+        def plan_one(m):
+            return self.planner.get_design_points(np.ascontiguousarray(m, np.float32), return_indices=True)
+
+        def mark(pts):
+            pix = np.array([np.digitize(pts[:, 1], d_up) - 1, range(0, pts.shape[0])]).T
+            vis[pix[:, 0], pix[:, 1], :] = [1, 0, 1]
+
+        pts_main, ks_main = plan_one(fr.numpy())                     # :559
+        mark(pts_main)
+        out, ks_all = [pts_main], [ks_main]
+        for _ in range(cfg["step"]):                                 # :570
+            towork = fr.numpy().copy()
+            temp = towork.copy()
+            sampled_pts = []
+            for c in range(0, temp.shape[1], cfg["interval"]):       # :585-591
+                ray = temp[:, c]
+                ray[np.isnan(ray)] = 1e-5
+                ray = ray / np.sum(ray)
+                s = np.random.choice(ray.shape[0], 1, p=ray)
+                sampled_pts.append([c, s[0], 5.])
+            sampled_pts = np.array(sampled_pts).astype(np.float32)
+            spline = spline_oracle.fit_bspline(sampled_pts).astype(np.int64)            # :596-598
+            spline = spline[(spline[:, 0] >= 0) & (spline[:, 0] < vis.shape[1]) & (spline[:, 1] >= 0) & (spline[:, 1] < vis.shape[0])]
+            for sp in spline:
+                vis[sp[1], sp[0]] = (1, 0, 0)
+            empty = temp * 0                                         # :606-607
+            empty[spline[:, 1], spline[:, 0]] = 1.
+            for _i in range(3):                                      # :617-618
+                empty = cv2.GaussianBlur(empty, (5, 5), 1)
+            with np.errstate(divide="ignore", invalid="ignore"):
+                empty = empty / np.sum(empty, axis=0)                # :621-624
+                mult = towork * empty
+                towork = mult / np.sum(mult, axis=0)
+            towork[np.isnan(towork)] = 0.
+            pts, ks = plan_one(towork)                               # :630
+            out.append(pts)
+            ks_all.append(ks)
+            mark(pts)
+        return (out, vis, ks_all) if return_indices else (out, vis)
+
     def split_fields(self, frange, steps):
         """:695-708 -> list of umaps [main, (left_p, right_p) for p in steps], and the argmax row."""
         left, right = frange.clone(), frange.clone()

@@ -1,0 +1,115 @@
+"""Generates tests/golden/spline_ref.npz and tests/golden/plan_m1.npz.  Run in the build container (needs
+/root/reference):  python tests/golden/make_plan_m1.py
+
+spline_ref.npz -- the reference's own Algo::fitBSpline (external/lcsim/lcsim/src/algo.cpp:449-589, compiled from where
+it lies by oracle/ref_spline.py) on: integer pixel samples like plan_m1's (three sizes), non-integer points with
+varying weights, two points (the least the function is defined for), repeated points (zero-length segments).  Small
+curves are stored whole, the 400- and 768-column curves as length + sha256 + every 97th sample.
+
+plan_m1.npz -- the UNMODIFIED lc/light_curtain.py LightCurtain.plan_m1_high (:506-644) run on top of
+  planner.PlannerRT  = oracle/lcsim.py's (pinned to the reference's planning.cpp, tests/golden/planner_ref.npz),
+  pylc_lib.fitBSpline = the compiled reference function above,
+with np.random.seed(SEED) before the call (plan_m1 draws from numpy's global RNG).  `np.long`, which numpy 2 removed
+and :598 uses, is set to np.int64 for the run.
+"""
+import hashlib
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, HERE)
+sys.path.insert(0, ROOT)
+
+import ref_shim  # noqa: E402
+
+H_, IU = ref_shim.load()
+from oracle import lcsim, ref_spline  # noqa: E402
+
+torch.set_num_threads(1)
+
+
+def spline_cases():
+    rng = np.random.default_rng(5)
+    out = {}
+
+    def pixel_case(W, iv, R):
+        return np.array([[c, rng.integers(0, R), 5.] for c in range(0, W, iv)], np.float32)
+
+    cases_big = [pixel_case(400, 20, 128), pixel_case(768, 10, 256)]
+    cases = {"px96": pixel_case(96, 7, 64), "px64": pixel_case(64, 10, 32),
+             "real": np.stack([np.sort(rng.uniform(-3, 3, 9)), rng.uniform(4, 12, 9), rng.uniform(2, 7, 9)], 1).astype(np.float32),
+             "two": np.array([[0., 3., 5.], [40., 17., 5.]], np.float32),
+             "repeat": np.array([[0., 3., 5.], [10., 3., 5.], [10., 3., 5.], [20., 9., 5.], [30., 9., 5.]], np.float32)}
+    for k, p in cases.items():
+        curve, co = ref_spline.fit_bspline(p, with_coeffs=True)
+        out[k + "_pts"], out[k + "_curve"], out[k + "_coeffs"] = p, curve, co
+    for k, p in (("px400", cases_big[0]), ("px768", cases_big[1])):
+        curve = ref_spline.fit_bspline(p)
+        out[k + "_pts"] = p
+        out[k + "_len"] = np.int64(curve.shape[0])
+        out[k + "_sha256"] = np.frombuffer(hashlib.sha256(np.ascontiguousarray(curve).tobytes()).digest(), np.uint8)
+        out[k + "_every97"] = curve[::97]
+    np.savez_compressed(os.path.join(HERE, "spline_ref.npz"), **out)
+    print("wrote spline_ref", {k: np.shape(v) for k, v in out.items()})
+
+
+def plan_m1_case():
+    sim = types.ModuleType("sim")
+    sim.LCDevice = lcsim.LCDevice
+    pl = types.ModuleType("planner")
+    pl.PlannerRT = lcsim.PlannerRT
+    py = types.ModuleType("pylc_lib")
+    py.generateCameraAngles = lcsim.generateCameraAngles
+    py.transformPoints = lcsim.transformPoints
+    py.fitBSpline = lambda pts, params, compute: ref_spline.fit_bspline(pts)
+    py.SplineParamsVec = lambda: None
+    sys.modules["sim"], sys.modules["planner"], sys.modules["pylc_lib"] = sim, pl, py
+    if not hasattr(np, "long"):
+        np.long = np.int64
+    import lc.light_curtain as LC
+    g = torch.Generator().manual_seed(13)
+    D, H, W, Dup = 16, 32, 64, 32
+    h, w = H // 4, W // 4
+    cfg = ref_shim.AttrDict({"data": {"dataset_path": "kitti", "exp_name": "golden"},
+                             "var": {"d_min": 5., "d_max": 40., "qpower": 1.0}})
+    d = IU.powerf(5., 40., D, 1.0)
+    d_up = IU.powerf(5., 40., Dup, 1.0)
+    fx = (w / 2) / np.tan(np.radians(16.0 / 2))
+    fy = (h / 2) / np.tan(np.radians(10.0 / 2))
+    Klow = np.array([[fx, 0, w / 2], [0, fy, h / 2], [0, 0, 1]], np.float32)
+    Kup = Klow * 4
+    Kup[2, 2] = 1
+    model_input = {"intrinsics_up": torch.tensor(Kup).unsqueeze(0), "intrinsics": torch.tensor(Klow).unsqueeze(0),
+                   "rgb": torch.zeros(1, 2, 3, H, W), "dmaps": torch.zeros(1, h, w), "masks": torch.ones(1, 1, h, w),
+                   "d_candi": d, "d_candi_up": d_up}
+    lc = LC.LightCurtain()
+    lc.init(lc.expand_params(lc.gen_params_from_model_input(model_input), cfg, D, Dup))
+    # a field with structure: a ridge that wanders over the columns + noise, two NaN columns
+    cols = torch.arange(W).float()
+    ridge = 7.5 + 4.0 * torch.sin(cols / 9.0)
+    rows = torch.arange(D).float().unsqueeze(1)
+    uf = torch.exp(-0.5 * ((rows - ridge.unsqueeze(0)) / 1.3) ** 2) + 0.05 * torch.rand(D, W, generator=g)
+    uf = uf / uf.sum(0, keepdim=True)
+    uf[:, 20] = float("nan")
+    uf[3, 41] = float("nan")
+    m1_cfg = {"step": 3, "interval": 5}
+    SEED = 77
+    np.random.seed(SEED)
+    pts, vis = lc.plan_m1_high(uf.clone(), m1_cfg)
+    out = dict(uf=uf.numpy(), d_candi=np.asarray(d, np.float32), d_candi_up=np.asarray(d_up, np.float32), Kup=Kup,
+               step=3, interval=5, seed=SEED, field_visual=vis, n_curtains=len(pts))
+    for i, p in enumerate(pts):
+        out["pts%d" % i] = np.asarray(p, np.float32)
+    np.savez_compressed(os.path.join(HERE, "plan_m1.npz"), **out)
+    print("wrote plan_m1", {k: np.shape(v) for k, v in out.items()})
+
+
+if __name__ == "__main__":
+    assert ref_spline.build() is not None
+    spline_cases()
+    plan_m1_case()

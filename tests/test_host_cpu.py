@@ -36,6 +36,23 @@ def test_host_only_entry_points_match_oracle():
         lcsim.generateCameraAngles(g["intrinsics"], [0.1, 0, 0, 0, 0], 10, 10)
 
 
+def test_fit_bspline_matches_reference_golden():
+    """lc_fit_bspline (host arithmetic, no kernel) through lcsim.fitBSpline against the curves the reference's own
+    Algo::fitBSpline produced (tests/golden/spline_ref.npz): bit for bit, the caller truncates them to pixel indices."""
+    import hashlib
+    from depthestimation_b200 import lcsim
+    from depthestimation_b200._lib import DpvError
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "spline_ref.npz"))
+    for k in ("px96", "px64", "real", "two", "repeat"):
+        np.testing.assert_array_equal(lcsim.fitBSpline(g[k + "_pts"], lcsim.SplineParamsVec(), True), g[k + "_curve"], err_msg=k)
+    for k in ("px400", "px768"):
+        c = lcsim.fitBSpline(g[k + "_pts"])
+        assert c.shape[0] == int(g[k + "_len"])
+        assert hashlib.sha256(np.ascontiguousarray(c).tobytes()).digest() == g[k + "_sha256"].tobytes(), k
+    with pytest.raises(DpvError, match="at least 2 points"):
+        lcsim.fitBSpline(np.array([[1., 2., 5.]], np.float32))
+
+
 def test_polar_flowfield_matches_reference_golden():
     from depthestimation_b200.lc.light_curtain import polar_flowfield
     g = np.load(os.path.join(G, "light_curtain.npz"))

@@ -293,3 +293,59 @@ def test_planner_ref_golden_is_what_the_reference_produces_now():
     for i in (0, 2):
         n = int(g[name + "_counts"][i])
         np.testing.assert_array_equal(ref.get_design_points(g[name + "_maps"][i]), g[name + "_xz"][i, :n])
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# (f)3 plan_m1: the spline pinned to the reference's own Algo::fitBSpline (compiled from where it lies,
+# oracle/ref_spline.py -> tests/golden/spline_ref.npz), plan_m1 to the unmodified lc/light_curtain.py on top of it
+# (tests/golden/make_plan_m1.py -> plan_m1.npz)
+# ---------------------------------------------------------------------------------------------------------------
+SPLINE_WHOLE = ("px96", "px64", "real", "two", "repeat")
+SPLINE_HASHED = ("px400", "px768")
+
+
+def _curve_digest(c):
+    import hashlib
+    return hashlib.sha256(np.ascontiguousarray(c, np.float32).tobytes()).digest()
+
+
+def test_spline_oracle_matches_reference_fitbspline():
+    """oracle/spline_oracle.py against the curves the reference's function produced: every sample bit for bit (the
+    caller truncates them to pixels); the two long curves by length, SHA-256 and every 97th sample."""
+    from oracle import spline_oracle
+    g = np.load(os.path.join(G, "spline_ref.npz"))
+    for k in SPLINE_WHOLE:
+        np.testing.assert_array_equal(spline_oracle.fit_bspline(g[k + "_pts"]), g[k + "_curve"], err_msg=k)
+    for k in SPLINE_HASHED:
+        c = spline_oracle.fit_bspline(g[k + "_pts"])
+        assert c.shape[0] == int(g[k + "_len"]), k
+        np.testing.assert_array_equal(c[::97], g[k + "_every97"], err_msg=k)
+        assert _curve_digest(c) == g[k + "_sha256"].tobytes(), k
+
+
+def test_spline_golden_is_what_the_reference_produces_now():
+    """In the build container: cut + compile the reference's two functions again and regenerate two cases."""
+    from oracle import ref_spline
+    if not ref_spline.available():
+        pytest.skip("/root/reference is not on this machine")
+    g = np.load(os.path.join(G, "spline_ref.npz"))
+    for k in ("px64", "real"):
+        curve, co = ref_spline.fit_bspline(g[k + "_pts"], with_coeffs=True)
+        np.testing.assert_array_equal(curve, g[k + "_curve"])
+        np.testing.assert_array_equal(co, g[k + "_coeffs"])
+
+
+def test_plan_m1_oracle_matches_reference_golden():
+    """LightCurtainOracle.plan_m1 against the unmodified reference's plan_m1_high under the same numpy seed: the four
+    curtains (main + three sampled-spline rounds) and the drawn field visual are bit-identical (same torch / cv2 /
+    numpy calls on the CPU, pinned planner, pinned spline)."""
+    from oracle import lc_oracle as LO
+    g = np.load(os.path.join(G, "plan_m1.npz"))
+    D, W = g["uf"].shape
+    olc = LO.LightCurtainOracle(g["Kup"], W, 32, g["d_candi"], g["d_candi_up"])
+    np.random.seed(int(g["seed"]))
+    pts, vis = olc.plan_m1(torch.as_tensor(g["uf"]).clone(), {"step": int(g["step"]), "interval": int(g["interval"])})
+    assert len(pts) == int(g["n_curtains"])
+    for i, p in enumerate(pts):
+        np.testing.assert_array_equal(p, g["pts%d" % i], err_msg="curtain %d" % i)
+    np.testing.assert_array_equal(vis, g["field_visual"])
