@@ -190,7 +190,8 @@ def _lc_process_sweep(BV_cur_all, model_input, lc, mode, iterations, params, noi
 
 
 def _lc_process_separate_camera(BV_cur_all, model_input, lc, mode, iterations, planner, params, cfg, trace, score=False):
-    """lc_process for an LC camera posed or sized differently from the RGB camera (rTc != I / size_lc != size_rgb):
+    """lc_process for an LC camera posed or sized differently from the RGB camera (rTc != I / size_lc != size_rgb), and
+    for planner == "m1" with any camera (its planning is per sample on the host RNG):
     the fused sense+update kernel does not apply (a curtain return lands on other pixels than it was sensed on), so
     the loop is the reference's own composition (models.py:1027-1122) of GPU steps: uncertainty field -> planning field
     resized and warped RGB -> LC -> DP planner -> per curtain: depth re-projected into the LC camera, sensed,
@@ -224,6 +225,9 @@ def _lc_process_separate_camera(BV_cur_all, model_input, lc, mode, iterations, p
         for b in range(B):
             if planner == "default":
                 paths, _ = lc._plan_default(uf[b], {"step": list(get("step"))}, mode)
+            elif planner == "m1":                                              # models.py:1052-1053
+                paths, _ = (lc.plan_m1_high if mode == "high" else lc.plan_m1_low)(
+                    uf[b], {"step": int(get("step")), "interval": int(get("interval"))})
             else:
                 flat, _ = lc._plan_sweep(uf[b], {k: get(k) for k in ("start", "end", "step")}, mode)
                 paths = [torch.as_tensor(f, device=dev) for f in flat]
@@ -250,10 +254,11 @@ def lc_process(BV_cur_all, model_input, lc, mode="low", iterations=5, viz=False,
     if viz:
         raise NotImplementedError("lc_process(viz=True) drives the reference's PCL / OpenCV viewer (models.py:1072-1094): "
                                   "graphics, unavailable on this box")
-    if planner not in ("default", "sweep"):
-        raise NotImplementedError("planner %r: 'default' and 'sweep' are on the B200 path (plan_m1 is not: numpy RNG + "
-                                  "alglib spline fit, DESIGN.md section 8)" % planner)
-    if getattr(lc, "transform_needed", False):
+    if planner not in ("default", "sweep", "m1"):
+        raise Exception("lc_process: unknown planner " + str(planner))
+    # plan_m1 draws per sample from numpy's global RNG on the host (light_curtain.py:585-591), so it runs through the
+    # per-sample composition like a separately posed LC camera does
+    if getattr(lc, "transform_needed", False) or planner == "m1":
         return _lc_process_separate_camera(BV_cur_all, model_input, lc, mode, iterations, planner, params, cfg, trace,
                                            score)
     get = (lambda k: params[k]) if isinstance(params, dict) else (lambda k: getattr(params, k))
@@ -304,3 +309,129 @@ def lc_process(BV_cur_all, model_input, lc, mode="low", iterations=5, viz=False,
     else:
         out = out.clone()
     return out, unc_scores
+
+
+def integrate(final, DPVs, d_candi, spread_iter=1, spread_n=3):
+    """ros/ros_all.py:169-203 Planner.integrate: the running log-DPV `final` [B,D,H,W] multiplied by every likelihood
+    volume of `DPVs` ([D,H,W] or [B,D,H,W] each; clamp, multiply, renormalise), one 1 x 3 spread (what the node does for
+    its first 100 updates: pass spread_iter=0 afterwards), clamp, log -> the new log-DPV.  One kernel (dpv_bayes_fuse).
+    A NaN likelihood counts as 0 like in lc_process_real (models.py:961); the node's own integrate would propagate it."""
+    B = final.shape[0]
+    liks = torch.stack([ops.f32(d, final.device).reshape(-1, *final.shape[1:]).expand(B, -1, -1, -1) for d in DPVs], 1)
+    return ops.bayes_fuse(final, liks.contiguous(), d_candi, spread_iter, spread_n)[0]
+
+
+def _truth_field_in_lc(uf_truth, algo_lc):
+    """models.py:866-871: the ground-truth field [D,W_rgb] resized to [R,W_lc] (FieldWarp.preprocess), warped RGB -> LC
+    (transformZTheta) and blanked on 50 columns at either side.  A scoring side path: torch calls."""
+    r = algo_lc.rig("high")
+    R = len(algo_lc.d_candi_up)
+    f = torch.nn.functional.interpolate(uf_truth.reshape(1, 1, *uf_truth.shape), size=[R, r.width], mode="bilinear",
+                                        align_corners=False)[0, 0]
+    if algo_lc.transform_needed and r.flow_T is not None:
+        H, W = f.shape
+        yv, xv = torch.meshgrid([torch.arange(H, device=f.device).float(), torch.arange(W, device=f.device).float()],
+                                indexing="ij")
+        xs, ys = 2.0 / float(W - 1), 2.0 / float(H - 1)
+        grid = torch.stack([-1 + xv * xs - r.flow_T[..., 0] * xs, -1 + yv * ys - r.flow_T[..., 1] * ys], -1)
+        f = torch.nn.functional.grid_sample(f.reshape(1, 1, H, W), grid.unsqueeze(0), mode="bilinear",
+                                            padding_mode="zeros", align_corners=False)[0, 0]
+    f[:, 0:50] = float("nan")
+    f[:, -50:-1] = float("nan")
+    return f
+
+
+def lc_process_real(BV_cur_all, model_input, algo_lc, real_lc, iterations=5, viz=False, score=False, planner="default",
+                    params=None, cfg=None, trace=None):
+    """BaseModel.lc_process_real (models/models.py:839-978): the Bayesian loop on a RECORDED sweep of the real sensor.
+
+    model_input["sweep_arr_tensor"] [B,K,h,w,2] holds, per sample, K swept curtains as (depth, intensity) images at
+    half the LC camera's size.  Per sample and iteration: uncertainty field -> algo_lc plans curtains (default / m1 /
+    sweep) -> real_lc's device images each curtain against a wall at 1000 m (every ray returns the curtain's own
+    surface point and thickness) -> per pixel the recorded slice nearest in depth supplies the intensity
+    (lc_sweep_sample) -> the return is re-projected into the RGB camera (lc_transform_points, filtering 0) ->
+    intensity-model likelihood (lc_likelihood_true, sigma = thickness / 2, peak 0.2) -> Bayesian update
+    (dpv_bayes_fuse).  All curtains of an iteration go through each kernel in one launch.
+    Returns (fused log-DPV [B,D,H,W], unc_scores) like the reference.  model_input is not modified (the reference
+    overwrites the NaNs of the recorded depths in place)."""
+    if viz:
+        raise NotImplementedError("lc_process_real(viz=True) opens OpenCV windows (models.py:940-950): graphics, "
+                                  "unavailable on this box")
+    if planner not in ("default", "m1", "sweep"):
+        raise Exception("lc_process_real: unknown planner " + str(planner))
+    from . import lcsim
+    get = (lambda k: params[k]) if isinstance(params, dict) else (lambda k: getattr(params, k))
+    spread_iter, spread_n = int(get("spread_iter")), int(get("spread_n"))
+    dev = BV_cur_all.device
+    B = BV_cur_all.shape[0]
+    uf_par = img_utils.uf_params(cfg if cfg is not None else "kitti")
+    rdev = real_lc.rig("high").dev
+    RP = real_lc.PARAMS
+    Wr, Hr = int(RP["size_rgb"][0]), int(RP["size_rgb"][1])
+    wall = torch.full((1, rdev.H, rdev.W), 1000.0, device=dev)                              # :911
+    fused, unc_scores_all = [], []
+    for b in range(B):
+        K = model_input["intrinsics_up"][b].to(dev).float().reshape(1, 3, 3)
+        sweep = model_input["sweep_arr_tensor"][b].to(dev).float()
+        feat_z = torch.nan_to_num(sweep[..., 0], nan=1000.0, posinf=float("inf"), neginf=float("-inf"))   # :852
+        feat_int = sweep[..., 1]
+        up = [feat_z.shape[1] * 2, feat_z.shape[2] * 2]                                     # :855-856
+        feat_int = torch.nn.functional.interpolate(feat_int.unsqueeze(0), size=up, mode="bicubic").contiguous()
+        feat_z = torch.nn.functional.interpolate(feat_z.unsqueeze(0), size=up, mode="bicubic").contiguous()
+        if tuple(up) != (rdev.H, rdev.W):
+            raise ValueError("lc_process_real: the sweep images upsampled x2 are %s, the real LC camera is %s"
+                             % (up, [rdev.H, rdev.W]))
+        uf_truth = None
+        if score:
+            dm = {"dmaps": model_input["dmaps"][b:b + 1], "masks": model_input["masks"][b:b + 1]}
+            depth_up = torch.nn.functional.interpolate(dm["dmaps"].to(dev).float().unsqueeze(1), scale_factor=4,
+                                                       mode="nearest").squeeze(1).contiguous()
+            uf_truth = _truth_field_in_lc(_truth_field(dm, depth_up, K, algo_lc, uf_par, "high", dev)[0], algo_lc)
+        final = BV_cur_all[b:b + 1].detach().float().contiguous()
+        D_in = final.shape[1]
+        if D_in != algo_lc.expand_A:                                                        # :877-878
+            final = ops.resample_depth(final, algo_lc.expand_A, bv_log=True)
+        scores = []
+        for it in range(iterations):
+            mean = ops.expectation(final, algo_lc.d_candi, True)
+            uf, _ = ops.ufield(final, mean, K, algo_lc.d_candi, uf_par, bv_log=True, want_depth=False)
+            if score:                                                                       # :899-901
+                if tuple(uf_truth.shape) != tuple(uf[0].shape):
+                    raise ValueError("lc_process_real(score=True): truth field in the LC camera is %s, predicted field %s "
+                                     "(the reference compares them bin by bin: expand_A must equal expand_B and the "
+                                     "cameras' widths must agree)" % (tuple(uf_truth.shape), tuple(uf[0].shape)))
+                scores.append(ops.unc_rmse(uf_truth, uf[0], algo_lc.d_candi).item())
+            if planner == "default":                                                        # :905-910
+                paths, _ = algo_lc.plan_default_high(uf[0], params)
+            elif planner == "m1":
+                paths, _ = algo_lc.plan_m1_high(uf[0], params)
+            else:
+                paths, _ = algo_lc.plan_sweep_high(uf[0], params)
+            nc = len(paths)
+            if nc:
+                npts = max(int(p.shape[0]) for p in paths)
+                xz = torch.zeros(nc, npts, 2, device=dev)
+                for c, pth in enumerate(paths):
+                    xz[c, :pth.shape[0]] = ops.f32(pth, dev)[:, :2]
+                counts = torch.tensor([int(p.shape[0]) for p in paths], device=dev, dtype=torch.int32)
+                planes = rdev.curtain_planes(xz, counts)
+                img, th = rdev.sense_image(planes, wall, nc, rdev.noise_like(nc))            # :912
+                img[torch.isnan(img[..., 0])] = 0                                           # :913-914
+                th[torch.isnan(th)] = 0
+                img[..., 3] = lcsim.sweep_sample(img[..., 2].unsqueeze(0).contiguous(), feat_z, feat_int)[0]   # :917-920
+                sensed = lcsim.transform_points(img.reshape(nc, -1, 4), th.reshape(nc, -1), RP["intr_rgb"], RP["rTc"],
+                                                Wr, Hr, 0)                                  # :923, [nc,3,Hr,Wr]
+                hit = (sensed[:, 0] > 0).float()                                            # gen_lc_dpv_true, std_div 2
+                liks = ops.likelihood_true(sensed[:, 0], sensed[:, 1] * hit / 255., sensed[:, 2] * hit / 2.0,
+                                           real_lc.d_candi, 0.1, 0.2).permute(1, 0, 2, 3).unsqueeze(0).contiguous()
+            else:
+                liks = torch.empty(1, 0, *final.shape[1:], device=dev)
+            if trace is not None:
+                trace.append(dict(b=b, it=it, uf=uf[0].clone(), paths=[ops.f32(p, dev).clone() for p in paths],
+                                  sensed=sensed.clone() if nc else None, liks=liks[0].clone()))
+            final, _ = ops.bayes_fuse(final, liks, algo_lc.d_candi, spread_iter, spread_n)   # :953-972
+        if final.shape[1] != D_in:                                                          # :974-975
+            final = ops.resample_depth(final, D_in, bv_log=True)
+        fused.append(final)
+        unc_scores_all.append(scores)
+    return torch.cat(fused, 0), unc_scores_all

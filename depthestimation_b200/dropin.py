@@ -70,6 +70,17 @@ def _lc_process_method():
     return lc_process
 
 
+def _lc_process_real_method():
+    """BaseModel.lc_process_real with the reference's exact signature (models/models.py:839)."""
+    from . import dpv_head
+
+    def lc_process_real(self, BV_cur_all, model_input, algo_lc, real_lc, iterations=5, viz=False, score=False,
+                        planner="default", params=None):
+        return dpv_head.lc_process_real(BV_cur_all, model_input, algo_lc, real_lc, iterations, viz, score, planner,
+                                        params, cfg=getattr(self, "cfg", None))
+    return lc_process_real
+
+
 def _set(obj, name, value):
     _installed.append((obj, name, getattr(obj, name, _MISSING)))
     setattr(obj, name, value)
@@ -120,6 +131,9 @@ def install(reference_root=None, strict=False, lcsim_modules=True):
         models = importlib.import_module("models.models")
         _set(models.BaseModel, "lc_process", _lc_process_method())
         report["patched"].append("models.models.BaseModel.lc_process")
+        if hasattr(models.BaseModel, "lc_process_real"):
+            _set(models.BaseModel, "lc_process_real", _lc_process_real_method())
+            report["patched"].append("models.models.BaseModel.lc_process_real")
     except Exception as e:
         if strict:
             raise

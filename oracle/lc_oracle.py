@@ -334,3 +334,65 @@ def lc_loop(logp, depth_gt, lc, K_up, uf_par, iterations, steps, spread_iter, sp
     if final.shape[1] != start.shape[1]:
         final = O.resample_depth_bins(final, N=start.shape[1], BV_log=True)   # :1124
     return final
+
+
+def lc_loop_real(logp, sweep_arr, algo, real, K_up, uf_par, iterations, planner, params, spread_iter, spread_n,
+                 trace=None):
+    """BaseModel.lc_process_real body for ONE sample (models/models.py:839-978; score / viz left out).
+    logp [1,D,H,W] log-DPV; sweep_arr [K,h,w,2] (depth, intensity) of the recorded sweep at half the real LC camera's
+    size; algo / real: LightCurtainOracle of the planning rig and of the real sensor (real.rgb = the RGB camera its
+    returns are re-projected into; None: the LC camera itself).  planner "default" (params["step"] list), "m1"
+    (params step / interval, numpy global RNG) or "sweep" (start / end / step).  -> fused log-DPV [1,D,H,W]."""
+    from . import aux_oracle as AO
+    K = torch.as_tensor(K_up).float()
+    sweep_arr = torch.as_tensor(sweep_arr).float()
+    feat_z = sweep_arr[:, :, :, 0].clone()
+    feat_int = sweep_arr[:, :, :, 1]
+    feat_z[torch.isnan(feat_z)] = 1000                                          # :852
+    up = [feat_int.shape[1] * 2, feat_int.shape[2] * 2]
+    feat_int = F.interpolate(feat_int.unsqueeze(0), size=up, mode="bicubic").squeeze(0)      # :855-856
+    feat_z = F.interpolate(feat_z.unsqueeze(0), size=up, mode="bicubic").squeeze(0)
+    if real.rgb is None:
+        K_rgb, size_rgb, rTc = real.K, (real.W, real.H), np.eye(4, dtype=np.float32)
+    else:
+        K_rgb, size_rgb, rTc = real.rgb["K"], real.rgb["size"], real.rgb["rTc"]
+    start = logp
+    final = logp.detach().clone()
+    if final.shape[1] != len(algo.d_candi):
+        final = O.resample_depth_bins(final, N=len(algo.d_candi), BV_log=True)   # :877-878
+    dc = torch.tensor(np.asarray(real.d_candi, np.float32))
+    for it in range(iterations):
+        uf, _ = O.ufield(final, algo.d_candi, K, uf_par, BV_log=True)           # :891
+        uf_rec = uf.clone()
+        if planner == "default":                                                # :905-910
+            paths = [p for p in algo.plan(uf.squeeze(0), list(params["step"]))[0]]
+        elif planner == "m1":
+            paths, _ = algo.plan_m1(uf.squeeze(0), params)
+        else:
+            paths, _ = algo.plan_sweep(uf.squeeze(0), params)
+        liks, sensed_all = [], []
+        for path in paths:
+            depth_lc = np.ones((feat_int.shape[1], feat_int.shape[2]), np.float32) * 1000          # :911
+            out_lc, th_lc = real.dev.get_return(depth_lc, np.asarray(path, np.float32), True)
+            out_lc[np.isnan(out_lc[:, :, 0])] = 0                                                   # :913-914
+            th_lc[np.isnan(th_lc)] = 0
+            sd = torch.tensor(out_lc[:, :, 2])                                                      # :917-920
+            inds = torch.argmin(torch.abs(sd.reshape(1, sd.shape[0], sd.shape[1]) - feat_z), dim=0)
+            out_lc[:, :, 3] = torch.gather(feat_int, 0, inds.unsqueeze(0)).squeeze(0).numpy()
+            ds, its, ts = lcsim.transformPoints(out_lc.reshape(-1, 4), th_lc.flatten(), K_rgb, np.asarray(rTc),
+                                                int(size_rgb[0]), int(size_rgb[1]), {"filtering": 0})  # :923
+            sensed = np.stack([ds, its, ts])
+            mask = (sensed[0] > 0).astype(np.float32)                            # gen_lc_dpv_true :1106-1125
+            z = torch.tensor(sensed[0]).float().unsqueeze(-1)
+            x = torch.tensor(sensed[1] * mask / 255.).float().unsqueeze(-1)
+            sg = torch.tensor((sensed[2] * mask / 2) ** 1).float().unsqueeze(-1)
+            peak = torch.ones(sensed[0].shape).float().unsqueeze(-1) * 0.2
+            _, dpv = O.intensity_model_likelihood(dc, z, x, sg, 0.1, peak)
+            liks.append(dpv.permute(2, 0, 1))
+            sensed_all.append(sensed)
+        final = O.bayes_fuse(final, liks, spread_iter, spread_n)                # :953-972
+        if trace is not None:
+            trace.append(dict(uf=uf_rec, paths=paths, sensed=sensed_all, liks=liks, logp=final))
+    if final.shape[1] != start.shape[1]:
+        final = O.resample_depth_bins(final, N=start.shape[1], BV_log=True)     # :974-975
+    return final

@@ -58,7 +58,7 @@ def spline_cases():
     print("wrote spline_ref", {k: np.shape(v) for k, v in out.items()})
 
 
-def plan_m1_case():
+def _install_stubs():
     sim = types.ModuleType("sim")
     sim.LCDevice = lcsim.LCDevice
     pl = types.ModuleType("planner")
@@ -71,6 +71,10 @@ def plan_m1_case():
     sys.modules["sim"], sys.modules["planner"], sys.modules["pylc_lib"] = sim, pl, py
     if not hasattr(np, "long"):
         np.long = np.int64
+
+
+def plan_m1_case():
+    _install_stubs()
     import lc.light_curtain as LC
     g = torch.Generator().manual_seed(13)
     D, H, W, Dup = 16, 32, 64, 32
@@ -109,7 +113,87 @@ def plan_m1_case():
     print("wrote plan_m1", {k: np.shape(v) for k, v in out.items()})
 
 
+def lc_process_real_case():
+    """The UNMODIFIED BaseModel.lc_process_real (models/models.py:839-978) on a synthetic recorded sweep: the planning
+    rig is the RGB camera itself (64 x 32), the real sensor a separately posed 80 x 40 LC camera (rTc != I), the sweep
+    K = 12 recorded curtains at half its size.  planner "default" (2 iterations) and "m1" (1 iteration, seeded)."""
+    _install_stubs()
+    import lc.light_curtain as LC
+    import models.models as MM
+    if not torch.cuda.is_available():        # transform_measurement (:1086-1088) pins and uploads its result: no-ops here
+        torch.Tensor.pin_memory = lambda self, *a, **k: self
+        torch.Tensor.cuda = lambda self, *a, **k: self
+    g = torch.Generator().manual_seed(31)
+    D, Dup = 16, 32
+    Wr, Hr, Wl, Hl = 64, 32, 80, 40
+    h, w = Hr // 4, Wr // 4
+    cfg = ref_shim.AttrDict({"data": {"dataset_path": "kitti", "exp_name": "golden"},
+                             "var": {"d_min": 5., "d_max": 40., "qpower": 1.0}})
+    d = IU.powerf(5., 40., D, 1.0)
+    d_up = IU.powerf(5., 40., Dup, 1.0)
+    K_rgb = np.array([[150., 0., 32.], [0., 150., 16.], [0., 0., 1.]], np.float32)
+    K_lc = np.array([[170., 0., 40.], [0., 170., 20.], [0., 0., 1.]], np.float32)
+    a = np.radians(2.0)
+    rTc = np.eye(4, dtype=np.float32)
+    rTc[:3, :3] = np.array([[np.cos(a), 0., np.sin(a)], [0., 1., 0.], [-np.sin(a), 0., np.cos(a)]], np.float32)
+    rTc[:3, 3] = [0.06, -0.03, 0.02]
+    lTc = np.eye(4, dtype=np.float32)
+    lTc[0, 3] = 0.2
+    eye = np.eye(4, dtype=np.float32)
+
+    def params(intr_lc, size_lc, T, name):
+        return {"intr_rgb": K_rgb, "dist_rgb": [0.] * 5, "size_rgb": [Wr, Hr], "intr_lc": intr_lc, "dist_lc": [0.] * 5,
+                "size_lc": size_lc, "rTc": T, "lTc": lTc, "laser_fov": 80., "d_candi": d, "r_candi": d,
+                "d_candi_up": d_up, "r_candi_up": d_up, "name": name, "laser_timestep": 3.5e-5,
+                "device": torch.device("cpu"), "expand_A": D, "expand_B": Dup}
+    algo = LC.LightCurtain()
+    algo.init(params(K_rgb, [Wr, Hr], eye, "golden_real_algo"))
+    real = LC.LightCurtain()
+    real.init(params(K_lc, [Wl, Hl], rTc, "golden_real_sensor"))
+    # the recorded sweep: K slices, each a (depth, intensity) image at half the LC camera's size
+    Ks = 12
+    zs = torch.linspace(6., 28., Ks)
+    cols = torch.arange(Wl // 2).float()
+    scene = (13. + 5. * torch.sin(cols / 6.0)).reshape(1, -1).repeat(Hl // 2, 1)
+    sweep = torch.zeros(Ks, Hl // 2, Wl // 2, 2)
+    for k in range(Ks):
+        sweep[k, :, :, 0] = zs[k] + 0.3 * torch.rand(Hl // 2, Wl // 2, generator=g)
+        sweep[k, :, :, 1] = 255. * torch.exp(-((zs[k] - scene) / 2.0) ** 2) * (0.8 + 0.2 * torch.rand(Hl // 2, Wl // 2, generator=g))
+    sweep[3, 2:4, 5:9, 0] = float("nan")
+    dm = (13. + 5. * torch.sin(torch.arange(w).float() / 1.5)).reshape(1, w).repeat(h, 1)
+    dm_up = torch.nn.functional.interpolate(dm.reshape(1, 1, h, w), scale_factor=4, mode="nearest")[0, 0]
+    logits = -((torch.tensor(d).float().reshape(D, 1, 1) - (dm_up * 1.1 + 1.0)) ** 2) / 30.0 \
+        + 0.2 * torch.randn(D, Hr, Wr, generator=g)
+    logp = torch.log_softmax(logits, 0).unsqueeze(0)
+
+    def model_input():
+        return {"intrinsics_up": torch.tensor(K_rgb).unsqueeze(0), "rgb": torch.zeros(1, 2, 3, Hr, Wr),
+                "dmaps": dm.unsqueeze(0).clone(), "masks": torch.ones(1, 1, h, w),
+                "sweep_arr_tensor": sweep.unsqueeze(0).clone()}
+
+    class _Self:
+        pass
+    me = _Self()
+    me.cfg, me.viz, me.real_lc = cfg, None, real
+    IU.spread_kernel = None
+    prm = ref_shim.AttrDict({"step": [0.5], "spread_iter": 1, "spread_n": 5})
+    fused_default, _ = MM.BaseModel.lc_process_real(me, logp.clone(), model_input(), algo, real, iterations=2,
+                                                    planner="default", params=prm)
+    IU.spread_kernel = None
+    prm_m1 = ref_shim.AttrDict({"step": 2, "interval": 6, "spread_iter": 1, "spread_n": 5})
+    np.random.seed(19)
+    fused_m1, _ = MM.BaseModel.lc_process_real(me, logp.clone(), model_input(), algo, real, iterations=1,
+                                               planner="m1", params=prm_m1)
+    IU.spread_kernel = None
+    out = dict(logp=logp.numpy(), sweep=sweep.numpy(), dmaps=dm.numpy(), d_candi=np.asarray(d, np.float32),
+               d_candi_up=np.asarray(d_up, np.float32), K_rgb=K_rgb, K_lc=K_lc, rTc=rTc, size_rgb=[Wr, Hr],
+               size_lc=[Wl, Hl], fused_default=fused_default.numpy(), fused_m1=fused_m1.numpy(), seed_m1=19)
+    np.savez_compressed(os.path.join(HERE, "lc_process_real.npz"), **out)
+    print("wrote lc_process_real", {k: np.shape(v) for k, v in out.items()})
+
+
 if __name__ == "__main__":
     assert ref_spline.build() is not None
     spline_cases()
     plan_m1_case()
+    lc_process_real_case()

@@ -96,6 +96,8 @@ def test_mirrored_functions_keep_the_reference_signatures():
     import models.models as models
     wrapper = dropin._lc_process_method()
     assert str(inspect.signature(wrapper)) == str(inspect.signature(models.BaseModel.lc_process))
+    wrapper = dropin._lc_process_real_method()
+    assert str(inspect.signature(wrapper)) == str(inspect.signature(models.BaseModel.lc_process_real))
 
 
 @have_ref
@@ -146,6 +148,7 @@ def test_install_rebinds_the_real_reference_modules():
         assert iw.inverse_warp.__module__ == "depthestimation_b200.utils.inverse_warp"
         assert lcm.LightCurtain.__module__ == "depthestimation_b200.lc.light_curtain"
         assert mm.BaseModel.lc_process.__module__ == "depthestimation_b200.dropin"
+        assert mm.BaseModel.lc_process_real.__module__ == "depthestimation_b200.dropin"
         assert mm.warp_homo.est_swp_volume_v4 is wh.est_swp_volume_v4          # models.py:6 looks it up through the module
         assert not rep["skipped"], rep["skipped"]
     finally:

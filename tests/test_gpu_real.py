@@ -312,3 +312,102 @@ def test_depth_to_points_bit_exact():
         assert torch.equal(img_utils.depth_to_pts(depth[b:b + 1], K).cpu(), exp[:, :3].t().reshape(3, H, W))
     with pytest.raises(Exception):
         img_utils.depth_to_pts(depth, K)
+
+
+def _real_rigs(g):
+    from depthestimation_b200.lc.light_curtain import LightCurtain
+    Wr, Hr = [int(v) for v in g["size_rgb"]]
+    Wl, Hl = [int(v) for v in g["size_lc"]]
+    lTc = np.eye(4, dtype=np.float32)
+    lTc[0, 3] = 0.2
+
+    def params(K_lc, size_lc, T, name):
+        return {"intr_rgb": g["K_rgb"], "dist_rgb": [0.] * 5, "size_rgb": [Wr, Hr], "intr_lc": K_lc, "dist_lc": [0.] * 5,
+                "size_lc": size_lc, "rTc": T, "lTc": lTc, "laser_fov": 80., "d_candi": g["d_candi"], "r_candi": g["d_candi"],
+                "d_candi_up": g["d_candi_up"], "r_candi_up": g["d_candi_up"], "name": name, "laser_timestep": 3.5e-5,
+                "device": torch.device("cuda", 0), "expand_A": len(g["d_candi"]), "expand_B": len(g["d_candi_up"]),
+                "hit_noise": 0.0}
+    algo, real = LightCurtain(), LightCurtain()
+    algo.init(params(g["K_rgb"], [Wr, Hr], np.eye(4, dtype=np.float32), "real_algo"))
+    real.init(params(g["K_lc"], [Wl, Hl], g["rTc"], "real_sensor"))
+    return algo, real
+
+
+def _volume_close(got, ref, what):
+    """Composed loops: a pixel may differ when a curtain point moved by a DP tie, a z-buffer border or a near-tie of the
+    nearest recorded slice (all decided on values 1e-6 apart); those pixels are counted (< 2 %), the rest compared at
+    rtol 1e-3 / atol 2e-3 on log-probabilities that accumulate three fp32 stages (field, likelihood, update)."""
+    bad = np.abs(got - ref).max(1) > 1e-3 * np.maximum(np.abs(ref).max(1), 1.0)
+    assert bad.mean() < 0.02, (what, bad.mean())
+    keep = ~bad[0]
+    np.testing.assert_allclose(got[0][:, keep], ref[0][:, keep], rtol=1e-3, atol=2e-3, err_msg=what)
+    return bad.mean()
+
+
+def test_lc_process_real_against_reference_golden():
+    """(f)2 lc_process_real (models/models.py:839-978): plan on the RGB rig, image each curtain with the separately
+    posed real LC device, sample the recorded sweep, re-project, intensity-model likelihood, Bayesian update -- every
+    step a kernel of this library, all curtains of an iteration per launch -- against the UNMODIFIED reference
+    (tests/golden/lc_process_real.npz), planner "default" and "m1" (same numpy seed); integrate() (ros_all.py:169-203)
+    against the oracle's update."""
+    import os
+    from depthestimation_b200 import dpv_head
+    from oracle import dpv_oracle as O
+    g = dict(np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "lc_process_real.npz")))
+    algo, real = _real_rigs(g)
+    assert not algo.transform_needed and real.transform_needed
+    logp = torch.as_tensor(g["logp"]).cuda()
+    sweep = torch.as_tensor(g["sweep"]).unsqueeze(0)
+    keep = sweep.clone()
+    mi = {"intrinsics_up": torch.as_tensor(g["K_rgb"]).unsqueeze(0), "dmaps": torch.as_tensor(g["dmaps"]).unsqueeze(0),
+          "masks": torch.ones(1, 1, *g["dmaps"].shape), "sweep_arr_tensor": sweep}
+    trace = []
+    fused, scores = dpv_head.lc_process_real(logp, mi, algo, real, iterations=2, planner="default",
+                                             params={"step": [0.5], "spread_iter": 1, "spread_n": 5}, trace=trace)
+    assert torch.equal(torch.nan_to_num(sweep), torch.nan_to_num(keep))            # model_input is not edited
+    assert scores == [[]] and len(trace) == 2 and trace[0]["liks"].shape[0] == 3
+    _volume_close(fused.cpu().numpy(), g["fused_default"], "default")
+    np.random.seed(int(g["seed_m1"]))
+    fused_m1, _ = dpv_head.lc_process_real(logp, mi, algo, real, iterations=1, planner="m1",
+                                           params={"step": 2, "interval": 6, "spread_iter": 1, "spread_n": 5})
+    _volume_close(fused_m1.cpu().numpy(), g["fused_m1"], "m1")
+    # two samples at once give each sample's own result
+    mi2 = {k: torch.cat([v, v]) for k, v in mi.items()}
+    both, _ = dpv_head.lc_process_real(torch.cat([logp, logp]), mi2, algo, real, iterations=2, planner="default",
+                                       params={"step": [0.5], "spread_iter": 1, "spread_n": 5})
+    assert torch.equal(both[0], fused[0]) and torch.equal(both[1], fused[0])
+    # Planner.integrate: one update from the traced likelihoods, against the oracle's multiply-renormalise
+    liks = [l for l in trace[0]["liks"]]
+    new = dpv_head.integrate(logp, liks, g["d_candi"])
+    ref = O.bayes_fuse(torch.as_tensor(g["logp"]), [l.cpu() for l in liks], 1, 3)
+    np.testing.assert_allclose(new.cpu().numpy(), ref.numpy(), rtol=1e-4, atol=1e-5)
+    with pytest.raises(NotImplementedError):
+        dpv_head.lc_process_real(logp, mi, algo, real, iterations=1, viz=True, params={"step": [0.5], "spread_iter": 1, "spread_n": 5})
+
+
+def test_lc_process_m1_planner_against_oracle():
+    """lc_process(planner="m1") (models.py:1052-1053) on the simulated sensor: per-sample host planning + per-curtain
+    sensing + Bayesian update, against the oracle's loop under the same numpy seed."""
+    import os
+    from depthestimation_b200 import dpv_head
+    from oracle import dpv_oracle as O
+    from oracle import lc_oracle as LO
+    g = dict(np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "lc_process_real.npz")))
+    algo, _ = _real_rigs(g)
+    Wr, Hr = [int(v) for v in g["size_rgb"]]
+    logp = torch.as_tensor(g["logp"])
+    dm = torch.as_tensor(g["dmaps"])
+    mi = {"intrinsics_up": torch.as_tensor(g["K_rgb"]).unsqueeze(0), "dmaps": dm.unsqueeze(0)}
+    prm = {"step": 2, "interval": 6, "spread_iter": 1, "spread_n": 5}
+    np.random.seed(3)
+    fused, _ = dpv_head.lc_process(logp.cuda(), mi, algo, mode="high", iterations=2, planner="m1", params=prm)
+    olc = LO.LightCurtainOracle(g["K_rgb"], Wr, Hr, g["d_candi"], g["d_candi_up"])
+    dm_up = torch.nn.functional.interpolate(dm.reshape(1, 1, *dm.shape), scale_factor=4, mode="nearest")[0, 0].numpy()
+    K = torch.as_tensor(g["K_rgb"])
+    final = logp.clone()
+    np.random.seed(3)
+    for _ in range(2):
+        uf, _u = O.ufield(final, olc.d_candi, K, O.uf_params("kitti"), BV_log=True)
+        paths, _v = olc.plan_m1(uf.squeeze(0), prm)
+        final = O.bayes_fuse(final, [olc.sense(dm_up, p)[0] for p in paths], 1, 5)
+    _volume_close(fused.cpu().numpy(), final.numpy(), "lc_process m1")

@@ -349,3 +349,31 @@ def test_plan_m1_oracle_matches_reference_golden():
     for i, p in enumerate(pts):
         np.testing.assert_array_equal(p, g["pts%d" % i], err_msg="curtain %d" % i)
     np.testing.assert_array_equal(vis, g["field_visual"])
+
+
+def _real_oracles(g):
+    from oracle import lc_oracle as LO
+    Wr, Hr = [int(v) for v in g["size_rgb"]]
+    Wl, Hl = [int(v) for v in g["size_lc"]]
+    algo = LO.LightCurtainOracle(g["K_rgb"], Wr, Hr, g["d_candi"], g["d_candi_up"])
+    real = LO.LightCurtainOracle(g["K_lc"], Wl, Hl, g["d_candi"], g["d_candi_up"])
+    real.set_input_camera(g["K_rgb"], [Wr, Hr], g["rTc"])
+    return algo, real
+
+
+def test_lc_loop_real_oracle_matches_reference_golden():
+    """(f)2: the oracle's composition of lc_process_real (recorded-sweep sampling, re-projection, intensity-model
+    likelihood, Bayesian update) against the UNMODIFIED BaseModel.lc_process_real (tests/golden/lc_process_real.npz):
+    bit-identical for planner "default" (2 iterations) and "m1" (1 iteration, same numpy seed)."""
+    from oracle import dpv_oracle as O
+    from oracle import lc_oracle as LO
+    g = np.load(os.path.join(G, "lc_process_real.npz"))
+    algo, real = _real_oracles(g)
+    logp = torch.as_tensor(g["logp"])
+    out = LO.lc_loop_real(logp, g["sweep"], algo, real, g["K_rgb"], O.uf_params("kitti"), 2, "default", {"step": [0.5]}, 1, 5)
+    np.testing.assert_array_equal(out.numpy(), g["fused_default"])
+    np.random.seed(int(g["seed_m1"]))
+    out = LO.lc_loop_real(logp, g["sweep"], algo, real, g["K_rgb"], O.uf_params("kitti"), 1, "m1",
+                          {"step": 2, "interval": 6}, 1, 5)
+    np.testing.assert_array_equal(out.numpy(), g["fused_m1"])
+    assert np.abs(g["fused_default"] - g["logp"]).max() > 1.0          # the sweep did change the volume
