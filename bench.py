@@ -290,6 +290,7 @@ def run_b200(args):
         for p_ in pipes:
             p_.fuse_events = [] if on else None
             p_.planner_events = [] if on else None
+            p_.lsm_events = None
 
     if graphs is None:
         run_steps(args.steps)                           # as above for eager launches
@@ -341,7 +342,7 @@ def run_b200(args):
     with torch.cuda.stream(main):
         pipe.step(xs[0])                                # warm: eager launches after graph replays
         s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        pipe.fuse_events, pipe.planner_events = [], []
+        pipe.fuse_events, pipe.planner_events, pipe.lsm_events = [], [], []
         s0.record(main)
         for _ in range(3):
             pipe.step(xs[0])
@@ -350,6 +351,7 @@ def run_b200(args):
     single_batch_ms = s0.elapsed_time(s1) / 3
     fuse_solo = [a.elapsed_time(b) for a, b in pipe.fuse_events]
     plan_solo = [a.elapsed_time(b) for a, b in pipe.planner_events]
+    lsm_solo = [a.elapsed_time(b) for a, b in pipe.lsm_events]
     set_kernel_events(False)
     graphs = replay
 
@@ -362,6 +364,19 @@ def run_b200(args):
     # dominates by TIME (the DP planner: latency-bound, SURVEY 8d reports it in microseconds and SMs, not GB/s)
     alg = pipe.algorithmic_bytes()
     roof = None
+    traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+    traffic = json.load(open(traffic_file)) if os.path.exists(traffic_file) else {}
+    t_lsm = statistics.mean(lsm_solo) / 1e3
+    lsm = {"kernel": "lsm_stats_tma_kernel" if meta["D"] in (64, 128) else "lsm_stats_kernel", "bound": "hbm",
+           "achieved": round(alg["lsm_full"] / t_lsm / 1e9, 1), "peak": peak_gbs, "peak_source": peak_src, "unit": "GB/s",
+           "frac": round(alg["lsm_full"] / t_lsm / 1e9 / peak_gbs, 4), "traffic": traffic.get("lsm_stats_tma_kernel"),
+           "launch_ms": round(t_lsm * 1e3, 4), "launches_timed": len(lsm_solo),
+           "algorithmic_bytes_per_launch": alg["lsm_full"],
+           "timed_with": "CUDA events around each launch, 1 batch in flight (pass after the timed region)",
+           "share_of_single_batch_step": round(sum(lsm_solo) / 3 / single_batch_ms, 4),
+           "role": "full-resolution log-softmax + statistics + carry (TMA tiles): reads the logits, writes the DPV"}
+    if not fuse_solo:
+        roof = lsm                       # a workload without LC iterations: this is the kernel that moves the most bytes
     if fuse_solo:
         t = statistics.mean(fuse_solo) / 1e3
         ach = alg["sense_fuse"] / t / 1e9
@@ -378,9 +393,8 @@ def run_b200(args):
             roof["in_flight"] = {"launch_ms": round(statistics.mean(tin), 4), "batches": S,
                                  "note": "event-to-event inside the timed region: includes the slices other batches' "
                                          "kernels get on the same SMs, so it is not the kernel's own duration"}
-        tr = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tr):
-            roof["traffic"] = json.load(open(tr)).get("sense_fuse_kernel")
+        roof["traffic"] = traffic.get("sense_fuse_kernel")
+        roof["also"] = {"lsm": lsm}
         if plan_solo:
             nmaps = B * (1 + 2 * len(meta["step"]))
             roof["dominant_by_time"] = {

@@ -151,6 +151,7 @@ class DpvLcPipeline:
         self._center, self._center_key = None, None
         self.fuse_events = None          # optional list collecting (start, end) CUDA events of sense+fuse launches
         self.planner_events = None       # the same for the DP planner solves
+        self.lsm_events = None           # the same for the full-resolution log-softmax + statistics launch
         self.trace = None                # optional list: per-iteration uf / umaps / ks / logp clones (parity tests)
 
     def step(self, x):
@@ -171,7 +172,13 @@ class DpvLcPipeline:
         if m.get("warp_feature", True):                              # nmode "lc" has no feature warp (models.py:640-661)
             warped = ops.warp_feature(x["feat_raw"], x["K"], x["R"], x["t"], x["rays"], center, d)
         bv_upd = ops.logsoftmax_stats(bv, d, add=x["bv_resi"], want_var=False, want_entropy=False)["logp"]
+        if self.lsm_events is not None:
+            l0, l1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            l0.record()
         r = ops.logsoftmax_stats(x["dec_logits"], d, want_carry=True)
+        if self.lsm_events is not None:
+            l1.record()
+            self.lsm_events.append((l0, l1))
         out = dict(depth=r["mean"], var=r["var"], entropy=r["entropy"], carry=r["carry"], bv_low=bv_upd, warped=warped,
                    logp=r["logp"])
         if m["iterations"] > 0:
