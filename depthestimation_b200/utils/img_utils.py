@@ -106,7 +106,11 @@ ERROR_NAMES = ("mae", "rmse", "inverse mae", "inverse rmse", "log mae", "log rms
 
 def depth_error(predicted, truth):
     """img_utils.py:162-167 + depthError (evaluate_depth.h:20-118): 9 errors of one image pair.
-    Accepts CUDA tensors [H,W] (or [n,H,W] -> [n,9]); zeros are invalid, as in the reference."""
+    Accepts CUDA tensors [H,W] (or [n,H,W] -> [n,9]); zeros are invalid, as in the reference.
+    As in the reference, `predicted` is what the C++ side takes for its ground-truth parameter
+    (dlib.depthError(predicted + eps, truth + eps) against depthError(D_gt, D_ipol)): validity is read from the predicted
+    map -- the trainer multiplies it by the mask first, default_trainer.py:328-331 -- and the two relative errors are
+    divided by it (tests/golden/deval_ref.npz records the reference's numbers)."""
     p = torch.as_tensor(predicted)
     t = torch.as_tensor(truth)
     single = p.dim() == 2
@@ -114,9 +118,9 @@ def depth_error(predicted, truth):
         p, t = p.unsqueeze(0), t.unsqueeze(0)
     p = torch.where(p == 0, torch.full_like(p, -1.0), p) + epsilon
     t = torch.where(t == 0, torch.full_like(t, -1.0), t) + epsilon
-    out = ops.depth_errors(p, t)
+    out = ops.depth_errors(pred=t, gt=p)
     if bool((out[:, 9] == 0).any()):
-        raise RuntimeError("depth_error: ground truth has no valid pixel")   # evaluate_depth.h:94-97 throws
+        raise RuntimeError("depth_error: no valid pixel")                    # evaluate_depth.h:94-97 throws
     return out[0, :9] if single else out[:, :9]
 
 

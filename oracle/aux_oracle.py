@@ -127,8 +127,11 @@ def correlation_backward(grad_out, x1, x2, pad_size, kernel_size, max_displaceme
 # (f)1: external/deval_lib/src/evaluate_depth.h depthError, utils/img_utils.py depth_error / compute_unc_rmse
 # --------------------------------------------------------------------------
 def depth_errors(pred, gt):
-    """depthError, evaluate_depth.h:20-118, after img_utils.depth_error's zero -> -1 (+ eps) marking
-    (img_utils.py:162-167).  Sequential float accumulation in the reference's loop order (u outer, v inner)."""
+    """C++ depthError(D_gt = gt, D_ipol = pred), evaluate_depth.h:20-118, after img_utils.depth_error's zero -> -1
+    (+ eps) marking (img_utils.py:162-167).  Sequential float accumulation in the reference's loop order (u outer, v
+    inner).  Pinned to the reference's own header compiled verbatim (oracle/ref_deval.py, tests/golden/deval_ref.npz):
+    identical except the three log metrics, where numpy's float32 log and glibc's logf differ in the last bit (4e-7).
+    The reference's Python wrapper passes the maps the other way round: see depth_error_py."""
     eps = np.float32(np.finfo(np.float64).eps)
     p = np.asarray(pred, np.float32).copy()
     g = np.asarray(gt, np.float32).copy()
@@ -165,6 +168,13 @@ def depth_errors(pred, gt):
         err[7] = seq(e / dg) / n
         err[8] = seq(e2 / (dg * dg)) / n
     return err
+
+
+def depth_error_py(predicted, truth):
+    """utils/img_utils.py:162-167 AS THE REFERENCE RUNS IT: dlib.depthError(predicted + eps, truth + eps) binds the
+    C++ parameters (D_gt, D_ipol) positionally, so the PREDICTED map plays D_gt -- validity comes from it (the trainer
+    has multiplied it by the mask, default_trainer.py:328-331) and abs / squared relative are divided by it."""
+    return depth_errors(pred=truth, gt=predicted)
 
 
 def unc_rmse(field_truth, field_pred, d_candi):

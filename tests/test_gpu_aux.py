@@ -217,13 +217,23 @@ def test_depth_error_and_eval_errors():
     gt = 5.0 + 30.0 * torch.rand(3, H, W, generator=gen)
     gt[torch.rand(3, H, W, generator=gen) < 0.3] = 0.0              # KITTI-style sparse ground truth
     pred = (gt + torch.randn(3, H, W, generator=gen)).clamp(min=0.5)
-    pred[gt == 0] = 7.0
+    pred[gt == 0] = 0.0                                              # default_trainer.py:328-331: prediction * mask
     got = img_utils.depth_error(pred.cuda(), gt.cuda())
     assert got.shape == (3, 9)
     for i in range(3):
-        ref = A.depth_errors(pred[i].numpy(), gt[i].numpy())
+        ref = A.depth_error_py(pred[i].numpy(), gt[i].numpy())
         # the reference accumulates 4e5 terms sequentially in fp32 (relative error ~1e-5); the kernel sums in fp64
         np.testing.assert_allclose(got[i].cpu().numpy(), ref, rtol=1e-4)
+    # the reference's own numbers (evaluate_depth.h compiled verbatim under the unmodified img_utils.depth_error)
+    d = load("deval_ref")
+    errs = []
+    for i in range(3):
+        e = img_utils.depth_error(cu(d["pred%d" % i]), cu(d["truth%d" % i]))
+        np.testing.assert_allclose(e.cpu().numpy(), d["err%d" % i], rtol=1e-4)
+        errs.append(e)
+    res = img_utils.eval_errors(errs)
+    assert list(res) == [str(n) for n in d["eval_names"]]
+    np.testing.assert_allclose(np.array([res[k] for k in res], np.float32), d["eval"], rtol=1e-4)
     one = img_utils.depth_error(pred[0].cuda(), gt[0].cuda())
     assert one.shape == (9,) and torch.equal(one, got[0])
     res = img_utils.eval_errors([got[i] for i in range(3)])
@@ -231,7 +241,7 @@ def test_depth_error_and_eval_errors():
     np.testing.assert_allclose(res["mae"][0], float(got[:, 0].mean()), rtol=1e-6)
     assert res["mae"][1] == min(1.0, float(got[:, 0].min())) and res["mae"][2] == float(got[:, 0].max())
     with pytest.raises(RuntimeError):
-        img_utils.depth_error(pred[0].cuda(), torch.zeros(H, W).cuda())
+        img_utils.depth_error(torch.zeros(H, W).cuda(), gt[0].cuda())          # validity is read from the predicted map
 
 
 def test_compute_unc_rmse_and_field():

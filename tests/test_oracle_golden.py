@@ -163,9 +163,46 @@ def test_aux_rows_against_reference():
     close(real_sensor_likelihood(g["true_d"], g["true_sensed"], 3.0, g["true_peak_img"]), g["true_dpv_peak"], rtol=1e-5)
 
 
+def test_depth_error_oracle_matches_reference_header():
+    """(f)1 pinned: utils/img_utils.py depth_error / eval_errors on top of the reference's evaluate_depth.h compiled
+    verbatim (tests/golden/make_deval_ref.py -> deval_ref.npz).  The restatement is identical except where numpy's
+    float32 log and glibc's logf differ in the last bit (log mae / log rmse / scale-invariant log: <= 1e-6 relative)."""
+    from oracle import aux_oracle as A
+    g = np.load(os.path.join(G, "deval_ref.npz"))
+    errs = []
+    for i in range(3):
+        e = A.depth_error_py(g["pred%d" % i], g["truth%d" % i])
+        np.testing.assert_array_equal(e[[0, 1, 2, 3, 7, 8]], g["err%d" % i][[0, 1, 2, 3, 7, 8]])
+        np.testing.assert_allclose(e[[4, 5, 6]], g["err%d" % i][[4, 5, 6]], rtol=1e-6)
+        errs.append(g["err%d" % i])
+    # the wrapper's argument order matters: with the maps the other way round the relative errors differ
+    other = A.depth_errors(pred=g["pred0"], gt=g["truth0"])
+    assert abs(other[7] - g["err0"][7]) > 1e-4 * g["err0"][7]
+    # evaluateErrors: mean, min (starts at 1), max (starts at 0) per metric
+    e = np.stack(errs)
+    for k in range(9):
+        mean = np.float32(0)
+        for v in e[:, k]:
+            mean = np.float32(mean + v)
+        np.testing.assert_array_equal(g["eval"][k], np.array([mean / np.float32(3), min(1.0, e[:, k].min()),
+                                                              max(0.0, e[:, k].max())], np.float32))
+
+
+def test_deval_golden_is_what_the_reference_produces_now():
+    from oracle import ref_deval
+    if not ref_deval.available():
+        pytest.skip("/root/reference is not on this machine")
+    g = np.load(os.path.join(G, "deval_ref.npz"))
+    eps = np.finfo(float).eps
+    p, t = g["pred2"].copy(), g["truth2"].copy()
+    p[p == 0] = -1
+    t[t == 0] = -1
+    got = ref_deval.depth_error(pred=(t + eps).astype(np.float32), gt=(p + eps).astype(np.float32))   # (D_gt, D_ipol) = (predicted, truth)
+    np.testing.assert_array_equal(got, g["err2"])
+
+
 def test_depth_errors_restatement_properties():
-    """depthError has no golden vector in the reference (parity unpinned, see oracle/aux_oracle.py): check the
-    restatement on hand-computable cases."""
+    """The restatement of the C++ function on hand-computable cases (the pin is the test above)."""
     from oracle import aux_oracle as A
     gt = np.array([[2.0, 4.0, 0.0], [8.0, 0.0, 1.0]], np.float32)
     e = A.depth_errors(gt, gt)
