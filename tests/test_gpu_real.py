@@ -284,10 +284,7 @@ def test_lc_process_with_separate_lc_camera_against_oracle():
     np.testing.assert_allclose(trace[0]["uf"].cpu().numpy(), otrace[0]["uf"][0].numpy(), rtol=1e-4, atol=1e-6,
                                equal_nan=True)
     got, ref = fused.cpu().numpy(), exp.numpy()
-    bad = np.abs(got - ref).max(1) > 1e-3 * np.maximum(np.abs(ref).max(1), 1.0)
-    assert bad.mean() < 0.02, bad.mean()               # pixels whose curtain point moved by a DP tie / z-buffer border
-    keep = ~bad[0]
-    np.testing.assert_allclose(got[0][:, keep], ref[0][:, keep], rtol=1e-3, atol=2e-3)
+    _volume_close(got, ref, "separate LC camera")      # 1e-4; pixels whose curtain point moved by a DP tie / z-buffer border counted
 
 
 def test_depth_to_points_bit_exact():
@@ -334,13 +331,14 @@ def _real_rigs(g):
 
 
 def _volume_close(got, ref, what):
-    """Composed loops: a pixel may differ when a curtain point moved by a DP tie, a z-buffer border or a near-tie of the
-    nearest recorded slice (all decided on values 1e-6 apart); those pixels are counted (< 2 %), the rest compared at
-    rtol 1e-3 / atol 2e-3 on log-probabilities that accumulate three fp32 stages (field, likelihood, update)."""
+    """Composed loops, north_star's 1e-4: a pixel may differ when a curtain point moved by a DP tie, a z-buffer border
+    or a near-tie of the nearest recorded slice (all decided on values 1e-6 apart); such pixels are counted (< 0.5 %;
+    measured on a B200: none), the rest compared at rtol 1e-4 with an absolute floor of 1e-4 in log space (measured:
+    max |d log p| 1.9e-5, profiles/diag_composed.py)."""
     bad = np.abs(got - ref).max(1) > 1e-3 * np.maximum(np.abs(ref).max(1), 1.0)
-    assert bad.mean() < 0.02, (what, bad.mean())
+    assert bad.mean() < 0.005, (what, bad.mean())
     keep = ~bad[0]
-    np.testing.assert_allclose(got[0][:, keep], ref[0][:, keep], rtol=1e-3, atol=2e-3, err_msg=what)
+    np.testing.assert_allclose(got[0][:, keep], ref[0][:, keep], rtol=1e-4, atol=1e-4, err_msg=what)
     return bad.mean()
 
 
