@@ -47,6 +47,9 @@ def parse():
                     help="exchange of the per-frame depth maps between ranks: one all_gather per round of S steps on a "
                          "side stream (default), one per step, one after the last step, or none (diagnostic only: the "
                          "path requires the exchange)")
+    ap.add_argument("--planner-pack", type=int, default=1, choices=[1, 2],
+                    help="maps per CTA pair of the DP planner in the throughput region (diagnostic: 2 halves the SMs a "
+                         "solve holds and measured 1-5 %% lower throughput, DESIGN.md 6); the single-batch pass uses 1")
     ap.add_argument("--streams", type=int, default=6,
                     help="independent batches in flight (steps are issued round-robin on this many CUDA streams)")
     return ap.parse_args()
@@ -179,7 +182,8 @@ def run_b200(args):
     B = meta["B"]
     S = pick_slots(args.streams, args.steps)
     hit_noise = args.hit_noise if meta["iterations"] > 0 else 0.0
-    pipes = [DpvLcPipeline(meta, dev, hit_noise=hit_noise, noise_seed=1000 * rank + sl) for sl in range(S)]
+    pack = args.planner_pack
+    pipes = [DpvLcPipeline(meta, dev, hit_noise=hit_noise, noise_seed=1000 * rank + sl, planner_pack=pack) for sl in range(S)]
     streams = [torch.cuda.Stream(dev) for _ in range(S)]
     pipe = pipes[0]
     x = {k: v.to(dev) for k, v in host.items()}
@@ -339,6 +343,7 @@ def run_b200(args):
     # own durations -- the condition the ncu launch list measures too.  Right after the timed region, same data.
     replay, graphs = graphs, None
     set_kernel_events(False)
+    pipe.set_planner_pack(1)                            # one batch alone: the latency setting (the graphs keep theirs)
     with torch.cuda.stream(main):
         pipe.step(xs[0])                                # warm: eager launches after graph replays
         s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -353,6 +358,7 @@ def run_b200(args):
     plan_solo = [a.elapsed_time(b) for a, b in pipe.planner_events]
     lsm_solo = [a.elapsed_time(b) for a, b in pipe.lsm_events]
     set_kernel_events(False)
+    pipe.set_planner_pack(pack)
     graphs = replay
 
     # ---- e2e: host buffers in, host results out, copies inside the timed region ------------------
@@ -419,6 +425,7 @@ def run_b200(args):
                            "curtains_per_iteration": 1 + 2 * len(meta["step"]), "hit_noise": hit_noise,
                            "noise": "pre-generated pool per batch slot" if hit_noise > 0 else "none",
                            "parallelism": "batch-shard x%d" % world, "streams_in_flight": S, "launch": launch_mode,
+                           "planner_pack": {"throughput_region": pack, "single_batch_pass": 1},
                            "gather": ({"round": "one all_gather per round of %d steps on a side stream" % S,
                                        "step": "per-step all_gather on a side stream", "end": "one all_gather after "
                                        "the last step", "none": "DISABLED (diagnostic run)"}[args.gather]

@@ -61,6 +61,7 @@ SIGNATURES = {
     "lc_planner_destroy": (None, [c_vp]),
     "lc_planner_edge_count": (c_ll, [c_vp]),
     "lc_planner_solve": (c_int, [c_vp, c_fp, c_int, c_ip, c_fp, c_ip, c_vp]),
+    "lc_planner_set_pack": (c_int, [c_vp, c_int]),
     "lc_curtain_planes": (c_int, [c_vp, c_fp, c_ip, c_int, c_int, c_fp, c_fp, c_vp]),
     "lc_sense_image": (c_int, [c_vp, c_fp, c_fp, c_fp, c_int, c_int, c_fp, c_fp, c_vp]),
     "lc_sense_likelihood": (c_int, [c_vp, c_fp, c_fp, c_fp, c_int, c_int, c_fp, c_int, c_fp, c_vp]),

@@ -72,4 +72,5 @@ struct LcPlanner {
   };
   std::map<void*, Log> logs;    // keyed by cudaStream_t
   std::mutex mu;
+  int pack = 1;                 // maps per CTA pair (lc_planner_set_pack): 1 = lowest latency, 2 = half the SMs per solve
 };

@@ -59,22 +59,40 @@ __device__ __forceinline__ unsigned long long ld_relaxed(const unsigned long lon
   return v;
 }
 
+// A "team" is the set of threads that solves one map inside a CTA.  PACK = 1: the whole CTA (threadIdx.x, blockDim.x,
+// __syncthreads(): the code is what it was).  PACK = 2 (throughput mode, lc_planner_set_pack): a CTA of 1024 threads
+// holds two teams of 512, each with its own half of the dynamic shared memory and its own named barrier, so a cluster
+// of two CTAs solves two maps on two SMs instead of one: the solve is a dependent chain that leaves most issue slots
+// idle (part A works with 8 of its 16 warps), and two independent chains share an SM's schedulers.
+constexpr int kTeamThreads = 512;
+template <int PACK> __device__ __forceinline__ int team_tid() { return PACK == 1 ? (int)threadIdx.x : (int)(threadIdx.x & (kTeamThreads - 1)); }
+template <int PACK> __device__ __forceinline__ int team_size() { return PACK == 1 ? (int)blockDim.x : kTeamThreads; }
+template <int PACK> __device__ __forceinline__ void team_sync(int half, int count) {
+  if (PACK == 1) __syncthreads();
+  else asm volatile("bar.sync %0, %1;" ::"r"(half + 1), "r"(count) : "memory");
+}
+
 // ------------------------------------------------------------------------------------------------
 // part A: first keys (unc) of every ray, successor where a single edge wins
 // ------------------------------------------------------------------------------------------------
-template <int LANES, int NQL>
+template <int LANES, int NQL, int PACK>
 __device__ __forceinline__ void planner_part_a(unsigned char* smraw, const float* __restrict__ umap, int W, int R,
-                                               const uint8_t* __restrict__ win, unsigned long long* __restrict__ lg, unsigned tag) {
+                                               const uint8_t* __restrict__ win, unsigned long long* __restrict__ lg, unsigned tag,
+                                               int half) {
   constexpr int NQ = LANES * NQL;                                 // groups of four per ray
   constexpr int RP = 4 * NQ;                                      // padded ray length
   constexpr int SLOT = RP + 2 * NQ;                               // unc (pad -inf) + qm (padded: no index clamp)
   float* state = reinterpret_cast<float*>(smraw);                 // [2][SLOT]
-  const int k = threadIdx.x / LANES, s = threadIdx.x % LANES;
+  const int tid = team_tid<PACK>();
+  const int k = tid / LANES, s = tid % LANES;
   const bool active = k < R;
   const unsigned full = 0xffffffffu;
-  for (int i = threadIdx.x; i < 2 * SLOT; i += blockDim.x) state[i] = -INFINITY;
-  __syncthreads();
-  if ((int)threadIdx.x >= ((R * LANES + 31) & ~31)) {             // warps without nodes only keep the barriers company
+  const int nact = (R * LANES + 31) & ~31;                        // threads of the warps that hold nodes
+  if (PACK > 1 && tid >= nact) return;                            // a named barrier counts only those
+  const int nth = PACK == 1 ? team_size<PACK>() : nact;
+  for (int i = tid; i < 2 * SLOT; i += nth) state[i] = -INFINITY;
+  team_sync<PACK>(half, nact);
+  if (PACK == 1 && tid >= nact) {                                 // warps without nodes only keep the barriers company
     for (int i = W - 1; i >= 0; i--) __syncthreads();
     return;
   }
@@ -183,7 +201,7 @@ __device__ __forceinline__ void planner_part_a(unsigned char* smraw, const float
         st_relaxed(lg + (size_t)i * RP + k, log_entry(bu, code, tag));
       }
     }
-    __syncthreads();                                              // ray i complete in shared memory
+    team_sync<PACK>(half, nact);                                  // ray i complete in shared memory
   }
 }
 
@@ -196,12 +214,12 @@ struct LogRay {          // what a node's thread needs of one ray
   unsigned w;
 };
 
-template <int NCH>
+template <int NCH, int PACK>
 __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float* __restrict__ umap, int W, int R,
                                                const float* __restrict__ theta, const float* __restrict__ node_xz,
                                                const uint8_t* __restrict__ win, const unsigned long long* lg,
                                                unsigned tag, int map, int32_t* __restrict__ ks,
-                                               float* __restrict__ xz, int32_t* __restrict__ counts) {
+                                               float* __restrict__ xz, int32_t* __restrict__ counts, int half) {
   constexpr int RP = 128 * NCH;
   constexpr int SLOT = 3 * RP;                                    // unc (pad -inf), las, th of one ray
   float* state = reinterpret_cast<float*>(smraw);                 // [3][SLOT] ring over rays
@@ -209,20 +227,24 @@ __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float
   int* list = reinterpret_cast<int*>(nin + 2 * RP);               // [2][RP] tie nodes of a ray
   int16_t* path = reinterpret_cast<int16_t*>(list + 2 * RP);      // [W rounded to 8]
   uint8_t* sub = reinterpret_cast<uint8_t*>(path + ((W + 7) & ~7));   // [W][R]
-  __shared__ int s_nt[3];                                         // tie counts, ring like state
-  __shared__ int s_cnt;
-  __shared__ volatile int s_gaveup;                               // some wait ran out of polls: the result is void
+  __shared__ int s_nt_all[PACK][3];                               // tie counts, ring like state
+  __shared__ int s_cnt_all[PACK];
+  __shared__ volatile int s_gaveup_all[PACK];                     // some wait ran out of polls: the result is void
+  int* s_nt = s_nt_all[half];
+  int& s_cnt = s_cnt_all[half];
+  volatile int& s_gaveup = s_gaveup_all[half];
 
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-  const int k = threadIdx.x;                                      // node whose log entries this thread follows
+  const int tid = team_tid<PACK>(), nth = team_size<PACK>();
+  const int lane = tid & 31, warp = tid >> 5, nwarps = nth >> 5;
+  const int k = tid;                                              // node whose log entries this thread follows
   const bool node = k < R;
   const bool node_warp = warp * 32 < R;
   const unsigned full = 0xffffffffu;
 
-  for (int i = threadIdx.x; i < 3 * SLOT; i += blockDim.x) state[i] = ((i % SLOT) < RP) ? -INFINITY : 0.f;
-  if (threadIdx.x < 3) s_nt[threadIdx.x] = 0;
-  if (threadIdx.x == 0) s_gaveup = 0;
-  __syncthreads();
+  for (int i = tid; i < 3 * SLOT; i += nth) state[i] = ((i % SLOT) < RP) ? -INFINITY : 0.f;
+  if (tid < 3) s_nt[tid] = 0;
+  if (tid == 0) s_gaveup = 0;
+  team_sync<PACK>(half, nth);
 
   auto load_ray = [&](int i) {                                    // may come back with an old tag: checked at use
     LogRay r;
@@ -286,13 +308,13 @@ __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float
   int code = kCodeBare;
   float tn = 0.f;
   if (node_warp) stage_ray(W - 1, load_ray(W - 1), sb, code, tn);
-  __syncthreads();
+  team_sync<PACK>(half, nth);
 
   for (int i = W - 1; i >= 0; i--) {
     const float* sp = state + sa * SLOT;                          // ray i+1: unc, las, th
     float* sc = state + sb * SLOT;                                // ray i
     uint8_t* subi = sub + (size_t)i * R;
-    if (threadIdx.x == 0) s_nt[sa] = 0;                           // its ties were read a step ago; pushed again next step
+    if (tid == 0) s_nt[sa] = 0;                                   // its ties were read a step ago; pushed again next step
     if (node_warp) {
       // ---- nodes A finished: second key from the successor (planning.cpp:197-198); bare nodes: las 0
       if (node) {
@@ -344,12 +366,15 @@ __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float
         subi[rk] = (uint8_t)be;
       }
     }
-    __syncthreads();
+    team_sync<PACK>(half, nth);
     const int t = sa; sa = sb; sb = sc_; sc_ = t;                 // ray i+1's slot is free for ray i-2
   }
   const int pc = sa;                                              // ray 0 after the last rotation
   // ray 0 is in buffer pc.  Best start against a default (0,0,null) trajectory (planning.cpp:99-104)
-  if (threadIdx.x == 0) {
+  // (the thread index and team size are read again here instead of being kept in registers across the ray loop, and
+  // for PACK = 1 with the built-in variables' own types: either difference puts the kernel at 64 registers and into
+  // its slow schedule)
+  if ((PACK == 1 ? threadIdx.x : (unsigned)team_tid<PACK>()) == 0) {
     const float* u0 = state + pc * 3 * RP;
     const float* l0 = u0 + RP;
     float bu = 0.f, bl = 0.f;
@@ -374,9 +399,11 @@ __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float
     s_cnt = cnt;
     if (counts) counts[map] = cnt;
   }
-  __syncthreads();
+  team_sync<PACK>(half, kTeamThreads);
   const int cnt = s_cnt;
-  for (int i = threadIdx.x; i < W; i += blockDim.x) {
+  const unsigned first = PACK == 1 ? threadIdx.x : (unsigned)team_tid<PACK>();
+  const unsigned stride = PACK == 1 ? blockDim.x : (unsigned)kTeamThreads;
+  for (int i = first; i < W; i += stride) {
     int kk = i < cnt ? path[i] : -1;
     if (ks) ks[(size_t)map * W + i] = kk;
     if (xz) {
@@ -391,16 +418,19 @@ __device__ __forceinline__ void planner_part_b(unsigned char* smraw, const float
 }
 
 // grid = 2 CTAs per umap, launched as clusters of two so that the producer and its consumer are co-resident
-template <int LANES, int NQL, bool DEVTAG>
-__global__ void __launch_bounds__(1024)
-planner_solve_kernel(const float* __restrict__ umaps, int W, int R, const float* __restrict__ theta,
+template <int LANES, int NQL, bool DEVTAG, int PACK>
+__device__ __forceinline__ void planner_solve_body(const float* __restrict__ umaps, int W, int R, const float* __restrict__ theta,
                      const float* __restrict__ node_xz, const uint8_t* __restrict__ win, unsigned long long* log_base,
                      size_t log_per_map, unsigned host_tag, unsigned* __restrict__ epoch, int32_t* __restrict__ ks,
-                     float* __restrict__ xz, int32_t* __restrict__ counts) {
+                     float* __restrict__ xz, int32_t* __restrict__ counts, int nmaps, unsigned team_smem) {
   constexpr int RP = 4 * LANES * NQL;
   static_assert(RP % 128 == 0, "ray length must fill whole warps in part B");
-  extern __shared__ __align__(16) unsigned char smraw[];
-  const int map = blockIdx.x >> 1;
+  static_assert(PACK == 1 || !DEVTAG, "the device-counter tag variant is one map per CTA pair");
+  extern __shared__ __align__(16) unsigned char smraw_all[];
+  const int half = PACK == 1 ? 0 : (int)(threadIdx.x / kTeamThreads);
+  unsigned char* smraw = PACK == 1 ? smraw_all : smraw_all + (size_t)half * team_smem;
+  const int map = PACK == 1 ? (int)(blockIdx.x >> 1) : (int)(blockIdx.x >> 1) * PACK + half;
+  if (PACK > 1 && map >= nmaps) return;                           // an odd number of maps: the last pair's second team
   const float* umap = umaps + (size_t)map * R * W;
   unsigned long long* lg = log_base + (size_t)map * log_per_map;
   // The tag of this solve's log entries.  Launched directly, it is a kernel parameter the host counts up (1..32767;
@@ -412,9 +442,9 @@ planner_solve_kernel(const float* __restrict__ umaps, int W, int R, const float*
   const unsigned tag = DEVTAG ? 32768u + (*reinterpret_cast<volatile unsigned*>(epoch) & 32767u) : (host_tag & 0xffffu);
   if ((blockIdx.x & 1) == 0) {
     if (host_tag >> 31) return;                                   // test hook (DPV_PLANNER_TEST_NO_PRODUCER): A never writes
-    planner_part_a<LANES, NQL>(smraw, umap, W, R, win, lg, tag);
+    planner_part_a<LANES, NQL, PACK>(smraw, umap, W, R, win, lg, tag, half);
   }
-  else planner_part_b<RP / 128>(smraw, umap, W, R, theta, node_xz, win, lg, tag, map, ks, xz, counts);
+  else planner_part_b<RP / 128, PACK>(smraw, umap, W, R, theta, node_xz, win, lg, tag, map, ks, xz, counts, half);
   if (DEVTAG) {
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -424,6 +454,27 @@ planner_solve_kernel(const float* __restrict__ umaps, int W, int R, const float*
       }
     }
   }
+}
+
+template <int LANES, int NQL, bool DEVTAG>
+__global__ void __launch_bounds__(1024)
+planner_solve_kernel(const float* __restrict__ umaps, int W, int R, const float* __restrict__ theta,
+                     const float* __restrict__ node_xz, const uint8_t* __restrict__ win, unsigned long long* log_base,
+                     size_t log_per_map, unsigned host_tag, unsigned* __restrict__ epoch, int32_t* __restrict__ ks,
+                     float* __restrict__ xz, int32_t* __restrict__ counts) {
+  planner_solve_body<LANES, NQL, DEVTAG, 1>(umaps, W, R, theta, node_xz, win, log_base, log_per_map, host_tag, epoch, ks, xz,
+                                            counts, 0, 0u);
+}
+
+// two maps per CTA pair (lc_planner_set_pack(2)): teams of 512 threads, see team_sync
+template <int LANES, int NQL>
+__global__ void __launch_bounds__(1024)
+planner_solve_pack2_kernel(const float* __restrict__ umaps, int W, int R, const float* __restrict__ theta,
+                           const float* __restrict__ node_xz, const uint8_t* __restrict__ win, unsigned long long* log_base,
+                           size_t log_per_map, unsigned host_tag, unsigned* __restrict__ epoch, int32_t* __restrict__ ks,
+                           float* __restrict__ xz, int32_t* __restrict__ counts, int nmaps, unsigned team_smem) {
+  planner_solve_body<LANES, NQL, false, 2>(umaps, W, R, theta, node_xz, win, log_base, log_per_map, host_tag, epoch, ks, xz,
+                                           counts, nmaps, team_smem);
 }
 
 }  // namespace dpv
@@ -497,17 +548,22 @@ int launch_solve(LcPlanner* p, const float* umaps, int n, int warps, int32_t* ks
   }
   if (const char* e = getenv("DPV_PLANNER_TEST_NO_PRODUCER"))    // exercises part B's bounded wait (tests only)
     if (atoi(e) != 0 && !devtag) host_tag |= 0x80000000u;
-  auto kern = devtag ? planner_solve_kernel<LANES, NQL, true> : planner_solve_kernel<LANES, NQL, false>;
-  DPV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int threads = ((R * LANES + 31) / 32) * 32;                     // part A: LANES threads per node
   if (warps < 1) warps = 1;                                       // part B: one warp per tie node
   if (threads < 32 * warps) threads = 32 * warps;
   if (threads < ((R + 31) / 32) * 32) threads = ((R + 31) / 32) * 32;            // B follows one node per thread
   DPV_REQUIRE(threads <= 1024, "lc_planner_solve: R=%d needs %d threads", R, threads);
+  // two maps per CTA pair (lc_planner_set_pack) when both teams' shared memory fits and a team is 512 threads
+  const size_t team_smem = (smem + 127) & ~(size_t)127;
+  const bool pack2 = p->pack == 2 && !devtag && n >= 2 && threads <= kTeamThreads && 2 * team_smem + 128 <= 227 * 1024;
+  auto kern = devtag ? planner_solve_kernel<LANES, NQL, true> : planner_solve_kernel<LANES, NQL, false>;
+  auto kern2 = planner_solve_pack2_kernel<LANES, NQL>;
+  if (pack2) DPV_CUDA(cudaFuncSetAttribute(kern2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * team_smem)));
+  else DPV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)(2 * n));
-  cfg.blockDim = dim3((unsigned)threads);
-  cfg.dynamicSmemBytes = smem;
+  cfg.gridDim = dim3((unsigned)(pack2 ? 2 * ((n + 1) / 2) : 2 * n));
+  cfg.blockDim = dim3((unsigned)(pack2 ? 2 * kTeamThreads : threads));
+  cfg.dynamicSmemBytes = pack2 ? 2 * team_smem : smem;
   cfg.stream = st;
   cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -518,13 +574,25 @@ int launch_solve(LcPlanner* p, const float* umaps, int n, int warps, int32_t* ks
   attr[1].val.priority = high_priority();
   cfg.attrs = attr;
   cfg.numAttrs = 2;
-  DPV_CUDA(cudaLaunchKernelEx(&cfg, kern, umaps, W, R, (const float*)p->d_theta, (const float*)p->d_xz,
-                              (const uint8_t*)p->d_win, (unsigned long long*)L.d_log, per_map, host_tag, L.d_epoch, ks, xz,
-                              counts));
+  if (pack2)
+    DPV_CUDA(cudaLaunchKernelEx(&cfg, kern2, umaps, W, R, (const float*)p->d_theta, (const float*)p->d_xz,
+                                (const uint8_t*)p->d_win, (unsigned long long*)L.d_log, per_map, host_tag, L.d_epoch, ks,
+                                xz, counts, n, (unsigned)team_smem));
+  else
+    DPV_CUDA(cudaLaunchKernelEx(&cfg, kern, umaps, W, R, (const float*)p->d_theta, (const float*)p->d_xz,
+                                (const uint8_t*)p->d_win, (unsigned long long*)L.d_log, per_map, host_tag, L.d_epoch, ks, xz,
+                                counts));
   return DPV_OK;
 }
 
 }  // namespace
+
+extern "C" int lc_planner_set_pack(LcPlanner* p, int pack) {
+  DPV_REQUIRE(p, "lc_planner_set_pack: null pointer");
+  DPV_REQUIRE(pack == 1 || pack == 2, "lc_planner_set_pack: pack must be 1 or 2, got %d", pack);
+  p->pack = pack;
+  return DPV_OK;
+}
 
 extern "C" int lc_planner_solve(LcPlanner* p, const float* umaps, int n, int32_t* ks, float* xz, int32_t* counts,
                                 void* stream) {

@@ -255,6 +255,11 @@ class PlannerRT:
     def edge_count(self):
         return int(lib().lc_planner_edge_count(self._h))
 
+    def set_pack(self, pack):
+        """Maps per producer / consumer CTA pair (lc_planner_set_pack): 1 = lowest latency, 2 = half the SMs per solve."""
+        check(lib().lc_planner_set_pack(self._h, int(pack)))
+        self.pack = int(pack)
+
     def solve(self, umaps, ks=None, xz=None, counts=None):
         """umaps [n,R,W] CUDA -> (ks [n,W] int32, xz [n,W,2], counts [n] int32)."""
         umaps = f32(umaps, self.device)

@@ -118,11 +118,13 @@ STATIC_KEYS = ("K", "K_up", "R", "t", "rays")
 class DpvLcPipeline:
     """Holds the per-geometry handles (LC device, planner, polar flow) and runs one batch through the path."""
 
-    def __init__(self, meta, device, hit_noise=0.0, sigma=10.0, noise_seed=0):
+    def __init__(self, meta, device, hit_noise=0.0, sigma=10.0, noise_seed=0, planner_pack=1):
         """hit_noise: sigma of the simulator's intensity noise (the reference hard-codes 0.01 for both rigs,
         lc/light_curtain.py:270-285, drawn unseeded inside lcsim; parity tests use 0).  With hit_noise > 0 the draws of
         every LC iteration come from a pool generated once here (iterations x B*nc x H x W, seeded): the step stays
-        free of RNG launches and replays as a CUDA graph, at the cost of seeing the same draws every step."""
+        free of RNG launches and replays as a CUDA graph, at the cost of seeing the same draws every step.
+        planner_pack: maps per CTA pair of the DP planner (lc_planner_set_pack): 1 for the lowest latency of one batch, 2
+        when several batches are in flight and the SMs a solve holds are what it costs (same results)."""
         self.m = meta
         self.device = torch.device(device)
         self.sigma = sigma
@@ -141,6 +143,7 @@ class DpvLcPipeline:
                  "device": self.device, "expand_A": meta["D"], "expand_B": meta["R"], "hit_noise": hit_noise}
             self.lc = LightCurtain()
             self.lc.init(P)
+            self.set_planner_pack(planner_pack)
             nc = 1 + 2 * len(meta["step"])
             self.state = dpv_head.LcLoopState(meta["B"], meta["D"], H, W, meta["R"], nc, self.device)
             self.noise_pool = None
@@ -153,6 +156,10 @@ class DpvLcPipeline:
         self.planner_events = None       # the same for the DP planner solves
         self.lsm_events = None           # the same for the full-resolution log-softmax + statistics launch
         self.trace = None                # optional list: per-iteration uf / umaps / ks / logp clones (parity tests)
+
+    def set_planner_pack(self, pack):
+        if self.m["iterations"] > 0:
+            self.lc.rig("high").planner.set_pack(pack)
 
     def step(self, x):
         """x: dict of CUDA tensors (synthetic_batch layout) -> dict(depth, var, entropy, carry, carry_lc, logp_lc)."""

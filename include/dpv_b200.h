@@ -188,6 +188,13 @@ long long lc_planner_edge_count(const LcPlanner* pl);
  * a given size on its stream: not while that stream is being captured (DPV_EINVAL; run one solve of that size first). */
 int lc_planner_solve(LcPlanner* pl, const float* umaps, int n, int32_t* ks, float* xz, int32_t* counts,
                      void* stream);
+/* How many maps one producer / consumer CTA pair solves (no reference counterpart: a scheduling choice of this
+ * library; results are identical).  1 (default): one map per pair, lowest latency of a solve (n maps hold 2n SMs).
+ * 2: two maps per pair, each CTA running two independent teams of 512 threads -- n maps hold n SMs instead of 2n for
+ * a longer solve (C2 on a B200: 1.15 ms instead of 0.71 ms).  Measured in the bench's throughput mode it does not pay
+ * (a 1024-thread CTA takes its SM's whole register file, so nothing else runs beside it: -1 to -5 %); it is there for
+ * callers that must leave SMs free.  Falls back to 1 where two teams' shared memory does not fit an SM. */
+int lc_planner_set_pack(LcPlanner* pl, int pack);
 
 /* (d4) Curtain image formation.  dprocessor.cpp:995-1067 processPointsT = checkPoints :238-280 ->
  * findCameraIntersectionsOpt :514-634 -> calculateSurface :735-925 -> computeDepthHits :942-993.

@@ -22,10 +22,11 @@ def main():
     B, D, H, W, R, nc = st.shape
     um = st.umaps.view(B * nc, R, W)
     ref = None
-    for cl in (2, 4):
-        for warps in (16, 24, 32):
+    for cl, warps, pack in ((2, 16, 1), (2, 16, 2), (4, 16, 1), (2, 32, 1), (2, 8, 2)):
+        if True:
             os.environ["DPV_PLANNER_LANES"] = str(cl)
             os.environ["DPV_PLANNER_WARPS"] = str(warps)
+            rig.planner.set_pack(pack)
             ks = torch.empty_like(st.ks)
             xz = torch.empty_like(st.xz)
             cnt = torch.empty_like(st.counts)
@@ -44,7 +45,7 @@ def main():
             if ref is None:
                 ref = (ks.clone(), xz.clone(), cnt.clone())
             same = bool((ks == ref[0]).all() and (cnt == ref[2]).all() and torch.equal(xz, ref[1]))
-            print("lanes %d warps %2d : %8.3f ms   same_as_first=%s" % (cl, warps, ts[2], same), flush=True)
+            print("lanes %d warps %2d pack %d : %8.3f ms   same_as_first=%s" % (cl, warps, pack, ts[2], same), flush=True)
 
 
 if __name__ == "__main__":

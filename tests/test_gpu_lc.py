@@ -384,6 +384,14 @@ def test_planner_bit_exact_against_reference_planning_cpp(name):
         k = ks[i, :n].cpu().numpy()
         r = np.hypot(g[name + "_xz"][i, :n, 0].astype(np.float64), g[name + "_xz"][i, :n, 1].astype(np.float64))
         np.testing.assert_allclose(r, ranges[k], rtol=1e-5)
+    # two maps per CTA pair (lc_planner_set_pack(2): two teams of 512 threads per CTA): identical results, also for
+    # an odd number of maps (the last pair's second team has none) and back at one map per pair
+    for pack, sel in ((2, slice(None)), (2, slice(0, 3)), (2, slice(0, 1)), (1, slice(None))):
+        pl.set_pack(pack)
+        ks2, xz2, c2 = pl.solve(cu(g[name + "_maps"][sel]))
+        assert torch.equal(ks2, ks[sel]) and torch.equal(xz2, xz[sel]) and torch.equal(c2, counts[sel]), (pack, sel)
+    with pytest.raises(Exception, match="pack must be 1 or 2"):
+        pl.set_pack(3)
 
 
 def test_planner_one_handle_two_streams_concurrently():
