@@ -281,6 +281,7 @@ namespace dpv {
 
 constexpr int kPlaneThreads = 512;
 constexpr int kPlaneCols = 64;      // columns per CTA (grid.y splits the image width): 4 per warp
+constexpr int kPlaneMaxChunks = 128;  // chunk summaries of the first-hit search (curtains of up to 4097 points; more: no skipping)
 
 __device__ __forceinline__ float point_angle(float x, float z) {
   // -((atan2f(z, x) * 180 / M_PI) - 90) + 0 + 0   (dprocessor.cpp:528-531, 762)
@@ -343,6 +344,40 @@ curtain_planes_kernel(LcDeviceView dv, LcPlaneConsts pc, const float* __restrict
   const bool all_pts = (ngood == 0);            // findCameraIntersectionsOpt :519-523
   if (all_pts) ngood = N;
 
+  // Per chunk of 32 consecutive segments (33 points of the compacted sequence): the range of the points' angles and
+  // whether the angle gate (:557-561) can be decided for the chunk as a whole.  The gate drops a segment when BOTH its
+  // end points are more than `lim` degrees from the column's ray -- unless the two angles are equal.  If every point
+  // of a chunk lies above ray + lim, or every point below ray - lim (fp32 subtraction is monotone, so the chunk's
+  // minimum / maximum decide it for all of them), and no segment has equal or NaN end angles, no segment of the chunk
+  // passes the gate and the chunk cannot hold the first hit: it is skipped without looking at its segments
+  // (points are in front of the camera, z > 0, so the ray's backward half-line meets none of them).
+  // The planner's curtains are ordered by column, so a column's ray meets one or two chunks instead of all of them.
+  __shared__ float s_cmin[kPlaneMaxChunks], s_cmax[kPlaneMaxChunks];
+  __shared__ int s_cflag[kPlaneMaxChunks];
+  const int nchunks = ngood > 1 ? (ngood - 1 + 31) / 32 : 0;
+  const bool chunked = nchunks <= kPlaneMaxChunks;
+  if (chunked) {
+    for (int q = warp; q < nchunks; q += kPlaneThreads / 32) {
+      const int j = q * 32 + lane;
+      float lo = INFINITY, hi = -INFINITY;
+      bool odd = false;                         // a segment whose gate does not depend on the ray: equal or NaN angles
+      if (j + 1 < ngood) {
+        const float pa = ang[all_pts ? j : good[j]], pb = ang[all_pts ? j + 1 : good[j + 1]];
+        odd = !(pa != pb) || pa != pa || pb != pb;
+        lo = fminf(pa, pb);
+        hi = fmaxf(pa, pb);
+      }
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) {
+        lo = fminf(lo, __shfl_xor_sync(0xffffffffu, lo, off));
+        hi = fmaxf(hi, __shfl_xor_sync(0xffffffffu, hi, off));
+      }
+      const unsigned any_odd = __ballot_sync(0xffffffffu, odd);
+      if (lane == 0) { s_cmin[q] = lo; s_cmax[q] = hi; s_cflag[q] = any_odd != 0u; }
+    }
+    __syncthreads();
+  }
+
   // Columns of this CTA: [col0, col1).  Each WARP searches one column at a time: its 32 lanes test 32
   // consecutive segments j, and the lowest hitting lane is exactly the reference's "first j that hits".
   const int col0 = blockIdx.y * kPlaneCols, col1 = min(col0 + kPlaneCols, dv.W);
@@ -357,7 +392,21 @@ curtain_planes_kernel(LcDeviceView dv, LcPlaneConsts pc, const float* __restrict
     float ix = 0.f, iz = 0.f;
     for (int li = 0; li < 2 && !found; li++) {
       const float lim = li == 0 ? 1.f : 100.f;
-      for (int j0 = 0; j0 + 1 < ngood && !found; j0 += 32) {
+      // Chunks in ascending order, 32 chunk summaries per ballot; only the candidates are opened.
+      // pass 0 (lim = 1): a chunk whose points all lie more than a degree to one side of the ray fails the angle
+      // gate as a whole.  Pass 1 (lim = 100, which passes nearly every segment and exists for segments that SPAN the
+      // ray with both ends more than a degree away): such a chunk holds no segment the ray's line can cross -- the
+      // crossing point lies outside the segment by sin(1 deg) of its distance, six orders of magnitude above the
+      // rounding of the test below -- so the same bound skips it.  Without it a column that no segment covers (image
+      // edges outside the curtain) evaluates every segment twice and the CTA waits for it.
+      for (int qb = 0; qb < nchunks && !found; qb += 32) {
+       const int q = qb + lane;
+       bool keep = q < nchunks;
+       if (keep && chunked) keep = s_cflag[q] || !(s_cmin[q] - cam_angle > 1.f || cam_angle - s_cmax[q] > 1.f);
+       unsigned cand = __ballot_sync(0xffffffffu, keep);
+       while (cand && !found) {
+        const int j0 = (qb + __ffs(cand) - 1) * 32;
+        cand &= cand - 1;
         const int j = j0 + lane;
         bool hit = false;
         float qx = 0.f, qz = 0.f;
@@ -392,6 +441,7 @@ curtain_planes_kernel(LcDeviceView dv, LcPlaneConsts pc, const float* __restrict
           iz = __shfl_sync(0xffffffffu, qz, srcl);
           found = true;
         }
+       }
       }
     }
     if (lane == 0) {

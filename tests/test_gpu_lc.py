@@ -140,6 +140,35 @@ def test_curtain_image_bit_exact():
             np.testing.assert_array_equal(img, eimg)
 
 
+def test_curtain_first_hit_search_shapes_bit_exact():
+    """The first-hit segment search of curtain_planes (findCameraIntersectionsOpt, dprocessor.cpp:514-634) skips whole
+    chunks of 32 segments by their angle range; curtains that stress that against the oracle's plain scan at the bench
+    geometry (768 columns): a sparse curtain whose segments SPAN many degrees (found only by the second pass, lim = 100),
+    a zig-zag with non-monotone angles, points that share a ray (equal angles: the gate keeps such segments whatever the
+    ray), repeated points, a curtain covering only part of the field of view (columns with no hit at all), and one with
+    more points than the chunk table holds (no skipping).  Design points and plane coefficients bit for bit."""
+    g = load("planner_ref")
+    name = "bench_768"
+    w, h = [int(v) for v in g[name + "_size"]]
+    dev, odev = _devices(g[name + "_K"], w, h)
+    rng = np.random.default_rng(3)
+    xs = np.linspace(-12., 12., 700)
+    sparse = np.array([[-14., 9.], [-6., 14.], [-1., 7.], [0.5, 7.5], [5., 16.], [13., 8.]], np.float32)
+    zig = np.stack([xs, 10. + 2.5 * np.sin(xs * 3.0) + 0.3 * rng.standard_normal(700)], 1).astype(np.float32)
+    zig = zig[np.argsort(rng.random(700) * 0.05 + np.arange(700) / 700.)]        # locally shuffled order
+    same_ray = np.array([[x, z] for x0 in np.linspace(-5., 5., 60) for x, z in ((x0, 10.), (1.2 * x0, 12.), (x0, 10.))],
+                        np.float32)                                             # equal angles and repeated points
+    part = np.stack([np.linspace(1., 4., 300), np.linspace(8., 11., 300)], 1).astype(np.float32)
+    huge = np.stack([np.linspace(-12., 12., 5000), 9. + np.cos(np.linspace(0., 6., 5000))], 1).astype(np.float32)
+    depth = np.full((h, w), 12.0, np.float32)
+    for what, pts in (("sparse", sparse), ("zigzag", zig), ("same ray", same_ray), ("partial", part), ("5000 points", huge)):
+        planes, design = dev.curtain_planes(cu(pts).unsqueeze(0), want_design=True)
+        _, _, edes, epl = odev.get_return(depth, pts, True, debug=True)
+        np.testing.assert_array_equal(design[0].cpu().numpy(), edes, err_msg=what)
+        np.testing.assert_array_equal(planes[0].cpu().numpy(), epl, err_msg=what)
+    assert (design[0, :, 3] == 1).any()
+
+
 def test_sense_likelihood_golden():
     g = load("light_curtain")
     lc = _golden_lc(g)
