@@ -31,8 +31,9 @@ struct UfArgs {
 
 // convert_flowfield (img_utils.py:343-349) + grid_sample(mode='nearest', align_corners=False):
 // source index for destination index i under a constant flow; -1 = out of bounds (zero fill).
-__device__ __forceinline__ int nearest_src(int i, int n, float flow) {
-  const float step = (float)(2.0 / (double)(n - 1));
+// (`step` = grid_step(n): a double division, taken once per thread, not once per pixel)
+__device__ __forceinline__ float grid_step(int n) { return (float)(2.0 / (double)(n - 1)); }
+__device__ __forceinline__ int nearest_src(int i, int n, float flow, float step) {
   float g = __fsub_rn(__fadd_rn(-1.f, __fmul_rn((float)i, step)), __fmul_rn(flow, step));
   float pix = gs_unnormalize(g, n);
   float r = rintf(pix);
@@ -45,15 +46,18 @@ struct UfCtx {
   const float* mask;   // nullable
   int H, W, pshift;
   float fy, cy, ystart, yend, maxd1, mind, fill;
+  float step_h, step_w;  // grid_step(H), grid_step(W)
 };
 
-// depth_s at (r,c): expectation of the row-shifted DPV (img_utils.py:509-514)
-__device__ __forceinline__ float shifted_depth(const UfCtx& c, int r, int col, float* ms) {
-  int rs = r, cs = col;
-  if (c.pshift != 0) {
-    rs = nearest_src(r, c.H, (float)c.pshift);
-    cs = nearest_src(col, c.W, 0.f);
-  }
+// the column a shifted sample of column `col` reads (a function of the column only: callers hoist it out of their row loop)
+__device__ __forceinline__ int shifted_col(const UfCtx& c, int col) {
+  return c.pshift != 0 ? nearest_src(col, c.W, 0.f, c.step_w) : col;
+}
+
+// depth_s at (r,c): expectation of the row-shifted DPV (img_utils.py:509-514); cs = shifted_col(c, col)
+__device__ __forceinline__ float shifted_depth(const UfCtx& c, int r, int cs, float* ms) {
+  int rs = r;
+  if (c.pshift != 0) rs = nearest_src(r, c.H, (float)c.pshift, c.step_h);
   if (rs < 0 || cs < 0) {
     *ms = 0.f;
     return c.fill;
@@ -62,10 +66,10 @@ __device__ __forceinline__ float shifted_depth(const UfCtx& c, int r, int col, f
   return c.mean[(size_t)rs * c.W + cs];
 }
 
-// forward band mask at (r,c) before quash (img_utils.py:516-530)
-__device__ __forceinline__ float band_mask(const UfCtx& c, int r, int col, float* depth_s) {
+// forward band mask at (r,c) before quash (img_utils.py:516-530); cs = shifted_col(c, c_)
+__device__ __forceinline__ float band_mask(const UfCtx& c, int r, int cs, float* depth_s) {
   float ms;
-  float z = shifted_depth(c, r, col, &ms);
+  float z = shifted_depth(c, r, cs, &ms);
   *depth_s = z;
   float yf = __fdiv_rn(__fsub_rn((float)r, c.cy), c.fy);
   float Y = __fmul_rn(yf, z);
@@ -92,10 +96,14 @@ __device__ __forceinline__ UfCtx make_ctx(const UfArgs& a, int b, float fill) {
   c.ystart = a.prm.ystart; c.yend = a.prm.yend;
   c.maxd1 = a.prm.maxd - 1.f; c.mind = a.prm.mind;
   c.fill = fill;
+  c.step_h = grid_step(a.H);
+  c.step_w = grid_step(a.W);
   return c;
 }
 
-// expectation of a zero-filled log-DPV (p = 1 in every bin): what an out-of-bounds shifted pixel sees
+// expectation of a zero-filled log-DPV (p = 1 in every bin): what an out-of-bounds shifted pixel sees.
+// A sequential sum over D (the reference's order); one thread of the CTA takes it, the others read it after the
+// CTA's first barrier (it was 2 x D instructions in every thread, for eight pixels each).
 __device__ __forceinline__ float zero_fill_depth(const UfArgs& a) {
   float s = 0.f;
   if (a.prm.bv_log)
@@ -115,14 +123,17 @@ ufield_colmin_kernel(UfArgs a, float* __restrict__ cmin) {
   __shared__ float s_min[kUfCols];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, b = blockIdx.z;
   const int x = blockIdx.x * kUfCols + lane;
+  __shared__ float s_fill;
   if (threadIdx.x < kUfCols) s_min[threadIdx.x] = 3.0e38f;
+  if (threadIdx.x == 0) s_fill = zero_fill_depth(a);
   __syncthreads();
-  const UfCtx c = make_ctx(a, b, zero_fill_depth(a));
+  const UfCtx c = make_ctx(a, b, s_fill);
   if (x < a.W) {
     float mx = 3.0e38f;
+    const int cs = shifted_col(c, x);
     for (int y = blockIdx.y * kUfRows + warp; y < min(a.H, (int)(blockIdx.y + 1) * kUfRows); y += kUfWarps) {
       float z;
-      const float m = band_mask(c, y, x, &z);
+      const float m = band_mask(c, y, cs, &z);
       mx = fminf(mx, quash_key(z, m));
     }
     atomic_min_pos(&s_min[lane], mx);
@@ -139,11 +150,15 @@ ufield_mask_kernel(UfArgs a, const float* __restrict__ cmin, unsigned* __restric
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, b = blockIdx.z;
   const int x = blockIdx.x * kUfCols + lane;
   const bool xin = x < W;
+  __shared__ float s_fill;
   if (threadIdx.x < kUfCols) s_cnt[threadIdx.x] = 0;
+  if (threadIdx.x == 0) s_fill = zero_fill_depth(a);
   __syncthreads();
-  const UfCtx c = make_ctx(a, b, zero_fill_depth(a));
+  const UfCtx c = make_ctx(a, b, s_fill);
   // column that mask_back(.,x) looks at (inverse shift samples the forward mask at (ri[y], cs[x]))
-  const int xc = !xin ? -1 : (c.pshift != 0 ? nearest_src(x, W, 0.f) : x);
+  const int xc = !xin ? -1 : (c.pshift != 0 ? nearest_src(x, W, 0.f, c.step_w) : x);
+  // ... and the columns the forward masks at x and at xc read in turn (column-only: out of the row loop)
+  const int cs_x = xin ? shifted_col(c, x) : -1, cs_xc = xc >= 0 ? shifted_col(c, xc) : -1;
   float qx = 0.f, qc = 0.f;
   if (a.prm.quash) {
     if (xin) qx = cmin[(size_t)b * W + x];
@@ -154,7 +169,7 @@ ufield_mask_kernel(UfArgs a, const float* __restrict__ cmin, unsigned* __restric
     float mback = 0.f;
     if (xin) {
       float z;
-      float m = band_mask(c, y, x, &z);
+      float m = band_mask(c, y, cs_x, &z);
       if (a.prm.quash) {                                          // img_utils.py:537-539
         const float cl = quash_key(z, m);
         m = m * ((cl > qx - 1.0f && cl < qx + 1.0f) ? 1.f : 0.f);
@@ -162,10 +177,10 @@ ufield_mask_kernel(UfArgs a, const float* __restrict__ cmin, unsigned* __restric
       cnt += (m != 0.f);
       // img_utils.py:541-545: mask_back = grid_sample(mask, inverse shift, nearest)
       int ry = y;
-      if (c.pshift != 0) ry = nearest_src(y, H, -(float)c.pshift);
+      if (c.pshift != 0) ry = nearest_src(y, H, -(float)c.pshift, c.step_h);
       if (ry >= 0 && xc >= 0) {
         float zz;
-        float m2 = band_mask(c, ry, xc, &zz);
+        float m2 = band_mask(c, ry, cs_xc, &zz);
         if (a.prm.quash) {
           const float cl = quash_key(zz, m2);
           m2 = m2 * ((cl > qc - 1.0f && cl < qc + 1.0f) ? 1.f : 0.f);

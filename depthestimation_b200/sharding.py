@@ -21,6 +21,9 @@ def init_from_env(n_gpus=1, backend=None):
         kw = {}
         if backend == "nccl":
             kw["device_id"] = torch.device("cuda", local)
+            # NCCL's own banner / debug lines ("NCCL version ...", printed when the environment sets NCCL_DEBUG) go to
+            # stderr: a caller's stdout (bench.py: ONE JSON line) stays its own
+            os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group(backend, rank=rank, world_size=world, **kw)
     return rank, world, local
 
