@@ -24,6 +24,18 @@ if ROOT not in sys.path:
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    data = (line + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(line + "\n")
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 METRIC = "DPV+LC-fusion frames/sec"
 UNIT = "frames/s"
 
@@ -437,7 +449,7 @@ def run_b200(args):
                 "single_batch_note": "latency of ONE batch of %d frame(s) through the whole step, nothing else in "
                                      "flight (eager launches)" % B,
                 "step_spread_ms": step_spread, "ms_per_step_by_rank": ms_ranks}
-        print(json.dumps(line))
+        emit(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
@@ -524,11 +536,16 @@ def run_reference(args):
                              "sample": "each step = 1 frame of the workload through oracle/ (serial over batch like the "
                                        "reference, models.py:984)"},
             "e2e": {"value": round(v, 5), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(json.dumps(line))
 
 
 if __name__ == "__main__":
     a = parse()
+    # stdout carries ONE JSON line: whatever libraries print there (NCCL's version banner does, on rank 0, when the
+    # environment sets NCCL_DEBUG) goes to stderr instead; emit() writes the line to the real stdout
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if a.impl == "reference":
         run_reference(a)
     else:

@@ -61,27 +61,38 @@ class FrameOutputCollector:
     every rank, and 40 per-step gathers cost 8 % (efficiency 0.92), one gather after the last step 4 % (0.958), none at
     all 0.8 % (0.992).  A round is issued when every stream has finished its step, i.e. when the ranks are nearly in
     phase.  chunk = 0: a single all_gather in finish().  On CPU tensors (gloo tests) always a single all_gather in
-    finish().  Every rank must add() the same steps in the same order."""
+    finish().  Every rank must add() the same steps in the same order.
+
+    Result layout: finish() -> {key: [world, rounds, steps_per_round, B, H, W]}; step s of rank r is
+    res[key][r, s // steps_per_round, s % steps_per_round] (at(res[key], s) gives [world, B, H, W]).  It is a VIEW of
+    round-major storage [rounds, world, steps_per_round, ...]: a round's all_gather writes its final place directly
+    (a rank-major [world, n_steps, ...] result would need a second pass over everything received -- at N = 8 that
+    copy was as much HBM traffic as the gather itself).  Entries past the last step of a partial last round are
+    unspecified."""
 
     def __init__(self, n_steps, world, keys=("depth", "depth_lc"), chunk=0):
         self.n_steps, self.world, self.keys = n_steps, world, keys
         self.buf, self.full = {}, {}
         self.count = 0
         self.chunk = int(chunk) if chunk and chunk < n_steps else 0
+        self.per_round = self.chunk if self.chunk else n_steps
+        self.rounds = (n_steps + self.per_round - 1) // self.per_round
         self.comm = None                # side stream of the per-round gathers
         self.pending = []               # events of the steps added since the last gather
         self.done = 0                   # steps already handed to a gather
 
+    def at(self, gathered, step):
+        """[world, rounds, steps_per_round, ...] -> the maps of one step on every rank, [world, ...]."""
+        return gathered[:, step // self.per_round, step % self.per_round]
+
     def _alloc(self, k, t):
-        self.buf[k] = torch.empty((self.n_steps,) + tuple(t.shape), device=t.device, dtype=t.dtype)
+        # rank-local maps, padded to whole rounds so that every round's slice is a full, contiguous block
+        self.buf[k] = torch.empty((self.rounds * self.per_round,) + tuple(t.shape), device=t.device, dtype=t.dtype)
         if self.world > 1 and t.is_cuda:
-            # [rank, step, ...] as the result wants it; a round's gather lands in a staging block [rank, chunk, ...]
-            self.full[k] = torch.empty((self.world, self.n_steps) + tuple(t.shape), device=t.device, dtype=t.dtype)
-            if self.chunk:
-                self.stage = getattr(self, "stage", {})
-                self.stage[k] = torch.empty((self.world, self.chunk) + tuple(t.shape), device=t.device, dtype=t.dtype)
-                if self.comm is None:
-                    self.comm = torch.cuda.Stream(t.device)
+            self.full[k] = torch.empty((self.rounds, self.world, self.per_round) + tuple(t.shape), device=t.device,
+                                       dtype=t.dtype)
+            if self.chunk and self.comm is None:
+                self.comm = torch.cuda.Stream(t.device)
 
     def reserve(self, out):
         """Allocates every buffer for outputs shaped like `out` now (so that no cudaMalloc -- which synchronises the
@@ -97,24 +108,18 @@ class FrameOutputCollector:
         self.count, self.done, self.pending = 0, 0, []
         return self
 
-    def _gather_round(self, lo, hi):
-        """all_gather of steps [lo, hi) on the side stream, behind the events of those steps."""
+    def _gather_round(self, rnd):
+        """all_gather of round `rnd` (its whole slice, also when the last round is only partly filled) on the side
+        stream, behind the events of its steps, straight into its final place."""
+        lo = rnd * self.per_round
         with torch.cuda.stream(self.comm):
             for ev in self.pending:
                 self.comm.wait_event(ev)
             for k in self.buf:
-                if k not in self.full:
-                    continue
-                n = hi - lo
-                stage = self.stage[k][:, :n] if n == self.chunk else torch.empty(
-                    (self.world, n) + tuple(self.buf[k].shape[1:]), device=self.buf[k].device, dtype=self.buf[k].dtype)
-                if n == self.chunk:
-                    dist.all_gather_into_tensor(self.stage[k], self.buf[k][lo:hi])
-                else:
-                    dist.all_gather_into_tensor(stage, self.buf[k][lo:hi])
-                self.full[k][:, lo:hi].copy_(stage, non_blocking=True)      # [rank, round] -> [rank, step]
+                if k in self.full:
+                    dist.all_gather_into_tensor(self.full[k][rnd], self.buf[k][lo:lo + self.per_round])
         self.pending = []
-        self.done = hi
+        self.done = min(lo + self.per_round, self.n_steps)
 
     def add(self, out):
         """Copies this step's maps into the rank-local buffer (on the current stream); closes a round when it is full."""
@@ -133,26 +138,30 @@ class FrameOutputCollector:
             ev = torch.cuda.Event()
             ev.record()                                                # on the step's stream, after the copies
             self.pending.append(ev)
-            if self.count - self.done >= self.chunk:
-                self._gather_round(self.done, self.count)
+            if self.count - self.done >= self.per_round:
+                self._gather_round(self.done // self.per_round)
 
     def finish(self):
-        """-> {key: [world, n_steps, B, H, W]} on every rank; rank-local view if world = 1."""
+        """-> {key: [world, rounds, steps_per_round, B, H, W]} on every rank (world = 1: the rank-local maps)."""
         res = {}
         if self.comm is not None:
             if self.count > self.done:
-                self._gather_round(self.done, self.count)             # a last, partial round
+                self._gather_round(self.done // self.per_round)       # a last, partial round
             torch.cuda.current_stream(self.comm.device).wait_stream(self.comm)
         for k, t in self.buf.items():
+            shape = (self.rounds, self.per_round) + tuple(t.shape[1:])
             if self.world <= 1:
-                res[k] = t.unsqueeze(0)
+                res[k] = t.view((1,) + shape)
             elif self.comm is not None and k in self.full:
-                res[k] = self.full[k]
+                res[k] = self.full[k].permute(1, 0, *range(2, self.full[k].dim()))
             else:
-                full = self.full[k].view((self.world * t.shape[0],) + tuple(t.shape[1:])) if k in self.full else \
-                    torch.empty((self.world * t.shape[0],) + tuple(t.shape[1:]), device=t.device, dtype=t.dtype)
-                dist.all_gather_into_tensor(full, t)                   # concatenated along dim 0 (gloo needs this form)
-                res[k] = full.view((self.world,) + tuple(t.shape))
+                if k in self.full:                                     # CUDA, chunk = 0: one round
+                    dist.all_gather_into_tensor(self.full[k][0], t)
+                    res[k] = self.full[k].permute(1, 0, *range(2, self.full[k].dim()))
+                else:                                                  # CPU tensors (gloo): concatenated along dim 0
+                    flat = torch.empty((self.world * t.shape[0],) + tuple(t.shape[1:]), device=t.device, dtype=t.dtype)
+                    dist.all_gather_into_tensor(flat, t)
+                    res[k] = flat.view((self.world,) + shape)
         return res
 
 

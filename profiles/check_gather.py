@@ -32,8 +32,10 @@ for chunk in (0, 1, 3, 5):
         res = coll.finish()
         torch.cuda.synchronize(dev)
         for k, add in (("depth", 0.0), ("depth_lc", 0.5)):
-            got = res[k]
-            assert tuple(got.shape) == (world, n_steps, 2, 4, 6), got.shape
+            got = res[k]                                    # [world, rounds, steps per round, ...] (a view)
+            assert tuple(got.shape) == (world, coll.rounds, coll.per_round, 2, 4, 6), got.shape
+            assert torch.equal(coll.at(got, 7), got[:, 7 // coll.per_round, 7 % coll.per_round])
+            got = got.reshape(world, coll.rounds * coll.per_round, 2, 4, 6)[:, :n_steps]
             exp = torch.tensor([[1000.0 * r + 10 * i + rep + add for i in range(n_steps)] for r in range(world)], device=dev)
             good = bool((got[:, :, 0, 0, 0] == exp).all()) and bool((got == got[:, :, :1, :1, :1]).all())
             ok = ok and good

@@ -37,7 +37,8 @@ def _worker(rank, world, port, n_items, q):
         coll.add({"depth": pad + 100.0 * step + 1000.0 * r, "depth_lc": None})
     full = coll.finish()
     q.put((r, lo, hi, out["depth"][:, 0, 0].tolist(), sorted(out.keys()),
-           tuple(full["depth"].shape), full["depth"][:, :, 0, 0, 0].tolist(), sorted(full.keys())))
+           tuple(full["depth"].shape), torch.stack([coll.at(full["depth"], s)[:, 0, 0, 0] for s in range(3)], 1).tolist(),
+           sorted(full.keys())))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -60,7 +61,7 @@ def test_shard_and_gather_world2():
         got = [v for v in r[3] if v >= 0]
         assert got == [float(i) for i in range(n_items)]        # every rank holds every frame, in shard order
         assert r[4] == ["depth"]
-        assert r[5] == (world, 3, 4, 2, 3) and r[7] == ["depth"]
+        assert r[5] == (world, 1, 3, 4, 2, 3) and r[7] == ["depth"]       # [rank, round, step in round, frames, H, W]
         # [rank, step] -> first frame of that rank's shard + 100*step + 1000*rank
         assert r[6] == [[0.0, 100.0, 200.0], [1004.0, 1104.0, 1204.0]]
 
