@@ -582,7 +582,12 @@ def test_plan_m1_against_reference_golden_and_oracle():
     assert len(seq) == len(pts) + 1 and torch.equal(seq[0], seq[1])
     for a, b in zip(seq[1:], pts):
         assert torch.equal(a, b)
-    # a larger field (quarter-resolution rig too) against the oracle under one seed
+    # the quarter-resolution rig (plan_m1_low, light_curtain.py:384-385): 16 columns, every fifth sampled
+    np.random.seed(1)
+    low, vis_low = lc.plan_m1_low(uf[:, ::4].contiguous(), cfg)
+    assert len(low) == len(pts) and all(p.shape[1] == 2 and 0 < p.shape[0] <= W // 4 for p in low)
+    assert vis_low.shape == (len(g["d_candi_up"]), W // 4, 3)
+    # a larger field against the oracle under one seed
     gl = load("light_curtain")
     lc2 = _golden_lc(gl)
     Hh, Ww = gl["logp"].shape[2:]
