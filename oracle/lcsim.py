@@ -39,6 +39,8 @@ def lib():
         L.lco_device_destroy.argtypes = [ctypes.c_void_p]
         L.lco_device_angles.argtypes = [ctypes.c_void_p, c_fp]
         L.lco_device_lut.argtypes = [ctypes.c_void_p, c_fp]
+        L.lco_device_rays.argtypes = [ctypes.c_void_p, c_fp, c_fp]
+        L.lco_device_ztoramap.argtypes = [ctypes.c_void_p, c_fp]
         L.lco_get_return.restype = ctypes.c_int
         L.lco_get_return.argtypes = [ctypes.c_void_p, c_fp, c_fp, ctypes.c_int, c_fp, c_fp, c_fp, c_fp, c_fp]
         L.lco_planner_create.restype = ctypes.c_void_p
@@ -129,6 +131,17 @@ class LCDevice:
     def hit_lut(self):
         out = np.zeros(1000, np.float32)
         lib().lco_device_lut(self._h, _p(out))
+        return out
+
+    def rays(self):
+        """(nn_x [W], nn_y [H]): the un-normalised pixel rays (x, y, 1) of createNormalMap."""
+        nx, ny = np.zeros(self.W, np.float32), np.zeros(self.H, np.float32)
+        lib().lco_device_rays(self._h, _p(nx), _p(ny))
+        return nx, ny
+
+    def ztoramap(self):
+        out = np.zeros((self.H, self.W), np.float32)
+        lib().lco_device_ztoramap(self._h, _p(out))
         return out
 
     def get_return(self, np_depth_image, np_design_pts, get_thickness=False, noise=None, debug=False):

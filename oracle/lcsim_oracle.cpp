@@ -530,6 +530,12 @@ LcoDevice* lco_device_create(int W, int H, const float* K, const float* lTc, flo
 void lco_device_destroy(LcoDevice* d) { delete d; }
 void lco_device_angles(const LcoDevice* d, float* out) { std::memcpy(out, d->valid_angles.data(), sizeof(float) * d->W); }
 void lco_device_lut(const LcoDevice* d, float* out) { std::memcpy(out, d->hit_lut.data(), sizeof(float) * d->hit_N); }
+// the per-pixel tables the curtain return reads (for the pin against the reference's own functions, oracle/ref_hits.py)
+void lco_device_rays(const LcoDevice* d, float* nn_x, float* nn_y) {
+    std::memcpy(nn_x, d->nn_x.data(), sizeof(float) * d->W);
+    std::memcpy(nn_y, d->nn_y.data(), sizeof(float) * d->H);
+}
+void lco_device_ztoramap(const LcoDevice* d, float* out) { std::memcpy(out, d->ztoramap.data(), sizeof(float) * (size_t)d->W * d->H); }
 
 // processPointsT (dprocessor.cpp:995-1038) via LCDevice.get_return (python/sim.py:168-211).
 // pts [N,2] (x,z); depth [H,W]; noise nullable [H,W]; image [H,W,4]; thick [H,W];

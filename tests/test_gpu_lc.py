@@ -140,6 +140,25 @@ def test_curtain_image_bit_exact():
             np.testing.assert_array_equal(img, eimg)
 
 
+@pytest.mark.parametrize("mode", [0, 1])
+def test_curtain_return_matches_reference_functions(mode):
+    """LCDevice.get_return against the images the reference's OWN Util::intersect + computeDepthHits produce
+    (util.cpp:47-53, dprocessor.cpp:942-993 compiled from where they lie, tests/golden/hits_ref.npz): surface points,
+    thickness and the quantised hit intensity of every pixel, three curtains, NaN depth pixels, both hit modes."""
+    from depthestimation_b200 import lcsim
+    g = load("hits_ref")
+    H, W = g["depth"].shape
+    cp = dict(width=W, height=H, matrix=g["Kup"], distortion=[0.] * 5, hit_mode=mode, hit_noise=0.)
+    dev = lcsim.LCDevice(CAMERA_PARAMS=cp, LASER_PARAMS=dict(lTc=_lTc(), fov=80., laser_timestep=3.5e-5))
+    np.testing.assert_array_equal(dev.hit_lut(), g["lut"])
+    for i in range(3):
+        img, th = dev.get_return(g["depth"], g["pts%d" % i], True)
+        planes = dev.curtain_planes(cu(g["pts%d" % i]).unsqueeze(0))
+        np.testing.assert_array_equal(planes[0].cpu().numpy(), g["planes%d" % i])
+        np.testing.assert_array_equal(img, g["image%d_mode%d" % (i, mode)], err_msg="curtain %d" % i)
+        np.testing.assert_array_equal(th, g["thick%d" % i])
+
+
 def test_curtain_first_hit_search_shapes_bit_exact():
     """The first-hit segment search of curtain_planes (findCameraIntersectionsOpt, dprocessor.cpp:514-634) skips whole
     chunks of 32 segments by their angle range; curtains that stress that against the oracle's plain scan at the bench

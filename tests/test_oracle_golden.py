@@ -2,6 +2,7 @@
 (tests/golden/make_golden.py, run in the build container) and against the one known-answer
 fixture the reference ships for lcsim (example/dpv.npy['angles'])."""
 import os
+import sys
 
 import numpy as np
 import pytest
@@ -414,3 +415,49 @@ def test_lc_loop_real_oracle_matches_reference_golden():
                           {"step": 2, "interval": 6}, 1, 5)
     np.testing.assert_array_equal(out.numpy(), g["fused_m1"])
     assert np.abs(g["fused_default"] - g["logp"]).max() > 1.0          # the sweep did change the volume
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# a13 (part): the per-pixel curtain return pinned to the reference's own Util::intersect and computeDepthHits
+# (oracle/ref_hits.py -> tests/golden/hits_ref.npz)
+# ---------------------------------------------------------------------------------------------------------------
+def _hits_device(g, mode):
+    from oracle import lcsim as olcsim
+    H, W = g["depth"].shape
+    lTc = np.eye(4, dtype=np.float32)
+    lTc[0, 3] = 0.2
+    cp = dict(width=W, height=H, matrix=g["Kup"], distortion=[0.] * 5, hit_mode=mode, hit_noise=0.)
+    return olcsim.LCDevice(CAMERA_PARAMS=cp, LASER_PARAMS=dict(lTc=lTc, fov=80., laser_timestep=3.5e-5))
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_oracle_curtain_return_matches_reference_functions(mode):
+    """The restated simulator's surface point, thickness and quantised hit intensity of every pixel against what the
+    reference's own Util::intersect + computeDepthHits produce from the same plane coefficients, pixel rays, z-to-range
+    map, look-up table and depth image (three curtains, NaN depth pixels, both hit modes): bit for bit.  The tables are
+    the restated device model's own (checked equal to the stored inputs): their Eigen arithmetic stays unpinned."""
+    g = np.load(os.path.join(G, "hits_ref.npz"))
+    dev = _hits_device(g, mode)
+    nx, ny = dev.rays()
+    np.testing.assert_array_equal(nx, g["nn_x"])
+    np.testing.assert_array_equal(ny, g["nn_y"])
+    np.testing.assert_array_equal(dev.ztoramap(), g["ztoramap"])
+    np.testing.assert_array_equal(dev.hit_lut(), g["lut"])
+    for i in range(3):
+        img, th, _, planes = dev.get_return(g["depth"], g["pts%d" % i], True, debug=True)
+        np.testing.assert_array_equal(planes, g["planes%d" % i])
+        np.testing.assert_array_equal(img, g["image%d_mode%d" % (i, mode)], err_msg="curtain %d" % i)
+        np.testing.assert_array_equal(th, g["thick%d" % i])
+        assert (img[..., 3] > 0).sum() > 100 and np.isnan(img[..., 0]).any()
+
+
+def test_hits_golden_is_what_the_reference_produces_now():
+    from oracle import ref_hits
+    if not ref_hits.available():
+        pytest.skip("/root/reference is not on this machine")
+    sys.path.insert(0, G)
+    import make_hits_ref
+    g = np.load(os.path.join(G, "hits_ref.npz"))
+    img, unc = make_hits_ref.reference_return(g["planes1"], g["nn_x"], g["nn_y"], g["depth"], g["ztoramap"], g["lut"], 1)
+    np.testing.assert_array_equal(img, g["image1_mode1"])
+    np.testing.assert_array_equal(unc, g["thick1"])
