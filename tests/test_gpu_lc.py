@@ -554,8 +554,9 @@ def test_plan_m1_against_reference_golden_and_oracle():
     same numpy stream and the field only as probabilities, so they are the same unless a uniform variate falls within
     1e-6 of a CDF step; the spline is bit-exact given the draws (tests/test_host_cpu.py).  The DP then runs on maps that
     differ in the last bits: a near-tie between two paths may resolve differently and shift a stretch of columns.
-    Bar: the main curtain identical; every sampled round at least 90 % of the columns identical and the rest within
-    two range bins."""
+    Bar: the main curtain identical; every sampled round at least 98 % of the columns identical and the rest within
+    two range bins (measured on a B200 over nine seeds and both fields, profiles/diag_m1.py: every curtain identical
+    in every column)."""
     from depthestimation_b200.lc.light_curtain import LightCurtain
     from oracle import lc_oracle as LO
     g = load("plan_m1")
@@ -584,7 +585,7 @@ def test_plan_m1_against_reference_golden_and_oracle():
         if exact:
             assert same.all(), (what, same.mean())
             return
-        assert same.mean() >= 0.9, (what, same.mean())
+        assert same.mean() >= 0.98, (what, same.mean())
         r_got = np.hypot(got[:, 0], got[:, 1])
         r_ref = np.hypot(ref[:, 0], ref[:, 1])
         assert np.all(np.abs(np.digitize(r_got, d_up) - np.digitize(r_ref, d_up)) <= 2), what
