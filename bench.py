@@ -372,6 +372,18 @@ def run_b200(args):
     set_kernel_events(False)
     pipe.set_planner_pack(pack)
     graphs = replay
+    # the same, replaying slot 0's captured graph alone (what a caller with one batch and a captured step gets)
+    single_batch_graph_ms = None
+    if graphs is not None and pack == 1:
+        with torch.cuda.stream(streams[0]):
+            graphs[0][0].replay()
+            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            g0.record()
+            for _ in range(3):
+                graphs[0][0].replay()
+            g1.record()
+        torch.cuda.synchronize(dev)
+        single_batch_graph_ms = g0.elapsed_time(g1) / 3
 
     # ---- e2e: host buffers in, host results out, copies inside the timed region ------------------
     e2e = None
@@ -448,6 +460,7 @@ def run_b200(args):
                 "ms_per_frame": round(ms_per_step / B, 4), "single_batch_ms": round(single_batch_ms, 4),
                 "single_batch_note": "latency of ONE batch of %d frame(s) through the whole step, nothing else in "
                                      "flight (eager launches)" % B,
+                "single_batch_graph_ms": None if single_batch_graph_ms is None else round(single_batch_graph_ms, 4),
                 "step_spread_ms": step_spread, "ms_per_step_by_rank": ms_ranks}
         emit(json.dumps(line))
     if world > 1:
