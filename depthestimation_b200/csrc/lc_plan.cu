@@ -343,17 +343,22 @@ plan_prep_warp_kernel(const float* __restrict__ field_pre, const float* __restri
   const int pk = amax[lane];
   const int nmaps = 1 + 2 * steps.n;
   float* out = umaps + (size_t)b * nmaps * R * W;
-  for (int r = warp; r < R; r += kWarpWarps) {
-    const float v = fr[r * kPrepCols + lane];
-    out[(size_t)r * W + x] = v;
-    const float left = (r < pk) ? 1.f : v;        // left_field[rows < idx] = 1
-    const float right = (r >= pk) ? 1.f : v;      // right_field[rows >= idx] = 1
-    for (int s = 0; s < steps.n; s++) {
-      const float p = steps.p[s], q = 1.f - p;
-      float il = (pow_like_torch(left, p) * pow_like_torch(1.f - left, q)) / steps.den[s];
-      float ir = (pow_like_torch(right, p) * pow_like_torch(1.f - right, q)) / steps.den[s];
-      out[((size_t)(1 + 2 * s) * R + r) * W + x] = il;
-      out[((size_t)(2 + 2 * s) * R + r) * W + x] = ir;
+  // invert(x, p) = x^p (1 - x)^(1 - p) / (p^p (1 - p)^(1 - p))  (light_curtain.py:221-225).  Each row is 1 on one side
+  // of the peak (left_field[rows < idx] = 1, right_field[rows >= idx] = 1) and the field on the other, so one of the
+  // two inverted values per row is invert(1, p) -- the same expression on constants, taken once per step -- and only
+  // the other needs the two powers.
+  for (int r = warp; r < R; r += kWarpWarps) out[(size_t)r * W + x] = fr[r * kPrepCols + lane];
+  for (int s = 0; s < steps.n; s++) {
+    const float p = steps.p[s], q = 1.f - p, den = steps.den[s];
+    const float inv_one = (pow_like_torch(1.f, p) * pow_like_torch(1.f - 1.f, q)) / den;
+    float* outl = out + (size_t)(1 + 2 * s) * R * W + x;
+    float* outr = out + (size_t)(2 + 2 * s) * R * W + x;
+    for (int r = warp; r < R; r += kWarpWarps) {
+      const float v = fr[r * kPrepCols + lane];
+      const float iv = (pow_like_torch(v, p) * pow_like_torch(1.f - v, q)) / den;
+      const bool left_is_one = r < pk;            // then right = v; else left = v, right = 1
+      outl[(size_t)r * W] = left_is_one ? inv_one : iv;
+      outr[(size_t)r * W] = left_is_one ? iv : inv_one;
     }
   }
 }
