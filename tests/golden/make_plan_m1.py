@@ -185,9 +185,20 @@ def lc_process_real_case():
     fused_m1, _ = MM.BaseModel.lc_process_real(me, logp.clone(), model_input(), algo, real, iterations=1,
                                                planner="m1", params=prm_m1)
     IU.spread_kernel = None
+    # planner "sweep" (flat curtains at 8, 14, 20 m) on the recorded sweep, and the SIMULATED loop BaseModel.lc_process with
+    # planner "m1" (models.py:1052-1053) on the same RGB rig, seeded
+    prm_sw = ref_shim.AttrDict({"start": 8.0, "end": 24.0, "step": 6.0, "spread_iter": 1, "spread_n": 5})
+    fused_sweep, _ = MM.BaseModel.lc_process_real(me, logp.clone(), model_input(), algo, real, iterations=1,
+                                                  planner="sweep", params=prm_sw)
+    IU.spread_kernel = None
+    np.random.seed(23)
+    fused_sim_m1, _ = MM.BaseModel.lc_process(me, logp.clone(), model_input(), algo, mode="high", iterations=2,
+                                              planner="m1", params=prm_m1)
+    IU.spread_kernel = None
     out = dict(logp=logp.numpy(), sweep=sweep.numpy(), dmaps=dm.numpy(), d_candi=np.asarray(d, np.float32),
                d_candi_up=np.asarray(d_up, np.float32), K_rgb=K_rgb, K_lc=K_lc, rTc=rTc, size_rgb=[Wr, Hr],
-               size_lc=[Wl, Hl], fused_default=fused_default.numpy(), fused_m1=fused_m1.numpy(), seed_m1=19)
+               size_lc=[Wl, Hl], fused_default=fused_default.numpy(), fused_m1=fused_m1.numpy(), seed_m1=19,
+               fused_sweep=fused_sweep.numpy(), fused_sim_m1=fused_sim_m1.numpy(), seed_sim_m1=23)
     np.savez_compressed(os.path.join(HERE, "lc_process_real.npz"), **out)
     print("wrote lc_process_real", {k: np.shape(v) for k, v in out.items()})
 

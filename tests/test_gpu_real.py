@@ -369,6 +369,9 @@ def test_lc_process_real_against_reference_golden():
     fused_m1, _ = dpv_head.lc_process_real(logp, mi, algo, real, iterations=1, planner="m1",
                                            params={"step": 2, "interval": 6, "spread_iter": 1, "spread_n": 5})
     _volume_close(fused_m1.cpu().numpy(), g["fused_m1"], "m1")
+    fused_sw, _ = dpv_head.lc_process_real(logp, mi, algo, real, iterations=1, planner="sweep",
+                                           params={"start": 8.0, "end": 24.0, "step": 6.0, "spread_iter": 1, "spread_n": 5})
+    _volume_close(fused_sw.cpu().numpy(), g["fused_sweep"], "sweep")
     # two samples at once give each sample's own result
     mi2 = {k: torch.cat([v, v]) for k, v in mi.items()}
     both, _ = dpv_head.lc_process_real(torch.cat([logp, logp]), mi2, algo, real, iterations=2, planner="default",
@@ -397,6 +400,10 @@ def test_lc_process_m1_planner_against_oracle():
     dm = torch.as_tensor(g["dmaps"])
     mi = {"intrinsics_up": torch.as_tensor(g["K_rgb"]).unsqueeze(0), "dmaps": dm.unsqueeze(0)}
     prm = {"step": 2, "interval": 6, "spread_iter": 1, "spread_n": 5}
+    # the unmodified reference's own run of this loop under its seed (tests/golden/lc_process_real.npz)
+    np.random.seed(int(g["seed_sim_m1"]))
+    fused_ref_seed, _ = dpv_head.lc_process(logp.cuda(), mi, algo, mode="high", iterations=2, planner="m1", params=prm)
+    _volume_close(fused_ref_seed.cpu().numpy(), g["fused_sim_m1"], "lc_process m1 vs reference")
     np.random.seed(3)
     fused, _ = dpv_head.lc_process(logp.cuda(), mi, algo, mode="high", iterations=2, planner="m1", params=prm)
     olc = LO.LightCurtainOracle(g["K_rgb"], Wr, Hr, g["d_candi"], g["d_candi_up"])

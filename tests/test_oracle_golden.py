@@ -415,6 +415,19 @@ def test_lc_loop_real_oracle_matches_reference_golden():
                           {"step": 2, "interval": 6}, 1, 5)
     np.testing.assert_array_equal(out.numpy(), g["fused_m1"])
     assert np.abs(g["fused_default"] - g["logp"]).max() > 1.0          # the sweep did change the volume
+    out = LO.lc_loop_real(logp, g["sweep"], algo, real, g["K_rgb"], O.uf_params("kitti"), 1, "sweep",
+                          {"start": 8.0, "end": 24.0, "step": 6.0}, 1, 5)
+    np.testing.assert_array_equal(out.numpy(), g["fused_sweep"])       # flat curtains at 8 / 14 / 20 m
+    # the SIMULATED loop with planner "m1": the unmodified BaseModel.lc_process (models.py:1052-1053), two iterations
+    dm = torch.as_tensor(g["dmaps"])
+    dm_up = torch.nn.functional.interpolate(dm.reshape(1, 1, *dm.shape), scale_factor=4, mode="nearest")[0, 0].numpy()
+    K, final = torch.as_tensor(g["K_rgb"]), logp.clone()
+    np.random.seed(int(g["seed_sim_m1"]))
+    for _ in range(2):
+        uf, _u = O.ufield(final, algo.d_candi, K, O.uf_params("kitti"), BV_log=True)
+        paths, _v = algo.plan_m1(uf.squeeze(0), {"step": 2, "interval": 6})
+        final = O.bayes_fuse(final, [algo.sense(dm_up, p)[0] for p in paths], 1, 5)
+    np.testing.assert_array_equal(final.numpy(), g["fused_sim_m1"])
 
 
 # ---------------------------------------------------------------------------------------------------------------
